@@ -203,3 +203,103 @@ def ulp_diff(a, b):
     d[both_nan] = 0
     d[one_nan] = np.inf
     return d
+
+
+# ---------------------------------------------------------------------------------------------
+# plain-C restatement (oracle/baobzi_oracle.c)
+# ---------------------------------------------------------------------------------------------
+ARITH_GENERIC, ARITH_AVX, ARITH_AVX2, ARITH_AVX512 = 0, 1, 2, 3
+ARITH_FMA = ARITH_AVX2
+ARITH_OF_ARCH = {"generic": ARITH_GENERIC, "avx": ARITH_AVX, "avx2": ARITH_AVX2, "avx512": ARITH_AVX512}
+
+
+class OracleTreeStruct(C.Structure):
+    """oracle_tree_t (oracle/baobzi_oracle.h)."""
+    _fields_ = [("dim", C.c_int), ("order", C.c_int), ("output_dim", C.c_int), ("split_multi_eval", C.c_int),
+                ("tol", C.c_double),
+                ("box_center", C.c_double * 3), ("box_inv_half_length", C.c_double * 3),
+                ("lower_left", C.c_double * 3), ("upper_right", C.c_double * 3), ("inv_bin_size", C.c_double * 3),
+                ("n_subtrees", C.c_int * 3),
+                ("n_bins", C.c_int64), ("n_nodes", C.c_int64), ("n_leaves", C.c_int64), ("n_coeffs", C.c_int64),
+                ("subtree_node_offsets", C.POINTER(C.c_int32)),
+                ("center", c_double_p), ("inv_half_length", c_double_p),
+                ("first_child_idx", C.POINTER(C.c_uint32)), ("coeff_offset", C.POINTER(C.c_uint64)),
+                ("node_output_dim", C.POINTER(C.c_uint32)), ("coeffs", c_double_p)]
+
+
+def oracle_lib():
+    if "oracle" not in _cache:
+        lib = C.CDLL(ORACLE_SO)
+        P = C.POINTER(OracleTreeStruct)
+        lib.oracle_restore.restype = P
+        lib.oracle_restore.argtypes = [C.c_char_p]
+        lib.oracle_free.restype = None
+        lib.oracle_free.argtypes = [P]
+        lib.oracle_node_index_multi.restype = None
+        lib.oracle_node_index_multi.argtypes = [P, c_double_p, C.c_int64, C.POINTER(C.c_int64)]
+        lib.oracle_eval_multi.restype = None
+        lib.oracle_eval_multi.argtypes = [P, c_double_p, c_double_p, C.c_int64, C.c_int]
+        lib.oracle_eval.restype = None
+        lib.oracle_eval.argtypes = [P, c_double_p, c_double_p, C.c_int]
+        lib.oracle_cheb_eval.restype = C.c_double
+        lib.oracle_cheb_eval.argtypes = [C.c_int, C.c_int, c_double_p, c_double_p, C.c_int]
+        _cache["oracle"] = lib
+    return _cache["oracle"]
+
+
+class OracleTree:
+    def __init__(self, path):
+        self.lib = oracle_lib()
+        self.ptr = self.lib.oracle_restore(os.fsencode(path))
+        if not self.ptr:
+            raise RuntimeError("oracle_restore failed for %s" % path)
+        s = self.ptr[0]
+        self.dim, self.order, self.output_dim = s.dim, s.order, s.output_dim
+        self.n_nodes, self.n_leaves, self.n_bins, self.n_coeffs = s.n_nodes, s.n_leaves, s.n_bins, s.n_coeffs
+
+    def arrays(self):
+        """numpy copies of every field (for checking the product's flatten against)."""
+        s, d = self.ptr[0], self.dim
+        A = np.ctypeslib.as_array
+        return dict(
+            lower_left=np.array(s.lower_left[:d]), upper_right=np.array(s.upper_right[:d]),
+            inv_bin_size=np.array(s.inv_bin_size[:d]), n_subtrees=np.array(s.n_subtrees[:d]),
+            box_center=np.array(s.box_center[:d]), box_inv_half_length=np.array(s.box_inv_half_length[:d]),
+            tol=s.tol, split_multi_eval=s.split_multi_eval, output_dim=s.output_dim,
+            subtree_node_offsets=A(s.subtree_node_offsets, (s.n_bins + 1,)).copy(),
+            center=A(s.center, (s.n_nodes, d)).copy(), inv_half_length=A(s.inv_half_length, (s.n_nodes, d)).copy(),
+            first_child_idx=A(s.first_child_idx, (s.n_nodes,)).copy(),
+            coeff_offset=A(s.coeff_offset, (s.n_nodes,)).copy(),
+            node_output_dim=A(s.node_output_dim, (s.n_nodes,)).copy(),
+            coeffs=A(s.coeffs, (max(1, s.n_coeffs),)).copy()[:s.n_coeffs])
+
+    def node_indices(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        n = x.size // self.dim
+        idx = np.empty(n, dtype=np.int64)
+        self.lib.oracle_node_index_multi(self.ptr, dptr(x), n, idx.ctypes.data_as(C.POINTER(C.c_int64)))
+        return idx
+
+    def eval_multi(self, x, arith=ARITH_FMA):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        n = x.size // self.dim
+        res = np.empty(n, dtype=np.float64)
+        self.lib.oracle_eval_multi(self.ptr, dptr(x), dptr(res), n, arith)
+        return res
+
+    def eval(self, x, arith=ARITH_FMA):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.empty(max(1, self.output_dim), dtype=np.float64)
+        self.lib.oracle_eval(self.ptr, dptr(x), dptr(y), arith)
+        return y
+
+    def free(self):
+        if self.ptr:
+            self.lib.oracle_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
