@@ -1,0 +1,577 @@
+// abi.cu -- the C ABI of libbaobzi.so (declared in include/baobzi.h).
+//
+// Mirrors the reference's src/baobzi.cpp: same exported names, same handle struct, same error
+// conventions (NULL + stderr).  Behind the handle sits a bz::Function: the host image of the tree
+// (for save / stats / new replicas) plus one device replica per GPU that has been used, each with a
+// small pool of execution contexts (stream + chunk buffers) so that concurrent calls on one handle
+// from several host threads stay safe, as they are in the reference (eval is const there).
+#include "../../include/baobzi.h"
+#include "device_tree.hpp"
+#include "fit.hpp"
+#include "host_tree.hpp"
+
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+namespace bz {
+
+// One in-flight evaluation on one device: a stream, device staging for host-pointer calls, the binned
+// workspace, and pinned scratch for the scalar entry point.
+struct ExecContext {
+    cudaStream_t stream = nullptr;
+    // host-pointer pipeline: kSlots chunks in flight
+    static constexpr int kSlots = 3;
+    double *d_x[kSlots] = {nullptr, nullptr, nullptr};
+    double *d_res[kSlots] = {nullptr, nullptr, nullptr};
+    cudaStream_t slot_stream[kSlots] = {nullptr, nullptr, nullptr};
+    int64_t slot_points = 0;
+    BinWorkspace ws[kSlots];
+    double *pinned = nullptr; // scalar eval scratch: x[3] then y[out_dim]
+    size_t pinned_doubles = 0;
+    bool busy = false;
+};
+
+struct Replica {
+    DeviceTree dt;
+    std::vector<std::unique_ptr<ExecContext>> contexts;
+    cudaStream_t shard_stream = nullptr; // baobzi_eval_multi_sharded
+    BinWorkspace shard_ws;
+};
+
+enum Mode { kAuto = 0, kDirect = 1, kBinned = 2 };
+
+struct Function {
+    HostTree host;
+    std::mutex mu;
+    std::vector<std::unique_ptr<Replica>> replicas;
+    int mode = kAuto;
+    int64_t chunk = 0;
+    std::atomic<int64_t> launches{0};
+};
+
+namespace {
+
+class DeviceGuard {
+  public:
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev_);
+        if (dev != prev_)
+            cudaSetDevice(dev);
+        cur_ = dev;
+    }
+    ~DeviceGuard() {
+        if (cur_ != prev_)
+            cudaSetDevice(prev_);
+    }
+
+  private:
+    int prev_ = 0, cur_ = 0;
+};
+
+bool report(cudaError_t e, const char *what) {
+    if (e == cudaSuccess)
+        return false;
+    std::fprintf(stderr, "Baobzi (b200) CUDA error in %s: %s\n", what, cudaGetErrorString(e));
+    return true;
+}
+
+int64_t default_chunk() {
+    if (const char *s = std::getenv("BAOBZI_B200_CHUNK")) {
+        long long v = std::atoll(s);
+        if (v > 0)
+            return v;
+    }
+    return int64_t(1) << 21; // 2 Mi points: x + keys + perm + res of a chunk stay L2 resident
+}
+
+int env_mode() {
+    if (const char *s = std::getenv("BAOBZI_B200_MODE")) {
+        if (!std::strcmp(s, "direct"))
+            return kDirect;
+        if (!std::strcmp(s, "binned"))
+            return kBinned;
+    }
+    return kAuto;
+}
+
+// replica on `dev`, created on first use
+Replica *get_replica(Function *f, int dev) {
+    std::lock_guard<std::mutex> lock(f->mu);
+    for (auto &r : f->replicas)
+        if (r->dt.device == dev)
+            return r.get();
+    DeviceGuard g(dev);
+    auto r = std::make_unique<Replica>();
+    int rc = upload_tree(f->host, r->dt);
+    if (rc != 0) {
+        report((cudaError_t)rc, "tree upload");
+        return nullptr;
+    }
+    f->replicas.push_back(std::move(r));
+    return f->replicas.back().get();
+}
+
+ExecContext *acquire(Function *f, Replica *r) {
+    std::lock_guard<std::mutex> lock(f->mu);
+    for (auto &c : r->contexts)
+        if (!c->busy) {
+            c->busy = true;
+            return c.get();
+        }
+    auto c = std::make_unique<ExecContext>();
+    if (report(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking), "stream create"))
+        return nullptr;
+    c->busy = true;
+    r->contexts.push_back(std::move(c));
+    return r->contexts.back().get();
+}
+
+void release(Function *f, ExecContext *c) {
+    std::lock_guard<std::mutex> lock(f->mu);
+    c->busy = false;
+}
+
+void destroy_context(ExecContext &c) {
+    for (int s = 0; s < ExecContext::kSlots; ++s) {
+        if (c.d_x[s])
+            cudaFree(c.d_x[s]);
+        if (c.d_res[s])
+            cudaFree(c.d_res[s]);
+        if (c.slot_stream[s])
+            cudaStreamDestroy(c.slot_stream[s]);
+        free_workspace(c.ws[s]);
+    }
+    if (c.pinned)
+        cudaFreeHost(c.pinned);
+    if (c.stream)
+        cudaStreamDestroy(c.stream);
+}
+
+bool use_binned(const Function *f, const DeviceTree &dt, int64_t n) {
+    if (!binned_supported(dt.view.dim, dt.view.order))
+        return false;
+    if (f->mode == kDirect)
+        return false;
+    if (f->mode == kBinned)
+        return true;
+    // auto: worth it when the per-point coefficient gather (order^dim doubles) dwarfs the point itself and
+    // there are enough points per leaf to fill warp tiles
+    const int64_t block_bytes = 8 * (int64_t)std::pow((double)dt.view.order, dt.view.dim);
+    return dt.view.dim == 3 && block_bytes >= 1024 && n >= 64 * (int64_t)dt.view.n_leaves && n >= (1 << 16);
+}
+
+// evaluate n device-resident points on `stream`, chunking the binned path
+int eval_device(Function *f, Replica *r, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
+                cudaStream_t stream) {
+    int64_t launches = 0;
+    int rc = 0;
+    if (use_binned(f, r->dt, n)) {
+        const int64_t chunk = f->chunk > 0 ? f->chunk : default_chunk();
+        if (ws.chunk_capacity < (n < chunk ? n : chunk)) {
+            cudaStreamSynchronize(stream);
+            free_workspace(ws);
+            rc = alloc_workspace(r->dt, n < chunk ? n : chunk, ws);
+        }
+        for (int64_t o = 0; o < n && rc == 0; o += ws.chunk_capacity) {
+            const int64_t m = n - o < ws.chunk_capacity ? n - o : ws.chunk_capacity;
+            rc = launch_eval_binned(r->dt, ws, d_x + o * r->dt.view.dim, d_res + o, m, stream, &launches);
+        }
+    } else {
+        rc = launch_eval_direct(r->dt, d_x, d_res, nullptr, n, stream, &launches);
+    }
+    f->launches += launches;
+    return rc;
+}
+
+void fill_nan(double *res, int64_t n) {
+    for (int64_t i = 0; i < n; ++i)
+        res[i] = NAN;
+}
+
+int device_of_pointer(const void *p) { // -1: host (or unknown) memory
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return -1;
+    }
+    if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged)
+        return a.device;
+    return -1;
+}
+
+// ---- entry points stored in the handle (reference macros.h:29-51 generates 504 of these; here one set
+// serves every (dim, order) because dispatch happens at kernel-launch time)
+void fn_eval(const void *obj, const double *x, double *y) {
+    Function *f = (Function *)obj;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (f->replicas.size() == 1)
+        dev = f->replicas[0]->dt.device; // scalar calls stick to the replica that exists
+    Replica *r = get_replica(f, dev);
+    const int od = f->host.output_dim < 1 ? 1 : (int)f->host.output_dim;
+    ExecContext *c = r ? acquire(f, r) : nullptr;
+    if (!c) {
+        fill_nan(y, od);
+        return;
+    }
+    DeviceGuard g(r->dt.device);
+    bool bad = false;
+    if (c->pinned_doubles < (size_t)(3 + od)) {
+        if (c->pinned)
+            cudaFreeHost(c->pinned);
+        c->pinned = nullptr;
+        bad = report(cudaHostAlloc((void **)&c->pinned, sizeof(double) * (3 + od), cudaHostAllocMapped), "pinned alloc");
+        c->pinned_doubles = bad ? 0 : (size_t)(3 + od);
+    }
+    if (!bad) {
+        // zero-copy: the kernel reads the point from and writes the values to mapped pinned memory
+        for (int j = 0; j < f->host.dim; ++j)
+            c->pinned[j] = x[j];
+        for (int k = 0; k < od; ++k)
+            c->pinned[3 + k] = NAN;
+        int64_t launches = 0;
+        int rc = launch_eval_scalar(r->dt, c->pinned, c->pinned + 3, c->stream, &launches);
+        f->launches += launches;
+        bad = report((cudaError_t)rc, "scalar eval launch") || report(cudaStreamSynchronize(c->stream), "scalar eval");
+    }
+    if (bad)
+        fill_nan(y, od);
+    else
+        for (int k = 0; k < od; ++k)
+            y[k] = c->pinned[3 + k];
+    release(f, c);
+}
+
+bool ensure_slots(ExecContext *c, const DeviceTree &dt, int64_t points) {
+    if (c->slot_points >= points)
+        return true;
+    for (int s = 0; s < ExecContext::kSlots; ++s) {
+        if (c->d_x[s])
+            cudaFree(c->d_x[s]);
+        if (c->d_res[s])
+            cudaFree(c->d_res[s]);
+        c->d_x[s] = c->d_res[s] = nullptr;
+        if (!c->slot_stream[s] &&
+            report(cudaStreamCreateWithFlags(&c->slot_stream[s], cudaStreamNonBlocking), "stream create"))
+            return false;
+        if (report(cudaMalloc((void **)&c->d_x[s], sizeof(double) * points * dt.view.dim), "chunk alloc") ||
+            report(cudaMalloc((void **)&c->d_res[s], sizeof(double) * points), "chunk alloc")) {
+            c->slot_points = 0;
+            return false;
+        }
+    }
+    c->slot_points = points;
+    return true;
+}
+
+void fn_eval_multi(const void *obj, const double *x, double *res, int ntrg) {
+    Function *f = (Function *)obj;
+    if (ntrg <= 0)
+        return;
+    // Device pointers handed to the classic entry point are evaluated in place (zero copy).
+    const int xdev = device_of_pointer(x), rdev = device_of_pointer(res);
+    if (xdev >= 0 && rdev == xdev) {
+        Replica *r = get_replica(f, xdev);
+        ExecContext *c = r ? acquire(f, r) : nullptr;
+        if (!c)
+            return;
+        DeviceGuard g(xdev);
+        int rc = eval_device(f, r, c->ws[0], x, res, ntrg, c->stream);
+        report((cudaError_t)rc, "eval_multi (device pointers)");
+        report(cudaStreamSynchronize(c->stream), "eval_multi (device pointers)");
+        release(f, c);
+        return;
+    }
+
+    int dev = 0;
+    cudaGetDevice(&dev);
+    Replica *r = get_replica(f, dev);
+    ExecContext *c = r ? acquire(f, r) : nullptr;
+    if (!c) {
+        fill_nan(res, ntrg);
+        return;
+    }
+    DeviceGuard g(dev);
+    const int dim = f->host.dim;
+    // Host pointers: pipeline H2D -> kernels -> D2H over kSlots streams so that PCIe traffic in both
+    // directions overlaps evaluation.  Chunk: 4 Mi points, or less for small calls.
+    const int64_t n = ntrg;
+    int64_t chunk = int64_t(1) << 22;
+    if (n < chunk * ExecContext::kSlots)
+        chunk = (n + ExecContext::kSlots - 1) / ExecContext::kSlots;
+    if (chunk < 1)
+        chunk = 1;
+    bool bad = !ensure_slots(c, r->dt, chunk);
+    int slot = 0;
+    for (int64_t o = 0; o < n && !bad; o += chunk, slot = (slot + 1) % ExecContext::kSlots) {
+        const int64_t m = n - o < chunk ? n - o : chunk;
+        cudaStream_t st = c->slot_stream[slot];
+        bad = report(cudaMemcpyAsync(c->d_x[slot], x + o * dim, sizeof(double) * m * dim, cudaMemcpyHostToDevice, st),
+                     "H2D copy");
+        if (!bad)
+            bad = report((cudaError_t)eval_device(f, r, c->ws[slot], c->d_x[slot], c->d_res[slot], m, st), "eval launch");
+        if (!bad)
+            bad = report(cudaMemcpyAsync(res + o, c->d_res[slot], sizeof(double) * m, cudaMemcpyDeviceToHost, st),
+                         "D2H copy");
+    }
+    for (int s = 0; s < ExecContext::kSlots; ++s)
+        if (c->slot_stream[s])
+            bad = report(cudaStreamSynchronize(c->slot_stream[s]), "eval_multi") || bad;
+    if (bad)
+        fill_nan(res, n);
+    release(f, c);
+}
+
+void fn_save(const void *obj, const char *filename) {
+    const Function *f = (const Function *)obj;
+    std::string err;
+    if (!write_baobzi_file(filename, f->host, err))
+        std::fprintf(stderr, "Baobzi save error: %s\n", err.c_str());
+}
+
+void fn_stats(void *obj) {
+    Function *f = (Function *)obj;
+    const HostTree &h = f->host;
+    // same lines as the reference's print_stats (template.hpp:582-603), plus the device footprint
+    size_t host_bytes = h.coeffs.size() * 8 + (size_t)h.n_nodes() * (16 * h.dim + 16) + (size_t)h.n_bins() * 4;
+    std::printf("Baobzi function mapping %d to %u\n", h.dim, h.output_dim);
+    std::printf("Tree represented by %lld nodes, of which %lld are leaves\n", (long long)h.n_nodes(),
+                (long long)h.n_leaves());
+    std::printf("Nodes are distributed across %lld subtrees at an initial depth of %d with a maximum subtree depth of %d\n",
+                (long long)h.n_bins(), h.base_depth, h.max_subtree_depth);
+    std::printf("Total function evaluations required for fit: %llu\n", (unsigned long long)h.n_func_evals);
+    std::printf("Total time to create tree: %u milliseconds\n", h.fit_ms);
+    std::printf("Approximate memory usage of tree: %g MiB\n", (double)host_bytes / (1024.0 * 1024.0));
+    std::lock_guard<std::mutex> lock(f->mu);
+    for (auto &r : f->replicas)
+        std::printf("Device replica on GPU %d: %g MiB (64-byte node records + coefficients)\n", r->dt.device,
+                    (double)r->dt.blob_bytes / (1024.0 * 1024.0));
+    std::fflush(stdout);
+}
+
+void fn_free(void *obj) {
+    Function *f = (Function *)obj;
+    for (auto &r : f->replicas) {
+        DeviceGuard g(r->dt.device);
+        for (auto &c : r->contexts)
+            destroy_context(*c);
+        if (r->shard_stream)
+            cudaStreamDestroy(r->shard_stream);
+        free_workspace(r->shard_ws);
+        free_tree(r->dt);
+    }
+    delete f;
+}
+
+baobzi_t make_handle(std::unique_ptr<Function> f) {
+    int dev = 0;
+    if (report(cudaGetDevice(&dev), "device query (is a CUDA device visible? there is no CPU evaluation path)"))
+        return nullptr;
+    f->mode = env_mode();
+    if (!get_replica(f.get(), dev))
+        return nullptr;
+    baobzi_t res = (baobzi_t)std::malloc(sizeof(baobzi_struct));
+    res->DIM = f->host.dim;
+    res->ORDER = f->host.order;
+    res->OUTPUT_DIM = (int)f->host.output_dim;
+    res->eval = &fn_eval;
+    res->eval_multi = &fn_eval_multi;
+    res->save = &fn_save;
+    res->stats = &fn_stats;
+    res->free = &fn_free;
+    res->obj = f.release();
+    return res;
+}
+
+} // namespace
+} // namespace bz
+
+// ================================================================================================
+// exported C symbols
+// ================================================================================================
+using bz::Function;
+
+extern "C" {
+
+const baobzi_input_t baobzi_input_default; // zero + C++ member defaults, as reference baobzi.cpp:16
+
+const char *baobzi_b200_version(void) { return "baobzi-b200 0.1 (sm_100a)"; }
+
+void baobzi_eval(const baobzi_t func, const double *x, double *y) { func->eval(func->obj, x, y); }
+
+void baobzi_eval_multi(const baobzi_t func, const double *x, double *res, int ntrg) {
+    func->eval_multi(func->obj, x, res, ntrg);
+}
+
+void baobzi_save(const baobzi_t func, const char *filename) { func->save(func->obj, filename); }
+
+baobzi_t baobzi_restore(const char *filename) {
+    auto f = std::make_unique<Function>();
+    std::string err;
+    if (!bz::read_baobzi_file(filename, f->host, err)) {
+        // reference baobzi.cpp:94-114: silent NULL on a version mismatch, message otherwise
+        if (err.find("version") == std::string::npos) {
+            if (err.find("(DIM, ORDER)") != std::string::npos)
+                std::fprintf(stderr, "BAOBZI ERROR: %s\n", err.c_str());
+            else
+                std::fprintf(stderr, "Baobzi restore error: Unable to restore from '%s' (%s)\n", filename, err.c_str());
+        }
+        return nullptr;
+    }
+    return bz::make_handle(std::move(f));
+}
+
+baobzi_t baobzi_init(const baobzi_input_t *input, const double *center, const double *half_length) {
+    // argument checks in the order of reference baobzi.cpp:148-157
+    if (input->tol <= 0.0) {
+        std::fprintf(stderr, "Baobzi error: Unable to initialize Baobzi due to invalid 'tol' parameter. Please supply "
+                             "something greater than zero.\n");
+        return nullptr;
+    }
+    if (!input->func) {
+        std::fprintf(stderr, "BAOBZI ERROR: Unable to initialize Baobzi due to empty or invalid 'func' parameter. "
+                             "Please supply a valid function to fit.\n");
+        return nullptr;
+    }
+    if (!bz::supported_dim_order(input->dim, input->order)) { // reference baobzi.cpp:170-176
+        std::fprintf(stderr, "Baobzi error: Unable to initialize Baobzi function with variables (DIM, ORDER): (%d, %d)\n",
+                     input->dim, input->order);
+        return nullptr;
+    }
+    auto f = std::make_unique<Function>();
+    std::string err;
+    if (!bz::fit_tree(*input, center, half_length, f->host, err)) { // reference baobzi.cpp:178-182
+        std::fprintf(stderr, "%s\n", err.c_str());
+        return nullptr;
+    }
+    return bz::make_handle(std::move(f));
+}
+
+void baobzi_stats(baobzi_t func) {
+    if (!func)
+        return;
+    func->stats(func->obj);
+}
+
+baobzi_t baobzi_free(baobzi_t func) {
+    if (!func)
+        return nullptr;
+    if (func->obj)
+        func->free(func->obj);
+    std::free(func);
+    return nullptr;
+}
+
+// ---------------------------------------------------------------------------- device extension
+int baobzi_eval_multi_device(const baobzi_t func, const double *d_x, double *d_res, int64_t ntrg, void *cuda_stream) {
+    Function *f = (Function *)func->obj;
+    if (ntrg <= 0)
+        return 0;
+    int dev = bz::device_of_pointer(d_x);
+    if (dev < 0)
+        return (int)cudaErrorInvalidDevicePointer;
+    bz::Replica *r = bz::get_replica(f, dev);
+    if (!r)
+        return (int)cudaErrorMemoryAllocation;
+    bz::DeviceGuard g(dev);
+    // the binned workspace of the per-device shard slot is reused; calls on one handle+device are
+    // serialised on the caller's stream by construction (one workspace), so guard it
+    std::lock_guard<std::mutex> lock(f->mu);
+    return bz::eval_device(f, r, r->shard_ws, d_x, d_res, ntrg, (cudaStream_t)cuda_stream);
+}
+
+int baobzi_node_index_multi_device(const baobzi_t func, const double *d_x, int64_t *d_idx, int64_t ntrg,
+                                   void *cuda_stream) {
+    Function *f = (Function *)func->obj;
+    if (ntrg <= 0)
+        return 0;
+    int dev = bz::device_of_pointer(d_x);
+    if (dev < 0)
+        return (int)cudaErrorInvalidDevicePointer;
+    bz::Replica *r = bz::get_replica(f, dev);
+    if (!r)
+        return (int)cudaErrorMemoryAllocation;
+    bz::DeviceGuard g(dev);
+    int64_t launches = 0;
+    int rc = bz::launch_eval_direct(r->dt, d_x, nullptr, d_idx, ntrg, (cudaStream_t)cuda_stream, &launches);
+    f->launches += launches;
+    return rc;
+}
+
+int baobzi_node_index_multi(const baobzi_t func, const double *x, int64_t *idx, int64_t ntrg) {
+    Function *f = (Function *)func->obj;
+    if (ntrg <= 0)
+        return 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    bz::Replica *r = bz::get_replica(f, dev);
+    if (!r)
+        return (int)cudaErrorMemoryAllocation;
+    double *d_x = nullptr;
+    int64_t *d_idx = nullptr;
+    cudaError_t e = cudaMalloc((void **)&d_x, sizeof(double) * ntrg * f->host.dim);
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&d_idx, sizeof(int64_t) * ntrg);
+    if (e == cudaSuccess)
+        e = cudaMemcpy(d_x, x, sizeof(double) * ntrg * f->host.dim, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        int64_t launches = 0;
+        e = (cudaError_t)bz::launch_eval_direct(r->dt, d_x, nullptr, d_idx, ntrg, nullptr, &launches);
+        f->launches += launches;
+    }
+    if (e == cudaSuccess)
+        e = cudaMemcpy(idx, d_idx, sizeof(int64_t) * ntrg, cudaMemcpyDeviceToHost);
+    cudaFree(d_x);
+    cudaFree(d_idx);
+    return (int)e;
+}
+
+int baobzi_eval_multi_sharded(const baobzi_t func, int n_dev, const int *devices, const double *const *d_x,
+                              double *const *d_res, const int64_t *ntrg) {
+    Function *f = (Function *)func->obj;
+    int rc = 0;
+    for (int k = 0; k < n_dev && rc == 0; ++k) {
+        bz::Replica *r = bz::get_replica(f, devices[k]);
+        if (!r)
+            return (int)cudaErrorMemoryAllocation;
+        bz::DeviceGuard g(devices[k]);
+        if (!r->shard_stream)
+            rc = (int)cudaStreamCreateWithFlags(&r->shard_stream, cudaStreamNonBlocking);
+        if (rc == 0 && ntrg[k] > 0)
+            rc = bz::eval_device(f, r, r->shard_ws, d_x[k], d_res[k], ntrg[k], r->shard_stream);
+    }
+    return rc;
+}
+
+int baobzi_sync(const baobzi_t func) {
+    Function *f = (Function *)func->obj;
+    int rc = 0;
+    for (auto &r : f->replicas) {
+        bz::DeviceGuard g(r->dt.device);
+        if (r->shard_stream) {
+            int e = (int)cudaStreamSynchronize(r->shard_stream);
+            rc = rc ? rc : e;
+        }
+    }
+    return rc;
+}
+
+int baobzi_set_mode(baobzi_t func, int mode, int64_t chunk) {
+    Function *f = (Function *)func->obj;
+    if (mode < 0 || mode > 2)
+        return 1;
+    f->mode = mode;
+    f->chunk = chunk > 0 ? chunk : 0;
+    return 0;
+}
+
+int64_t baobzi_launch_count(const baobzi_t func) { return ((Function *)func->obj)->launches.load(); }
+
+} // extern "C"

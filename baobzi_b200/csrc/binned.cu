@@ -1,0 +1,306 @@
+// binned.cu -- the "group points by leaf, then evaluate" path for trees whose per-leaf coefficient block
+// is large (3D: 1.7 KB at order 6 ... 32 KB at order 16).
+//
+// Why: in the direct kernel every lane of a warp sits in a different leaf, so a warp pulls 32 different
+// multi-KB coefficient blocks through L2 for 32 results -- 4 KB of L2 traffic per evaluation at 3D
+// order 8, two orders of magnitude above the 32 algorithmic bytes, and far beyond what L2 can deliver
+// at the FP64 roofline.  Grouping makes every warp work inside ONE leaf: a coefficient is then a
+// warp-uniform 16-byte load (one L1 wavefront, broadcast to 32 lanes) feeding 2*P FMAs.
+//
+// Per chunk of points (sized so that the chunk's points, keys, slots and results stay L2 resident and
+// the grouping never touches HBM; DESIGN.md has the arithmetic):
+//   K1 bin_lookup   thread per point: bounds -> grid cell -> descent -> leaf rank; key[i] = rank,
+//                   count[rank] += 1 (fire-and-forget RED); out-of-domain points get NaN right here
+//   K2 bin_scan     one CTA: start[] = exclusive scan of counts rounded up to the warp-tile size,
+//                   tile_leaf[] = leaf of every tile, padding slots of perm[] = invalid, cursors reset
+//   K3 bin_scatter  thread per point: perm[start[key] + cursor[key]++] = i
+//   K4 bin_eval     warp per tile (32*P consecutive slots of one leaf): gather the P points per lane,
+//                   evaluate with register-blocked, reference-ordered arithmetic, scatter the results
+#include "cheb.cuh"
+#include "device_tree.hpp"
+
+#include <cstdio>
+
+#include "lookup.cuh"
+
+namespace bz {
+
+constexpr uint32_t kInvalidSlot = 0xFFFFFFFFu;
+constexpr int kBinThreads = 256;
+
+__host__ __device__ constexpr int points_per_lane(int dim, int order) {
+    return (dim == 3 && order <= 10) ? 2 : 1;
+}
+
+// ------------------------------------------------------------------------------------------ K1
+template <int DIM>
+__global__ void __launch_bounds__(kBinThreads)
+bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                  uint32_t *__restrict__ key, uint32_t *__restrict__ count, uint32_t n) {
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        double p[DIM];
+        load_point_keep<DIM>(x, i, p); // keep in L2: K4 gathers these again
+        if (outside<DIM>(tv, p)) {
+            res[i] = __longlong_as_double(0x7ff8000000000000ll);
+            key[i] = kNotLeaf;
+            continue;
+        }
+        NodeHead head;
+        const uint32_t node = locate<DIM>(tv, p, head);
+        const uint32_t rank = load_tail(tv.nodes, node).leaf_rank;
+        key[i] = rank;
+        atomicAdd(count + rank, 1u);
+    }
+}
+
+// ------------------------------------------------------------------------------------------ K2
+// Single CTA.  count[] in: histogram; out: zero (reused as cursor by K3).
+template <int TILE>
+__global__ void __launch_bounds__(1024)
+bin_scan_kernel(uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__restrict__ start,
+                uint32_t *__restrict__ tile_leaf, uint32_t *__restrict__ perm, uint32_t *__restrict__ n_tiles) {
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t carry_s;
+    if (threadIdx.x == 0)
+        carry_s = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t base = 0; base < n_leaves; base += blockDim.x) {
+        const uint32_t l = base + threadIdx.x;
+        const uint32_t cnt = l < n_leaves ? count[l] : 0u;
+        const uint32_t padded = (cnt + TILE - 1) / TILE * TILE;
+        // inclusive scan of `padded` across the CTA
+        uint32_t v = padded;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o)
+                v += t;
+        }
+        if (lane == 31)
+            warp_sums[warp] = v;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t w = warp_sums[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
+                if (lane >= o)
+                    w += t;
+            }
+            warp_sums[lane] = w;
+        }
+        __syncthreads();
+        const uint32_t carry = carry_s;
+        const uint32_t excl = carry + (warp ? warp_sums[warp - 1] : 0u) + v - padded;
+        if (l < n_leaves) {
+            start[l] = excl;
+            count[l] = 0;
+            for (uint32_t s = excl + cnt; s < excl + padded; ++s)
+                perm[s] = kInvalidSlot;
+            for (uint32_t t = excl / TILE; t < (excl + padded) / TILE; ++t)
+                tile_leaf[t] = l;
+        }
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1)
+            carry_s = carry + warp_sums[31];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0)
+        *n_tiles = carry_s / TILE;
+}
+
+// ------------------------------------------------------------------------------------------ K3
+__global__ void __launch_bounds__(kBinThreads)
+bin_scatter_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict__ start, uint32_t *__restrict__ cursor,
+                   uint32_t *__restrict__ perm, uint32_t n) {
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const uint32_t k = key[i];
+        if (k == kNotLeaf)
+            continue;
+        const uint32_t pos = __ldg(start + k) + atomicAdd(cursor + k, 1u);
+        perm[pos] = i;
+    }
+}
+
+// ------------------------------------------------------------------------------------------ K4
+// P points per lane, all in the same leaf: coefficient loads are warp-uniform.
+template <int O, int P>
+__device__ __forceinline__ void gemv_block_multi(const double *__restrict__ C, const double (&v)[P][O],
+                                                 double (&acc)[P][O]) {
+    const double2 *c2 = reinterpret_cast<const double2 *>(C);
+#pragma unroll
+    for (int r = 0; r < O; r += 2) {
+        const double2 c = __ldg(c2 + r / 2);
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            acc[p][r] = __dmul_rn(c.x, v[p][0]);
+            acc[p][r + 1] = __dmul_rn(c.y, v[p][0]);
+        }
+    }
+#pragma unroll
+    for (int k = 1; k < O; ++k) {
+#pragma unroll
+        for (int r = 0; r < O; r += 2) {
+            const double2 c = __ldg(c2 + (k * O + r) / 2);
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                acc[p][r] = __fma_rn(c.x, v[p][k], acc[p][r]);
+                acc[p][r + 1] = __fma_rn(c.y, v[p][k], acc[p][r + 1]);
+            }
+        }
+    }
+}
+
+template <int ORDER, int P>
+__global__ void __launch_bounds__(kBinThreads)
+bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                  const uint32_t *__restrict__ perm, const uint32_t *__restrict__ tile_leaf,
+                  const uint32_t *__restrict__ n_tiles_p) {
+    constexpr int O = ORDER;
+    constexpr int TILE = 32 * P;
+    const uint32_t n_tiles = __ldg(n_tiles_p);
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warps_per_cta = blockDim.x >> 5;
+    for (uint32_t t = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); t < n_tiles; t += gridDim.x * warps_per_cta) {
+        const uint32_t leaf = __ldg(tile_leaf + t);
+        const uint32_t node = __ldg(tv.leaf_node + leaf);
+        const NodeHead head = load_head(tv.nodes, node);
+        const NodeTail tail = load_tail(tv.nodes, node);
+        const double *C = tv.coeffs + 2ull * head.coeff16;
+
+        uint32_t idx[P];
+        double Ty[P][O], Tz[P][O], acc[P][O];
+        double x2[P], tx[P], tx_prev[P], val[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            idx[p] = __ldg(perm + (size_t)t * TILE + p * 32 + lane);
+            double px = head.c0, py = head.c1, pz = head.c2; // padding lanes evaluate the leaf centre
+            if (idx[p] != kInvalidSlot) {
+                const double *q = x + 3ull * idx[p];
+                px = __ldg(q);
+                py = __ldg(q + 1);
+                pz = __ldg(q + 2);
+            }
+            const double u = __dmul_rn(__dsub_rn(px, head.c0), tail.ih0);
+            const double v = __dmul_rn(__dsub_rn(py, head.c1), tail.ih1);
+            const double w = __dmul_rn(__dsub_rn(pz, head.c2), tail.ih2);
+            cheb_T<O>(v, Ty[p]);
+            cheb_T<O>(w, Tz[p]);
+            x2[p] = __dadd_rn(u, u);
+            tx_prev[p] = 1.0;
+            tx[p] = u; // becomes T_1 at i == 1
+            val[p] = 0.0;
+        }
+#pragma unroll 1
+        for (int i = 0; i < O; ++i) {
+            gemv_block_multi<O, P>(C + i * O * O, Tz, acc);
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                const double d = dot_packets<O>(Ty[p], acc[p]);
+                double ti;
+                if (i == 0) {
+                    ti = 1.0;
+                } else if (i == 1) {
+                    ti = tx[p];
+                } else {
+                    ti = __fma_rn(x2[p], tx[p], -tx_prev[p]);
+                    tx_prev[p] = tx[p];
+                    tx[p] = ti;
+                }
+                val[p] = __fma_rn(ti, d, val[p]);
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < P; ++p)
+            if (idx[p] != kInvalidSlot)
+                res[idx[p]] = val[p];
+    }
+}
+
+// ------------------------------------------------------------------------------------------ host side
+bool binned_supported(int dim, int order) { return dim == 3 && order >= 6 && order <= 16 && order % 2 == 0; }
+
+int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
+    if (chunk < 1)
+        chunk = 1;
+    if (chunk > 0x7FFFFFFFll)
+        chunk = 0x7FFFFFFFll;
+    const int P = points_per_lane(dt.view.dim, dt.view.order);
+    const int64_t tile = 32 * P;
+    const int64_t nl = dt.view.n_leaves;
+    ws.perm_capacity = chunk + nl * tile;
+    ws.tile_capacity = ws.perm_capacity / tile + 1;
+    cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.perm, sizeof(uint32_t) * ws.perm_capacity);
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.count, sizeof(uint32_t) * (nl + 1));
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.start, sizeof(uint32_t) * (nl + 1));
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.tile_leaf, sizeof(uint32_t) * ws.tile_capacity);
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.n_tiles, sizeof(uint32_t));
+    if (e == cudaSuccess)
+        e = cudaMemset(ws.count, 0, sizeof(uint32_t) * (nl + 1));
+    if (e != cudaSuccess) {
+        free_workspace(ws);
+        return (int)e;
+    }
+    ws.chunk_capacity = chunk;
+    return 0;
+}
+
+void free_workspace(BinWorkspace &ws) {
+    cudaFree(ws.key);
+    cudaFree(ws.perm);
+    cudaFree(ws.count);
+    cudaFree(ws.start);
+    cudaFree(ws.tile_leaf);
+    cudaFree(ws.n_tiles);
+    ws = BinWorkspace();
+}
+
+template <int O>
+static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, uint32_t n,
+                           cudaStream_t st) {
+    constexpr int P = points_per_lane(3, O);
+    constexpr int TILE = 32 * P;
+    const TreeView &tv = dt.view;
+    const unsigned cap = (unsigned)dt.sm_count * 16;
+    unsigned g1 = (n + kBinThreads - 1) / kBinThreads;
+    g1 = g1 < cap ? g1 : cap;
+    bin_lookup_kernel<3><<<g1, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.key, ws.count, n);
+    bin_scan_kernel<TILE><<<1, 1024, 0, st>>>(tv.n_leaves, ws.count, ws.start, ws.tile_leaf, ws.perm, ws.n_tiles);
+    bin_scatter_kernel<<<g1, kBinThreads, 0, st>>>(ws.key, ws.start, ws.count, ws.perm, n);
+    // persistent grid: 2 CTAs of 8 warps per SM, each CTA walks 8 consecutive tiles (same leaf, L1 reuse)
+    const unsigned g4 = (unsigned)dt.sm_count * 2;
+    bin_eval3d_kernel<O, P><<<g4, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.perm, ws.tile_leaf, ws.n_tiles);
+    return (int)cudaGetLastError();
+}
+
+int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
+                       cudaStream_t stream, int64_t *launches) {
+    if (n <= 0)
+        return 0;
+    if (dt.view.dim != 3 || n > ws.chunk_capacity)
+        return (int)cudaErrorInvalidValue;
+    int rc;
+    switch (dt.view.order) {
+    case 6: rc = launch_chunk_3d<6>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
+    case 8: rc = launch_chunk_3d<8>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
+    case 10: rc = launch_chunk_3d<10>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
+    case 12: rc = launch_chunk_3d<12>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
+    case 14: rc = launch_chunk_3d<14>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
+    case 16: rc = launch_chunk_3d<16>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
+    default: return (int)cudaErrorInvalidValue;
+    }
+    if (launches)
+        *launches += 4;
+    return rc;
+}
+
+} // namespace bz

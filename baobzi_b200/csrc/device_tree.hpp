@@ -1,0 +1,94 @@
+// device_tree.hpp -- the flattened, device-resident image of a fitted tree and the launch API of the
+// sm_100a kernels that read it (kernels.cu).  Plain C++ header: no CUDA types beyond cudaStream_t.
+//
+// Device layout (one replica per GPU, all arrays in HBM, small enough to live in the 126 MB L2 for
+// every benchmark tree except the deliberately oversized one):
+//
+//   bin_root [n_bins]  u32   global index of the root node of the subtree in grid cell `bin`
+//                            (= the reference's subtree_node_offsets_, template.hpp:553, 764-767)
+//   nodes    [n_nodes] 64 B  one NodeRec per node in the reference's global node order
+//                            (template.hpp:763-778).  The first 32-byte sector holds everything a
+//                            descent step needs (centre + global index of child 0), the second sector
+//                            what only a leaf needs (inverse half lengths); a leaf visit is one 64-byte
+//                            request, an internal-node visit one 32-byte sector.
+//   coeffs   [n_coeffs] f64  the reference's coeffs_ (template.hpp:558), blocks 16-byte aligned, layout
+//                            per leaf unchanged
+//   leaf_rank[n_nodes] u32   dense rank of a leaf among leaves in node order (kNotLeaf for internal
+//                            nodes) -- bin key of the binned path
+//   leaf_node[n_leaves] u32  inverse of leaf_rank
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime_api.h>
+
+namespace bz {
+
+struct HostTree;
+
+constexpr uint32_t kLeafMark = 0xFFFFFFFFu; // NodeRec::child0 of a leaf
+constexpr uint32_t kNotLeaf = 0xFFFFFFFFu;
+
+struct alignas(64) NodeRec {
+    double center[3];   // Box::center (template.hpp:93); unused dims are 0
+    uint32_t child0;    // GLOBAL node index of child 0 (children are child0 .. child0 + 2^dim - 1), kLeafMark for a leaf
+    uint32_t coeff16;   // leaf: offset of the coefficient block in units of 16 bytes (2 doubles)
+    double inv_half[3]; // Box::inv_half_length (template.hpp:94)
+    uint32_t out_dim;   // Node::output_dim (template.hpp:210)
+    uint32_t leaf_rank; // dense leaf number, kNotLeaf for internal nodes
+};
+static_assert(sizeof(NodeRec) == 64, "NodeRec must be one 64-byte record");
+
+// Passed to kernels by value (lives in the constant bank of the launch).
+struct TreeView {
+    double lower_left[3], upper_right[3], inv_bin_size[3];
+    int n_sub[3];
+    int dim, order;
+    uint32_t n_bins, n_nodes, n_leaves, out_dim;
+    const uint32_t *bin_root;
+    const NodeRec *nodes;
+    const double *coeffs;
+    const uint32_t *leaf_node;
+};
+
+// Workspace of the binned path for one chunk of points (device memory, reused chunk after chunk so it
+// stays resident in L2).
+struct BinWorkspace {
+    int64_t chunk_capacity = 0; // points
+    uint32_t *key = nullptr;    // [chunk]            leaf rank per point (kNotLeaf = outside the domain)
+    uint32_t *perm = nullptr;   // [chunk + padding]  point index (within the chunk) per sorted slot
+    uint32_t *count = nullptr;  // [n_leaves + 1]     histogram, then cursor
+    uint32_t *start = nullptr;  // [n_leaves + 1]     padded exclusive scan
+    uint32_t *tile_leaf = nullptr; // [max_tiles]     leaf rank of each warp tile
+    uint32_t *n_tiles = nullptr;   // [1]
+    int64_t perm_capacity = 0, tile_capacity = 0;
+};
+
+struct DeviceTree {
+    int device = -1;
+    TreeView view{};
+    void *blob = nullptr; // single allocation backing every array of `view`
+    size_t blob_bytes = 0;
+    int sm_count = 0;
+};
+
+// flatten + upload to the current device; returns cudaError_t (0 = ok)
+int upload_tree(const HostTree &h, DeviceTree &out);
+void free_tree(DeviceTree &dt);
+
+int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws);
+void free_workspace(BinWorkspace &ws);
+
+// ---- kernels (all asynchronous on `stream`; return cudaError_t of the launch; *launches += kernels launched)
+// Fused lookup + evaluation, one thread per point.  node_idx may be nullptr; when given, receives the
+// reference's global node index per point (-1 outside).  res may be nullptr (index query only).
+int launch_eval_direct(const DeviceTree &dt, const double *d_x, double *d_res, int64_t *d_node_idx, int64_t n,
+                       cudaStream_t stream, int64_t *launches);
+// Scalar twin: x[dim] -> y[out_dim] (reference Function::eval(x, res), template.hpp:851-860).
+int launch_eval_scalar(const DeviceTree &dt, const double *d_x, double *d_y, cudaStream_t stream, int64_t *launches);
+// Binned path over one chunk (n <= ws.chunk_capacity): lookup+histogram, padded scan, scatter, evaluation.
+int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
+                       cudaStream_t stream, int64_t *launches);
+// true when the binned path is implemented for this (dim, order)
+bool binned_supported(int dim, int order);
+
+} // namespace bz

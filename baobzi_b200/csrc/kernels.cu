@@ -1,0 +1,146 @@
+// kernels.cu -- sm_100a kernels of the batched evaluation path and their launchers.
+//
+// Reference path being replaced (include/baobzi_template.hpp): Function::eval(xp, res, n) 866-889 ->
+// bounds test 872-873 -> get_linear_bin 799-820 -> get_node_index 482-493 -> Node::eval 366-369 ->
+// cheb_eval 146-194.  See device_tree.hpp for the device layout and cheb.cuh for the arithmetic.
+//
+// Two execution strategies:
+//   direct  one fused kernel, one thread per point: bounds -> grid cell -> descent -> affine map ->
+//           Chebyshev sum with the leaf's coefficients fetched through L1/L2.  HBM-bound for 1D and
+//           small 2D blocks, L2-gather-bound when every lane of a warp sits in a different leaf with a
+//           multi-KB block (3D).
+//   binned  for large blocks: per L2-resident chunk of points, (1) lookup + histogram by leaf,
+//           (2) padded exclusive scan, (3) scatter of point indices into leaf-contiguous, warp-tile
+//           aligned slots, (4) evaluation where every warp works on ONE leaf, so each 16-byte
+//           coefficient load is a warp-uniform broadcast served from L1 and feeds 2*P FMAs
+//           (P points per thread, register blocked).  FP64-pipe bound.
+#include "cheb.cuh"
+#include "device_tree.hpp"
+#include "host_tree.hpp"
+#include "lookup.cuh"
+
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+namespace bz {
+
+// Node::eval (template.hpp:366-369) for the first output component.
+template <int DIM, int ORDER>
+__device__ __forceinline__ double eval_leaf(const TreeView &tv, uint32_t node, const NodeHead &head,
+                                            const double (&x)[DIM]) {
+    const NodeTail tail = load_tail(tv.nodes, node);
+    const double *C = tv.coeffs + 2ull * head.coeff16;
+    const double u = __dmul_rn(__dsub_rn(x[0], head.c0), tail.ih0);
+    if constexpr (DIM == 1) {
+        return cheb_eval_1d<ORDER>(u, C);
+    } else if constexpr (DIM == 2) {
+        const double v = __dmul_rn(__dsub_rn(x[1], head.c1), tail.ih1);
+        return cheb_eval_2d<ORDER>(u, v, C, LdgLoad());
+    } else {
+        const double v = __dmul_rn(__dsub_rn(x[1], head.c1), tail.ih1);
+        const double w = __dmul_rn(__dsub_rn(x[2], head.c2), tail.ih2);
+        return cheb_eval_3d<ORDER>(u, v, w, C, LdgLoad());
+    }
+}
+
+// ------------------------------------------------------------------------------------------ direct
+constexpr int kDirectThreads = 128;
+
+template <int DIM, int ORDER>
+__global__ void __launch_bounds__(kDirectThreads)
+eval_direct_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                   int64_t *__restrict__ node_idx, int64_t n) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        double p[DIM];
+        load_point<DIM>(x, i, p);
+        if (outside<DIM>(tv, p)) {
+            if (res)
+                __stcs(res + i, __longlong_as_double(0x7ff8000000000000ll)); // NAN, template.hpp:880-881
+            if (node_idx)
+                node_idx[i] = -1;
+            continue;
+        }
+        NodeHead head;
+        const uint32_t node = locate<DIM>(tv, p, head);
+        if (node_idx)
+            node_idx[i] = (int64_t)node;
+        if (res)
+            __stcs(res + i, eval_leaf<DIM, ORDER>(tv, node, head, p));
+    }
+}
+
+// Scalar twin (template.hpp:851-860 -> Node::eval(x, res, coeffs) 371-375): out_dim values, block k of
+// ORDER... the reference indexes `coeffs + coeff_offset + k*ORDER` for every DIM; only DIM == 1 is
+// meaningful and for DIM > 1 we evaluate component 0 only.
+template <int DIM, int ORDER>
+__global__ void eval_scalar_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ y) {
+    const uint32_t k = threadIdx.x;
+    if (k >= tv.out_dim)
+        return;
+    double p[DIM];
+#pragma unroll
+    for (int j = 0; j < DIM; ++j)
+        p[j] = x[j];
+    if (outside<DIM>(tv, p)) {
+        y[k] = __longlong_as_double(0x7ff8000000000000ll);
+        return;
+    }
+    NodeHead head;
+    const uint32_t node = locate<DIM>(tv, p, head);
+    if constexpr (DIM == 1) {
+        const NodeTail tail = load_tail(tv.nodes, node);
+        if (k >= tail.out_dim)
+            return;
+        const double u = __dmul_rn(__dsub_rn(p[0], head.c0), tail.ih0);
+        y[k] = cheb_eval_1d<ORDER>(u, tv.coeffs + 2ull * head.coeff16 + (size_t)k * ORDER);
+    } else {
+        if (k == 0)
+            y[0] = eval_leaf<DIM, ORDER>(tv, node, head, p);
+    }
+}
+
+#define BZ_DISPATCH_ORDER(DIM, order, CALL)                                                                            \
+    switch (order) {                                                                                                   \
+    case 6: { constexpr int O = 6; constexpr int D = DIM; CALL; } break;                                               \
+    case 8: { constexpr int O = 8; constexpr int D = DIM; CALL; } break;                                               \
+    case 10: { constexpr int O = 10; constexpr int D = DIM; CALL; } break;                                             \
+    case 12: { constexpr int O = 12; constexpr int D = DIM; CALL; } break;                                             \
+    case 14: { constexpr int O = 14; constexpr int D = DIM; CALL; } break;                                             \
+    case 16: { constexpr int O = 16; constexpr int D = DIM; CALL; } break;                                             \
+    default: return (int)cudaErrorInvalidValue;                                                                        \
+    }
+
+#define BZ_DISPATCH(dim, order, CALL)                                                                                  \
+    switch (dim) {                                                                                                     \
+    case 1: BZ_DISPATCH_ORDER(1, order, CALL) break;                                                                   \
+    case 2: BZ_DISPATCH_ORDER(2, order, CALL) break;                                                                   \
+    case 3: BZ_DISPATCH_ORDER(3, order, CALL) break;                                                                   \
+    default: return (int)cudaErrorInvalidValue;                                                                        \
+    }
+
+int launch_eval_direct(const DeviceTree &dt, const double *d_x, double *d_res, int64_t *d_node_idx, int64_t n,
+                       cudaStream_t stream, int64_t *launches) {
+    if (n <= 0)
+        return 0;
+    // enough CTAs to fill every SM several times over, capped so the grid-stride loop amortises launch cost
+    const int64_t want = (n + kDirectThreads - 1) / kDirectThreads;
+    const int64_t cap = (int64_t)dt.sm_count * 64;
+    const unsigned grid = (unsigned)(want < cap ? want : cap);
+    BZ_DISPATCH(dt.view.dim, dt.view.order,
+                (eval_direct_kernel<D, O><<<grid, kDirectThreads, 0, stream>>>(dt.view, d_x, d_res, d_node_idx, n)));
+    if (launches)
+        *launches += 1;
+    return (int)cudaGetLastError();
+}
+
+int launch_eval_scalar(const DeviceTree &dt, const double *d_x, double *d_y, cudaStream_t stream, int64_t *launches) {
+    const unsigned threads = dt.view.out_dim < 1 ? 1 : (dt.view.out_dim > 1024 ? 1024 : dt.view.out_dim);
+    BZ_DISPATCH(dt.view.dim, dt.view.order, (eval_scalar_kernel<D, O><<<1, threads, 0, stream>>>(dt.view, d_x, d_y)));
+    if (launches)
+        *launches += 1;
+    return (int)cudaGetLastError();
+}
+
+} // namespace bz

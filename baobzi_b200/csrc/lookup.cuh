@@ -1,0 +1,109 @@
+// lookup.cuh -- device code shared by the direct and binned kernels: node record loads, the bounds
+// test, the grid-cell floor transform and the subtree descent.
+#pragma once
+
+#include "device_tree.hpp"
+
+#include <cuda_runtime.h>
+
+namespace bz {
+
+// ------------------------------------------------------------------------------------------ lookup
+struct NodeHead { // first 32-byte sector of a NodeRec
+    double c0, c1, c2;
+    uint32_t child0, coeff16;
+};
+
+__device__ __forceinline__ NodeHead load_head(const NodeRec *nodes, uint32_t node) {
+    const double2 *p = reinterpret_cast<const double2 *>(nodes + node);
+    const double2 a = __ldg(p), b = __ldg(p + 1);
+    NodeHead h;
+    h.c0 = a.x;
+    h.c1 = a.y;
+    h.c2 = b.x;
+    const unsigned long long w = (unsigned long long)__double_as_longlong(b.y);
+    h.child0 = (uint32_t)w;
+    h.coeff16 = (uint32_t)(w >> 32);
+    return h;
+}
+
+struct NodeTail { // second sector
+    double ih0, ih1, ih2;
+    uint32_t out_dim, leaf_rank;
+};
+
+__device__ __forceinline__ NodeTail load_tail(const NodeRec *nodes, uint32_t node) {
+    const double2 *p = reinterpret_cast<const double2 *>(nodes + node) + 2;
+    const double2 a = __ldg(p), b = __ldg(p + 1);
+    NodeTail t;
+    t.ih0 = a.x;
+    t.ih1 = a.y;
+    t.ih2 = b.x;
+    const unsigned long long w = (unsigned long long)__double_as_longlong(b.y);
+    t.out_dim = (uint32_t)w;
+    t.leaf_rank = (uint32_t)(w >> 32);
+    return t;
+}
+
+// Bounds test of template.hpp:872-873: outside if any x < lower_left or any x >= upper_right
+// (comparisons with NaN are false, so NaN is "inside", as in the reference, and propagates to the result).
+template <int DIM>
+__device__ __forceinline__ bool outside(const TreeView &tv, const double (&x)[DIM]) {
+    bool out = false;
+#pragma unroll
+    for (int j = 0; j < DIM; ++j)
+        out = out || (x[j] < tv.lower_left[j]) || (x[j] >= tv.upper_right[j]);
+    return out;
+}
+
+// get_linear_bin (template.hpp:799-820): (int)((x - ll) * inv_bin), x fastest; then the subtree descent
+// (template.hpp:482-493): child bit j = x[j] > centre[j].  The bin is clamped to the grid (the reference
+// reads out of bounds when rounding pushes a point just under upper_right into bin n).
+template <int DIM>
+__device__ __forceinline__ uint32_t locate(const TreeView &tv, const double (&x)[DIM], NodeHead &head) {
+    int lin = 0, stride = 1;
+#pragma unroll
+    for (int j = 0; j < DIM; ++j) {
+        const double xb = __dsub_rn(x[j], tv.lower_left[j]);
+        int b = __double2int_rz(__dmul_rn(xb, tv.inv_bin_size[j]));
+        b = min(max(b, 0), tv.n_sub[j] - 1);
+        lin += stride * b;
+        stride *= tv.n_sub[j];
+    }
+    uint32_t node = __ldg(tv.bin_root + lin);
+    head = load_head(tv.nodes, node);
+    while (head.child0 != kLeafMark) {
+        uint32_t bits = (uint32_t)(x[0] > head.c0);
+        if (DIM > 1)
+            bits |= (uint32_t)(x[1] > head.c1) << 1;
+        if (DIM > 2)
+            bits |= (uint32_t)(x[2] > head.c2) << 2;
+        node = head.child0 + bits;
+        head = load_head(tv.nodes, node);
+    }
+    return node;
+}
+
+template <int DIM>
+__device__ __forceinline__ void load_point(const double *__restrict__ x, int64_t i, double (&p)[DIM]) {
+    if constexpr (DIM == 2) {
+        const double2 v = __ldcs(reinterpret_cast<const double2 *>(x) + i); // streamed once
+        p[0] = v.x;
+        p[1] = v.y;
+    } else {
+#pragma unroll
+        for (int j = 0; j < DIM; ++j)
+            p[j] = __ldcs(x + i * DIM + j);
+    }
+}
+
+
+// same, but with the default cache policy: the binned path reads each point twice (lookup, then gather)
+template <int DIM>
+__device__ __forceinline__ void load_point_keep(const double *__restrict__ x, size_t i, double (&p)[DIM]) {
+#pragma unroll
+    for (int j = 0; j < DIM; ++j)
+        p[j] = __ldg(x + i * DIM + j);
+}
+
+} // namespace bz

@@ -1,0 +1,151 @@
+/* baobzi.h -- C ABI of the B200-native libbaobzi.so (drop-in for the reference's include/baobzi.h).
+ *
+ * Every declaration in the "reference ABI" section is binary-compatible with the reference header
+ * (citations are file:line in flatironinstitute/baobzi): same symbol names, same argument meaning,
+ * same struct layouts, same error behaviour (NULL + a message on stderr; evaluation has no error
+ * channel and yields NaN outside the semi-open domain [center - half_length, center + half_length)).
+ * What differs is what happens behind the handle: on baobzi_init / baobzi_restore the fitted tree is
+ * flattened into device arrays on a B200 and every evaluation entry point launches hand-written
+ * sm_100a CUDA kernels.  There is no CPU evaluation path; without a usable CUDA device
+ * baobzi_init / baobzi_restore fail (NULL).
+ *
+ * The "device extension" section is new: evaluation on device-resident points/results, node-index
+ * queries (for parity testing) and multi-GPU point sharding.
+ */
+#ifndef BAOBZI_B200_BAOBZI_H
+#define BAOBZI_B200_BAOBZI_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ============================== reference ABI ============================================== */
+
+/* .baobzi container version written/accepted (reference include/baobzi/header.h:4) */
+#define BAOBZI_HEADER_VERSION 5
+
+/* First msgpack object of a .baobzi file (reference include/baobzi/header.h:10-18). */
+typedef struct {
+    int dim;
+    int order;
+    int version;
+} baobzi_header_t;
+
+/* User callback y = f(x; data): x has `dim` entries, y has `output_dim` (reference baobzi.h:13). */
+typedef void (*baobzi_input_func_t)(const double *x, double *y, const void *data);
+
+/* How `tol` is interpreted by the fitter (reference baobzi.h:15-18). */
+typedef enum {
+    BAOBZI_TOL_RELATIVE = 0,
+    BAOBZI_TOL_ABSOLUTE = 1,
+} baobzi_tol_t;
+
+/* Fit parameters (reference baobzi.h:21-38; field order and types are ABI).
+ * Supported: dim in {1,2,3}; order in {6,8,10,12,14,16} (reference make_source.sh:11-13).
+ * split_multi_eval is a CPU cache heuristic of the reference: accepted, persisted, ignored. */
+struct baobzi_input_t {
+    baobzi_input_func_t func;
+    void *data;
+    int dim;
+    int output_dim;
+    int order;
+    double tol;
+    double minimum_leaf_fraction;
+    int split_multi_eval;
+    int min_depth;
+    int max_depth;
+    baobzi_tol_t tol_type;
+#ifdef __cplusplus
+    /* same defaults as the reference's C++ constructor (baobzi.h:33-37) */
+    baobzi_input_t()
+        : func(nullptr), data(nullptr), dim(0), output_dim(1), order(8), tol(0.0), minimum_leaf_fraction(0.0),
+          split_multi_eval(1), min_depth(0), max_depth(50), tol_type(BAOBZI_TOL_RELATIVE) {}
+#endif
+};
+typedef struct baobzi_input_t baobzi_input_t;
+
+/* The handle (reference baobzi.h:47-57).  Callers read DIM / OUTPUT_DIM / ORDER directly
+ * (examples/C/baobzi_timing.c:44-45, src/python/__init__.py:95-97), so the layout is ABI.
+ * `obj` is opaque: here it owns the host copy of the tree plus its device replicas. */
+typedef struct {
+    void *obj;
+    int DIM;
+    int OUTPUT_DIM;
+    int ORDER;
+    void (*eval)(const void *, const double *, double *);
+    void (*eval_multi)(const void *, const double *, double *, int ntrg);
+    void (*save)(const void *, const char *);
+    void (*stats)(void *);
+    void (*free)(void *);
+} baobzi_struct;
+
+typedef baobzi_struct *baobzi_t;
+
+/* output_dim=1, order=8, split_multi_eval=1, max_depth=50, relative tol; everything else zero
+ * (reference src/baobzi.cpp:16). */
+extern const baobzi_input_t baobzi_input_default;
+
+/* Fit `input->func` on the box center +- half_length, then flatten + upload (reference baobzi.cpp:147-184).
+ * The callback runs on the host.  NULL + stderr message on: tol <= 0, NULL func, unsupported
+ * (dim, order), max_depth exceeded, or no usable CUDA device. */
+baobzi_t baobzi_init(const baobzi_input_t *input, const double *center, const double *half_length);
+
+/* Read a version-5 .baobzi file, flatten + upload (reference baobzi.cpp:75-116).  NULL on failure. */
+baobzi_t baobzi_restore(const char *filename);
+
+/* Write a version-5 .baobzi file the reference can restore (reference baobzi_template.hpp:914-919). */
+void baobzi_save(const baobzi_t func, const char *filename);
+
+/* One point: x[DIM] -> y[OUTPUT_DIM] (reference baobzi.cpp:61).  Runs the same CUDA kernel with n = 1. */
+void baobzi_eval(const baobzi_t func, const double *x, double *y);
+
+/* Batched: x[ntrg][DIM] (point-major) -> res[ntrg], first output component (reference baobzi.cpp:63-65,
+ * baobzi_template.hpp:866-889).  x / res are HOST pointers (pageable or pinned); the call pipelines
+ * H2D copy, kernels and D2H copy in chunks and returns when res is complete. */
+void baobzi_eval_multi(const baobzi_t func, const double *x, double *res, int ntrg);
+
+/* Print a summary to stdout (reference baobzi.cpp:118-122); NULL-safe. */
+void baobzi_stats(baobzi_t func);
+
+/* Release host + device state; returns NULL; NULL-safe (reference baobzi.cpp:124-131). */
+baobzi_t baobzi_free(baobzi_t func);
+
+/* ============================== device extension =========================================== */
+
+/* Batched evaluation with DEVICE pointers on the device that owns d_x (must be a device the handle
+ * has a replica on; replicas are created lazily).  Asynchronous on `cuda_stream` (a cudaStream_t,
+ * NULL = legacy default stream).  64-bit count.  Returns 0 or a cudaError_t value. */
+int baobzi_eval_multi_device(const baobzi_t func, const double *d_x, double *d_res, int64_t ntrg, void *cuda_stream);
+
+/* Global node index per point, exactly Function::get_global_node_index of the reference
+ * (baobzi_template.hpp:846-849; all nodes, subtree-major, breadth-first inside a subtree);
+ * -1 outside the domain.  Device and host pointer variants. */
+int baobzi_node_index_multi_device(const baobzi_t func, const double *d_x, int64_t *d_idx, int64_t ntrg,
+                                   void *cuda_stream);
+int baobzi_node_index_multi(const baobzi_t func, const double *x, int64_t *idx, int64_t ntrg);
+
+/* Point-sharded evaluation across n_dev GPUs: shard k is d_x[k] / d_res[k] with ntrg[k] points, resident
+ * on device devices[k].  The tree is replicated; there is no collective.  Launches are asynchronous on
+ * per-device internal streams; baobzi_sync waits for all of them.  Returns 0 or a cudaError_t value. */
+int baobzi_eval_multi_sharded(const baobzi_t func, int n_dev, const int *devices, const double *const *d_x,
+                              double *const *d_res, const int64_t *ntrg);
+int baobzi_sync(const baobzi_t func);
+
+/* Tuning knobs (also readable from the environment at init/restore):
+ *   mode: 0 = auto, 1 = direct (one fused kernel, thread per point), 2 = binned (points grouped by leaf in
+ *   L2-resident chunks before a register-blocked evaluation).  BAOBZI_B200_MODE=auto|direct|binned.
+ *   chunk: points per binned chunk (0 = default).  BAOBZI_B200_CHUNK. */
+int baobzi_set_mode(baobzi_t func, int mode, int64_t chunk);
+
+/* Counters for tests / benchmarks: number of kernel launches issued through this handle so far. */
+int64_t baobzi_launch_count(const baobzi_t func);
+
+/* Library identification string, e.g. "baobzi-b200 0.1 (sm_100a)". */
+const char *baobzi_b200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
