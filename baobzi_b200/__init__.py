@@ -1,0 +1,245 @@
+"""baobzi_b200 -- host-side mirror of the reference's Python binding (src/python/__init__.py) on top of the
+B200-native libbaobzi.so built from baobzi_b200/csrc.
+
+`Baobzi` keeps the reference class's constructor arguments, `__call__`, `save` and `stats`
+(reference src/python/__init__.py:77-138) and adds the device entry points of include/baobzi.h:
+torch CUDA tensors (or anything with ``__cuda_array_interface__``) are evaluated in place, zero copy.
+
+There is no CPU evaluation path: importing works anywhere (so the ABI can be inspected), but creating a
+`Baobzi` needs the CUDA library and a GPU and fails loudly otherwise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+__all__ = ["Baobzi", "load_library", "library_path", "build", "BaobziInput", "BaobziStruct"]
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "lib", "libbaobzi.so")
+_lib = None
+
+c_double_p = C.POINTER(C.c_double)
+INPUT_FUNC = C.CFUNCTYPE(None, c_double_p, c_double_p, C.c_void_p)
+
+
+class BaobziInput(C.Structure):
+    """baobzi_input_t, include/baobzi.h (reference baobzi.h:21-38; the reference's own ctypes mirror at
+    src/python/__init__.py:40-44 is stale -- it lacks tol_type)."""
+    _fields_ = [("func", C.c_void_p), ("data", C.c_void_p), ("dim", C.c_int), ("output_dim", C.c_int),
+                ("order", C.c_int), ("tol", C.c_double), ("minimum_leaf_fraction", C.c_double),
+                ("split_multi_eval", C.c_int), ("min_depth", C.c_int), ("max_depth", C.c_int),
+                ("tol_type", C.c_int)]
+
+
+class BaobziStruct(C.Structure):
+    """baobzi_struct, include/baobzi.h (reference baobzi.h:47-57)."""
+    _fields_ = [("obj", C.c_void_p), ("dim", C.c_int), ("output_dim", C.c_int), ("order", C.c_int),
+                ("eval", C.c_void_p), ("eval_multi", C.c_void_p), ("save", C.c_void_p),
+                ("stats", C.c_void_p), ("free", C.c_void_p)]
+
+
+baobzi_t = C.POINTER(BaobziStruct)
+
+# every symbol include/baobzi.h declares: name -> (restype, argtypes)
+ABI = {
+    "baobzi_init": (baobzi_t, [C.POINTER(BaobziInput), c_double_p, c_double_p]),
+    "baobzi_restore": (baobzi_t, [C.c_char_p]),
+    "baobzi_save": (None, [baobzi_t, C.c_char_p]),
+    "baobzi_eval": (None, [baobzi_t, C.c_void_p, C.c_void_p]),
+    "baobzi_eval_multi": (None, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int]),
+    "baobzi_stats": (None, [baobzi_t]),
+    "baobzi_free": (baobzi_t, [baobzi_t]),
+    "baobzi_eval_multi_device": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "baobzi_node_index_multi_device": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "baobzi_node_index_multi": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64]),
+    "baobzi_eval_multi_sharded": (C.c_int, [baobzi_t, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_void_p),
+                                            C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
+    "baobzi_sync": (C.c_int, [baobzi_t]),
+    "baobzi_set_mode": (C.c_int, [baobzi_t, C.c_int, C.c_int64]),
+    "baobzi_launch_count": (C.c_int64, [baobzi_t]),
+    "baobzi_b200_version": (C.c_char_p, []),
+}
+DATA_SYMBOLS = ["baobzi_input_default"]
+MODES = {"auto": 0, "direct": 1, "binned": 2}
+
+
+def library_path():
+    return _LIB_PATH
+
+
+def build(verbose=False):
+    """Compile baobzi_b200/csrc into baobzi_b200/lib/libbaobzi.so with nvcc for sm_100a (no GPU needed)."""
+    import subprocess
+    cmd = ["make", "-C", os.path.join(_HERE, "csrc"), "-j", str(min(16, os.cpu_count() or 4))]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if verbose or r.returncode != 0:
+        print(r.stdout)
+    if r.returncode != 0:
+        raise RuntimeError("building libbaobzi.so failed")
+    return _LIB_PATH
+
+
+def load_library():
+    """dlopen the CUDA library and declare its ABI.  Raises if it has not been built -- nothing falls back."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise OSError("baobzi_b200: %s is missing; run baobzi_b200.build() (needs nvcc). "
+                          "There is no CPU fallback." % _LIB_PATH)
+        lib = C.CDLL(_LIB_PATH)
+        for name, (res, args) in ABI.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def _device_pointer(a):
+    """(pointer, element count, keepalive) for a CUDA array: torch tensor or __cuda_array_interface__."""
+    if hasattr(a, "data_ptr") and hasattr(a, "is_cuda"):
+        if not a.is_cuda:
+            return None
+        import torch
+        if a.dtype != torch.float64 or not a.is_contiguous():
+            raise TypeError("CUDA input must be a contiguous float64 tensor")
+        return a.data_ptr(), a.numel(), a
+    cai = getattr(a, "__cuda_array_interface__", None)
+    if cai is not None:
+        if cai["typestr"] not in ("<f8", "=f8") or cai.get("strides") is not None:
+            raise TypeError("CUDA input must be contiguous float64")
+        n = 1
+        for s in cai["shape"]:
+            n *= s
+        return cai["data"][0], n, a
+    return None
+
+
+class Baobzi:
+    """Same surface as the reference's ``Baobzi`` (src/python/__init__.py:77-138).
+
+    ``fin`` is a Python callable f(x) -> float or sequence (x is a numpy view of `dim` doubles) or the address
+    of a C function with the baobzi_input_func_t signature.
+    """
+
+    def __init__(self, fin=None, dim=None, order=None, center=None, half_length=None, tol=None, output_dim=1,
+                 minimum_leaf_fraction=0.0, split_multi_eval=1, min_depth=0, max_depth=50, filename=None,
+                 data=None, tol_type=0, mode=None):
+        self.ptr = None
+        lib = self._lib = load_library()
+        if filename:
+            self.ptr = lib.baobzi_restore(os.fsencode(filename))
+        elif fin is not None:
+            if not (dim and order and center is not None and half_length is not None and tol):
+                raise ValueError("Baobzi: supply dim, order, center, half_length, and tol for init")
+            inp = BaobziInput()
+            if callable(fin):
+                def trampoline(xp, yp, _data, _f=fin, _d=dim, _o=output_dim):
+                    y = np.atleast_1d(np.asarray(_f(np.ctypeslib.as_array(xp, (_d,))), dtype=np.float64))
+                    for k in range(_o):
+                        yp[k] = y[k]
+                self._cb = INPUT_FUNC(trampoline)
+                inp.func = C.cast(self._cb, C.c_void_p)
+            else:
+                inp.func = int(fin)
+            self._data = None
+            if data is not None:
+                self._data = C.c_double(float(data))
+                inp.data = C.cast(C.pointer(self._data), C.c_void_p)
+            inp.dim, inp.output_dim, inp.order, inp.tol = dim, output_dim, order, tol
+            inp.minimum_leaf_fraction, inp.split_multi_eval = minimum_leaf_fraction, split_multi_eval
+            inp.min_depth, inp.max_depth, inp.tol_type = min_depth, max_depth, tol_type
+            c = np.ascontiguousarray(center, dtype=np.float64)
+            h = np.ascontiguousarray(half_length, dtype=np.float64)
+            self.ptr = lib.baobzi_init(C.byref(inp), c.ctypes.data_as(c_double_p), h.ctypes.data_as(c_double_p))
+        else:
+            raise ValueError("Baobzi requires either a 'filename' argument or a 'fin' argument")
+        if not self.ptr or not self.ptr[0].obj:
+            self.ptr = None
+            raise RuntimeError("Unable to create baobzi object")
+        self.dim, self.output_dim, self.order = self.ptr[0].dim, self.ptr[0].output_dim, self.ptr[0].order
+        if mode is not None:
+            self.set_mode(mode)
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    def free(self):
+        if getattr(self, "ptr", None):
+            self._lib.baobzi_free(self.ptr)
+            self.ptr = None
+
+    # ---- evaluation -------------------------------------------------------------------------------
+    def __call__(self, x, out=None, stream=None):
+        """Evaluate at points x ([n, dim] or flat).  numpy in -> numpy out through baobzi_eval_multi (host
+        pointers); CUDA tensor in -> CUDA tensor out through baobzi_eval_multi_device (zero copy)."""
+        dp = _device_pointer(x)
+        if dp is not None:
+            ptr, count, _keep = dp
+            n = count // self.dim
+            if out is None:
+                import torch
+                out = torch.empty(n, dtype=torch.float64, device=x.device)
+            optr = _device_pointer(out)[0]
+            if stream is None and hasattr(x, "is_cuda"):
+                import torch
+                stream = torch.cuda.current_stream(x.device).cuda_stream
+            rc = self._lib.baobzi_eval_multi_device(self.ptr, ptr, optr, n, stream or 0)
+            if rc != 0:
+                raise RuntimeError("baobzi_eval_multi_device failed with CUDA error %d" % rc)
+            return out
+        xarr = np.ascontiguousarray(x, dtype=np.float64)
+        n = xarr.size // self.dim
+        if n > 2**31 - 1:
+            raise ValueError("baobzi_eval_multi takes an int count; use the device entry for more points")
+        res = out if out is not None else np.empty(n, dtype=np.float64)
+        self._lib.baobzi_eval_multi(self.ptr, xarr.ctypes.data, res.ctypes.data, n)
+        return res
+
+    def eval(self, x):
+        """One point through baobzi_eval: returns output_dim values."""
+        xarr = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.empty(max(1, self.output_dim), dtype=np.float64)
+        self._lib.baobzi_eval(self.ptr, xarr.ctypes.data, y.ctypes.data)
+        return y
+
+    def node_index(self, x):
+        """Global node index per point (the reference's Function::get_global_node_index), -1 outside."""
+        dp = _device_pointer(x)
+        if dp is not None:
+            import torch
+            ptr, count, _keep = dp
+            n = count // self.dim
+            out = torch.empty(n, dtype=torch.int64, device=x.device)
+            rc = self._lib.baobzi_node_index_multi_device(self.ptr, ptr, out.data_ptr(), n,
+                                                          torch.cuda.current_stream(x.device).cuda_stream)
+            if rc != 0:
+                raise RuntimeError("baobzi_node_index_multi_device failed with CUDA error %d" % rc)
+            return out
+        xarr = np.ascontiguousarray(x, dtype=np.float64)
+        n = xarr.size // self.dim
+        idx = np.empty(n, dtype=np.int64)
+        rc = self._lib.baobzi_node_index_multi(self.ptr, xarr.ctypes.data, idx.ctypes.data, n)
+        if rc != 0:
+            raise RuntimeError("baobzi_node_index_multi failed with CUDA error %d" % rc)
+        return idx
+
+    # ---- the rest of the reference surface ----------------------------------------------------------
+    def save(self, filename):
+        self._lib.baobzi_save(self.ptr, os.fsencode(filename))
+
+    def stats(self):
+        self._lib.baobzi_stats(self.ptr)
+
+    # ---- extension knobs ----------------------------------------------------------------------------
+    def set_mode(self, mode, chunk=0):
+        m = MODES[mode] if isinstance(mode, str) else int(mode)
+        if self._lib.baobzi_set_mode(self.ptr, m, int(chunk)) != 0:
+            raise ValueError("bad mode")
+
+    @property
+    def launches(self):
+        return int(self._lib.baobzi_launch_count(self.ptr))
