@@ -58,6 +58,9 @@ ABI = {
     "baobzi_sync": (C.c_int, [baobzi_t]),
     "baobzi_set_mode": (C.c_int, [baobzi_t, C.c_int, C.c_int64]),
     "baobzi_launch_count": (C.c_int64, [baobzi_t]),
+    "baobzi_profile_begin": (C.c_int, [baobzi_t]),
+    "baobzi_profile_end": (C.c_int, [baobzi_t, c_double_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "baobzi_b200_fp64_peak": (C.c_int, [c_double_p]),
     "baobzi_b200_version": (C.c_char_p, []),
 }
 DATA_SYMBOLS = ["baobzi_input_default"]
@@ -239,6 +242,21 @@ class Baobzi:
         m = MODES[mode] if isinstance(mode, str) else int(mode)
         if self._lib.baobzi_set_mode(self.ptr, m, int(chunk)) != 0:
             raise ValueError("bad mode")
+
+    STAGES = ("lookup", "scan", "scatter", "eval_binned", "eval_direct")
+
+    def profile_begin(self):
+        self._lib.baobzi_profile_begin(self.ptr)
+
+    def profile_end(self):
+        """{stage: (total ms, launches, points)} for the kernels launched since profile_begin (synchronises)."""
+        ms = (C.c_double * 5)()
+        la = (C.c_int64 * 5)()
+        pts = (C.c_int64 * 5)()
+        rc = self._lib.baobzi_profile_end(self.ptr, ms, la, pts)
+        if rc != 0:
+            raise RuntimeError("baobzi_profile_end failed with CUDA error %d" % rc)
+        return {s: (ms[i], la[i], pts[i]) for i, s in enumerate(self.STAGES)}
 
     @property
     def launches(self):

@@ -54,6 +54,7 @@ struct Function {
     int mode = kAuto;
     int64_t chunk = 0;
     std::atomic<int64_t> launches{0};
+    std::unique_ptr<StageProfile> profile; // non-null while baobzi_profile_begin .. _end
 };
 
 namespace {
@@ -172,19 +173,23 @@ int eval_device(Function *f, Replica *r, BinWorkspace &ws, const double *d_x, do
                 cudaStream_t stream) {
     int64_t launches = 0;
     int rc = 0;
+    StageProfile *prof = f->profile.get();
+    ws.prof = prof;
     if (use_binned(f, r->dt, n)) {
-        const int64_t chunk = f->chunk > 0 ? f->chunk : default_chunk();
-        if (ws.chunk_capacity < (n < chunk ? n : chunk)) {
+        int64_t step = f->chunk > 0 ? f->chunk : default_chunk();
+        if (step > n)
+            step = n;
+        if (ws.chunk_capacity < step) {
             cudaStreamSynchronize(stream);
             free_workspace(ws);
-            rc = alloc_workspace(r->dt, n < chunk ? n : chunk, ws);
+            rc = alloc_workspace(r->dt, step, ws);
         }
-        for (int64_t o = 0; o < n && rc == 0; o += ws.chunk_capacity) {
-            const int64_t m = n - o < ws.chunk_capacity ? n - o : ws.chunk_capacity;
+        for (int64_t o = 0; o < n && rc == 0; o += step) {
+            const int64_t m = n - o < step ? n - o : step;
             rc = launch_eval_binned(r->dt, ws, d_x + o * r->dt.view.dim, d_res + o, m, stream, &launches);
         }
     } else {
-        rc = launch_eval_direct(r->dt, d_x, d_res, nullptr, n, stream, &launches);
+        rc = launch_eval_direct(r->dt, d_x, d_res, nullptr, n, stream, &launches, prof);
     }
     f->launches += launches;
     return rc;
@@ -573,5 +578,25 @@ int baobzi_set_mode(baobzi_t func, int mode, int64_t chunk) {
 }
 
 int64_t baobzi_launch_count(const baobzi_t func) { return ((Function *)func->obj)->launches.load(); }
+
+int baobzi_profile_begin(baobzi_t func) {
+    Function *f = (Function *)func->obj;
+    std::lock_guard<std::mutex> lock(f->mu);
+    f->profile = std::make_unique<bz::StageProfile>();
+    return 0;
+}
+
+int baobzi_profile_end(baobzi_t func, double *ms, int64_t *launches, int64_t *points) {
+    Function *f = (Function *)func->obj;
+    cudaError_t e = cudaDeviceSynchronize();
+    std::lock_guard<std::mutex> lock(f->mu);
+    if (!f->profile)
+        return (int)cudaErrorInvalidValue;
+    f->profile->collect(ms, launches, points);
+    f->profile.reset();
+    return (int)e;
+}
+
+int baobzi_b200_fp64_peak(double *tflops) { return bz::measure_fp64_peak(tflops, 5); }
 
 } // extern "C"

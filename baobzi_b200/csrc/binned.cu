@@ -273,12 +273,32 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
     const unsigned cap = (unsigned)dt.sm_count * 16;
     unsigned g1 = (n + kBinThreads - 1) / kBinThreads;
     g1 = g1 < cap ? g1 : cap;
+    StageProfile *pf = ws.prof;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (pf) {
+        for (auto &e : ev)
+            e = pf->get();
+        cudaEventRecord(ev[0], st);
+    }
     bin_lookup_kernel<3><<<g1, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.key, ws.count, n);
+    if (pf)
+        cudaEventRecord(ev[1], st);
     bin_scan_kernel<TILE><<<1, 1024, 0, st>>>(tv.n_leaves, ws.count, ws.start, ws.tile_leaf, ws.perm, ws.n_tiles);
+    if (pf)
+        cudaEventRecord(ev[2], st);
     bin_scatter_kernel<<<g1, kBinThreads, 0, st>>>(ws.key, ws.start, ws.count, ws.perm, n);
+    if (pf)
+        cudaEventRecord(ev[3], st);
     // persistent grid: 2 CTAs of 8 warps per SM, each CTA walks 8 consecutive tiles (same leaf, L1 reuse)
     const unsigned g4 = (unsigned)dt.sm_count * 2;
     bin_eval3d_kernel<O, P><<<g4, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.perm, ws.tile_leaf, ws.n_tiles);
+    if (pf) {
+        cudaEventRecord(ev[4], st);
+        pf->spans.push_back({kStageLookup, ev[0], ev[1], (int64_t)n});
+        pf->spans.push_back({kStageScan, ev[1], ev[2], (int64_t)n});
+        pf->spans.push_back({kStageScatter, ev[2], ev[3], (int64_t)n});
+        pf->spans.push_back({kStageEval, ev[3], ev[4], (int64_t)n});
+    }
     return (int)cudaGetLastError();
 }
 

@@ -20,6 +20,7 @@
 
 #include <cstdint>
 #include <cuda_runtime_api.h>
+#include <vector>
 
 namespace bz {
 
@@ -50,6 +51,24 @@ struct TreeView {
     const uint32_t *leaf_node;
 };
 
+// Optional per-launch timing (bench.py's roofline): when attached to a workspace / launch, every kernel is
+// bracketed by CUDA events on the launching stream; elapsed times are summed per stage after a sync.
+enum Stage { kStageLookup = 0, kStageScan = 1, kStageScatter = 2, kStageEval = 3, kStageDirect = 4, kNumStages = 5 };
+struct StageProfile {
+    struct Span {
+        int stage;
+        cudaEvent_t begin, end;
+        int64_t points;
+    };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> pool;
+    cudaEvent_t get();
+    void mark(int stage, int64_t points, cudaEvent_t b, cudaEvent_t e) { spans.push_back({stage, b, e, points}); }
+    // sums (ms), launch counts and point counts per stage; recycles the events.  Caller must have synchronised.
+    void collect(double ms[kNumStages], int64_t launches[kNumStages], int64_t points[kNumStages]);
+    ~StageProfile();
+};
+
 // Workspace of the binned path for one chunk of points (device memory, reused chunk after chunk so it
 // stays resident in L2).
 struct BinWorkspace {
@@ -61,6 +80,7 @@ struct BinWorkspace {
     uint32_t *tile_leaf = nullptr; // [max_tiles]     leaf rank of each warp tile
     uint32_t *n_tiles = nullptr;   // [1]
     int64_t perm_capacity = 0, tile_capacity = 0;
+    StageProfile *prof = nullptr; // not owned
 };
 
 struct DeviceTree {
@@ -82,7 +102,9 @@ void free_workspace(BinWorkspace &ws);
 // Fused lookup + evaluation, one thread per point.  node_idx may be nullptr; when given, receives the
 // reference's global node index per point (-1 outside).  res may be nullptr (index query only).
 int launch_eval_direct(const DeviceTree &dt, const double *d_x, double *d_res, int64_t *d_node_idx, int64_t n,
-                       cudaStream_t stream, int64_t *launches);
+                       cudaStream_t stream, int64_t *launches, StageProfile *prof = nullptr);
+// Dependent-DFMA microbenchmark on the current device: sustained FP64 FMA rate in TFLOP/s (2 flops per FMA).
+int measure_fp64_peak(double *tflops, int repeats);
 // Scalar twin: x[dim] -> y[out_dim] (reference Function::eval(x, res), template.hpp:851-860).
 int launch_eval_scalar(const DeviceTree &dt, const double *d_x, double *d_y, cudaStream_t stream, int64_t *launches);
 // Binned path over one chunk (n <= ws.chunk_capacity): lookup+histogram, padded scan, scatter, evaluation.

@@ -19,6 +19,7 @@
 #include "host_tree.hpp"
 #include "lookup.cuh"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <vector>
@@ -121,15 +122,25 @@ __global__ void eval_scalar_kernel(const TreeView tv, const double *__restrict__
     }
 
 int launch_eval_direct(const DeviceTree &dt, const double *d_x, double *d_res, int64_t *d_node_idx, int64_t n,
-                       cudaStream_t stream, int64_t *launches) {
+                       cudaStream_t stream, int64_t *launches, StageProfile *prof) {
     if (n <= 0)
         return 0;
+    cudaEvent_t eb = nullptr, ee = nullptr;
+    if (prof) {
+        eb = prof->get();
+        ee = prof->get();
+        cudaEventRecord(eb, stream);
+    }
     // enough CTAs to fill every SM several times over, capped so the grid-stride loop amortises launch cost
     const int64_t want = (n + kDirectThreads - 1) / kDirectThreads;
     const int64_t cap = (int64_t)dt.sm_count * 64;
     const unsigned grid = (unsigned)(want < cap ? want : cap);
     BZ_DISPATCH(dt.view.dim, dt.view.order,
                 (eval_direct_kernel<D, O><<<grid, kDirectThreads, 0, stream>>>(dt.view, d_x, d_res, d_node_idx, n)));
+    if (prof) {
+        cudaEventRecord(ee, stream);
+        prof->mark(kStageDirect, n, eb, ee);
+    }
     if (launches)
         *launches += 1;
     return (int)cudaGetLastError();
@@ -141,6 +152,108 @@ int launch_eval_scalar(const DeviceTree &dt, const double *d_x, double *d_y, cud
     if (launches)
         *launches += 1;
     return (int)cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------ profiling
+cudaEvent_t StageProfile::get() {
+    if (!pool.empty()) {
+        cudaEvent_t e = pool.back();
+        pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+
+void StageProfile::collect(double ms[kNumStages], int64_t launches[kNumStages], int64_t points[kNumStages]) {
+    for (int s = 0; s < kNumStages; ++s) {
+        ms[s] = 0.0;
+        launches[s] = 0;
+        points[s] = 0;
+    }
+    for (const Span &sp : spans) {
+        float t = 0.f;
+        if (cudaEventElapsedTime(&t, sp.begin, sp.end) == cudaSuccess) {
+            ms[sp.stage] += t;
+            launches[sp.stage] += 1;
+            points[sp.stage] += sp.points;
+        }
+    }
+    // adjacent spans may share an event: recycle each one once
+    std::vector<cudaEvent_t> evs;
+    for (const Span &sp : spans) {
+        evs.push_back(sp.begin);
+        evs.push_back(sp.end);
+    }
+    std::sort(evs.begin(), evs.end());
+    evs.erase(std::unique(evs.begin(), evs.end()), evs.end());
+    pool.insert(pool.end(), evs.begin(), evs.end());
+    spans.clear();
+}
+
+StageProfile::~StageProfile() {
+    double ms[kNumStages];
+    int64_t a[kNumStages], b[kNumStages];
+    collect(ms, a, b);
+    for (cudaEvent_t e : pool)
+        cudaEventDestroy(e);
+}
+
+// ------------------------------------------------------------------------------------------ FP64 peak
+// 16 independent dependent-FMA chains per thread: the roofline denominator for the FP64-bound kernels
+// (MEASURED_PEAKS.json carries only HBM and bf16 tensor numbers).
+__global__ void __launch_bounds__(256) dfma_peak_kernel(double *out, double a, double b, int iters) {
+    double v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+        v[k] = (double)(threadIdx.x + k) * 1e-3;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+            v[k] = __fma_rn(v[k], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+        s += v[k];
+    if (s == 12345.678)
+        out[0] = s;
+}
+
+int measure_fp64_peak(double *tflops, int repeats) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    double *d = nullptr;
+    cudaError_t e = cudaMalloc((void **)&d, 8);
+    if (e != cudaSuccess)
+        return (int)e;
+    cudaEvent_t b, f;
+    cudaEventCreate(&b);
+    cudaEventCreate(&f);
+    const int iters = 8192, grid = sms * 8, threads = 256;
+    dfma_peak_kernel<<<grid, threads>>>(d, 0.999999, 1e-9, 64); // warm-up
+    double best = 0.0;
+    for (int r = 0; r < repeats; ++r) {
+        cudaEventRecord(b);
+        dfma_peak_kernel<<<grid, threads>>>(d, 0.999999, 1e-9, iters);
+        cudaEventRecord(f);
+        e = cudaEventSynchronize(f);
+        if (e != cudaSuccess)
+            break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, b, f);
+        const double flops = 2.0 * 16.0 * iters * (double)grid * threads;
+        const double t = flops / (ms * 1e-3) / 1e12;
+        if (t > best)
+            best = t;
+    }
+    cudaEventDestroy(b);
+    cudaEventDestroy(f);
+    cudaFree(d);
+    *tflops = best;
+    return (int)e;
 }
 
 } // namespace bz

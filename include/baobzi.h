@@ -142,6 +142,18 @@ int baobzi_set_mode(baobzi_t func, int mode, int64_t chunk);
 /* Counters for tests / benchmarks: number of kernel launches issued through this handle so far. */
 int64_t baobzi_launch_count(const baobzi_t func);
 
+/* Per-kernel timing for benchmarks: between _begin and _end every kernel launched through this handle is
+ * bracketed by CUDA events on its stream.  _end synchronises the current device and returns, per stage
+ * (0 lookup, 1 scan, 2 scatter, 3 binned evaluation, 4 direct evaluation; arrays of BAOBZI_N_STAGES), the summed
+ * elapsed milliseconds, the number of launches and the number of points processed. */
+#define BAOBZI_N_STAGES 5
+int baobzi_profile_begin(baobzi_t func);
+int baobzi_profile_end(baobzi_t func, double *ms, int64_t *launches, int64_t *points);
+
+/* Dependent-FMA microbenchmark on the current device: FP64 rate in TFLOP/s (roofline denominator of the
+ * FP64-bound kernels).  Returns 0 or a cudaError_t value. */
+int baobzi_b200_fp64_peak(double *tflops);
+
 /* Library identification string, e.g. "baobzi-b200 0.1 (sm_100a)". */
 const char *baobzi_b200_version(void);
 

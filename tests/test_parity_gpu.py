@@ -1,0 +1,164 @@
+"""GPU suite: the CUDA path, called through the C ABI (ctypes -> libbaobzi.so), against the oracle and the
+golden vectors.  Bar: node indices exact; values BIT-EXACT against the reference's AVX2+FMA build (tolerance
+0 ulp, tighter than the 4 ulp north_star allows), NaN exactly where the reference gives NaN."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from conftest import golden_cases, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+def ulp(ref, a, b):
+    return ref.ulp_diff(a, b).max() if len(a) else 0
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_golden_host_pointers(gpu_lib, ref, name):
+    """baobzi_restore + baobzi_eval_multi (host pointers) + node indices + baobzi_eval vs the reference's outputs."""
+    path, g = load_golden(name)
+    b = gpu_lib.Baobzi(filename=path)
+    x = g["x"]
+    assert np.array_equal(b.node_index(x), g["node_idx"])
+    y = b(x)
+    assert ulp(ref, y, g["y_avx2"]) == 0
+    assert ulp(ref, y, g["y_avx512"]) <= 4 and ulp(ref, y, g["y_generic"]) <= 16  # the reference's own spread
+    for row, ys in zip(g["scalar_rows"], g["ys_avx2"]):
+        assert ulp(ref, b.eval(x[row]), ys) == 0
+    assert b.launches > 0
+    b.free()
+
+
+@pytest.mark.parametrize("name", golden_cases())
+@pytest.mark.parametrize("mode", ["direct", "binned"])
+def test_golden_device_pointers(gpu_lib, ref, name, mode):
+    import torch
+    path, g = load_golden(name)
+    b = gpu_lib.Baobzi(filename=path, mode=mode)
+    xd = torch.from_numpy(g["x"]).cuda()
+    yd = b(xd)
+    torch.cuda.synchronize()
+    assert ulp(ref, yd.cpu().numpy(), g["y_avx2"]) == 0
+    assert np.array_equal(b.node_index(xd).cpu().numpy(), g["node_idx"])
+    # the classic entry point also accepts device pointers (zero copy)
+    y2 = torch.empty_like(yd)
+    b._lib.baobzi_eval_multi(b.ptr, xd.data_ptr(), y2.data_ptr(), xd.shape[0])
+    assert torch.equal(torch.nan_to_num(y2, nan=-1.0), torch.nan_to_num(yd, nan=-1.0))
+    b.free()
+
+
+@pytest.mark.parametrize("name", ["tc_1d1", "t2d_o8", "t3d_o8", "t3d_o12"])
+@pytest.mark.parametrize("n", [0, 1, 31, 33, 1000, 100003])
+def test_ragged_sizes_and_modes(gpu_lib, ref, name, n):
+    """Empty and ragged batches; direct and binned kernels and any chunking give identical bits."""
+    import torch
+    path, g = load_golden(name)
+    t = ref.OracleTree(path)
+    a = t.arrays()
+    rng = np.random.default_rng(n + 1)
+    x = a["lower_left"] + rng.random((n, t.dim)) * (a["upper_right"] - a["lower_left"]) * 1.02 - 0.01  # some outside
+    want = t.eval_multi(x, ref.ARITH_AVX2) if n else np.empty(0)
+    b = gpu_lib.Baobzi(filename=path)
+    assert ulp(ref, b(x), want) == 0
+    if n:
+        xd = torch.from_numpy(x).cuda()
+        for mode, chunk in (("direct", 0), ("binned", 0), ("binned", 1000), ("binned", 4097)):
+            b.set_mode(mode, chunk)
+            yd = b(xd)
+            torch.cuda.synchronize()
+            assert ulp(ref, yd.cpu().numpy(), want) == 0, (mode, chunk)
+    b.free()
+
+
+def test_nan_and_inf_inputs(gpu_lib, ref):
+    """NaN coordinates pass the reference's bounds test (all comparisons false) and poison the value; infinities
+    are out of domain."""
+    path, _ = load_golden("t2d_o8")
+    b = gpu_lib.Baobzi(filename=path)
+    x = np.array([[np.nan, 3.0], [1.5, np.nan], [np.inf, 3.0], [-np.inf, 3.0], [1.5, 3.0]])
+    y = b(x)
+    assert np.all(np.isnan(y[:4])) and not np.isnan(y[4])
+    b.free()
+
+
+def test_save_is_byte_identical_and_restorable(gpu_lib, ref, tmp_path):
+    """baobzi_save of a restored handle reproduces the reference-written file byte for byte."""
+    for name in ("tc_1d2", "t2d_o10", "t3d_o6"):
+        path, g = load_golden(name)
+        b = gpu_lib.Baobzi(filename=path)
+        out = str(tmp_path / (name + ".out"))
+        b.save(out)
+        assert open(out, "rb").read() == open(path, "rb").read()
+        b2 = gpu_lib.Baobzi(filename=out)
+        assert ulp(ref, b2(g["x"]), g["y_avx2"]) == 0
+        b.free()
+        b2.free()
+
+
+FIT_CASES = [  # reference tests/test_c.cpp: 27-71, 73-121, 123-168, 170-215 (3D tolerance relaxed to keep it quick)
+    ("testfun_1d", 1, 8, 1e-10, [3.0], [1.0], 1.5, 1),
+    ("testfun_1d2", 1, 8, 1e-10, [3.0], [1.0], 1.5, 2),
+    ("testfun_2d", 2, 6, 1e-10, [-10.0, 3.0], [np.pi / 5, np.pi / 5], 1.5, 1),
+    ("testfun_3d1", 3, 12, 1e-8, [3.0, -2.0, 1.0], [np.pi / 5, np.pi / 5, np.pi / 10], 1.5, 1),
+]
+
+
+@pytest.mark.parametrize("func,dim,order,tol,center,hl,data,od", FIT_CASES)
+def test_reference_test_c_cases_through_init(gpu_lib, ref, tmp_path, func, dim, order, tol, center, hl, data, od):
+    """The reference's own test cases, run against our library: baobzi_init, accuracy at the lower-left corner
+    and the centre via baobzi_eval, then save -> restore -> bitwise equal (test_c.cpp:42-68 etc.)."""
+    c, h = np.array(center), np.array(hl)
+    b = gpu_lib.Baobzi(fin=ref.func_ptr(func), dim=dim, order=order, center=c, half_length=h, tol=tol, data=data,
+                       output_dim=od)
+    f = getattr(ref.funcs_lib(), func)
+    f.restype, f.argtypes = None, [ref.c_double_p, ref.c_double_p, C.c_void_p]
+    dat = C.c_double(data)
+    for p in (c - h, c):
+        p = np.ascontiguousarray(p)
+        ye = np.zeros(od)
+        f(p.ctypes.data_as(ref.c_double_p), ye.ctypes.data_as(ref.c_double_p), C.addressof(dat))
+        assert np.all(np.abs((b.eval(p) - ye) / ye) < tol)
+    out = str(tmp_path / "t.baobzi")
+    b.save(out)
+    b2 = gpu_lib.Baobzi(filename=out)
+    assert np.array_equal(b.eval(c), b2.eval(c))
+    # and the batched path equals the oracle on the same saved tree
+    rng = np.random.default_rng(11)
+    x = c + (rng.random((20000, dim)) * 2 - 1) * h
+    assert ulp(ref, b2(x), ref.OracleTree(out).eval_multi(x, ref.ARITH_AVX2)) == 0
+    b.stats()
+    b.free()
+    b2.free()
+
+
+def test_python_callback_init(gpu_lib):
+    b = gpu_lib.Baobzi(fin=lambda x: np.sin(x[0]) + 2.0, dim=1, order=10, center=np.array([1.0]),
+                       half_length=np.array([2.0]), tol=1e-11)
+    x = np.linspace(-0.99, 2.99, 1001)
+    assert np.max(np.abs(b(x) - (np.sin(x) + 2))) < 1e-10
+    b.free()
+
+
+def test_concurrent_calls_on_one_handle(gpu_lib, ref):
+    """eval is const in the reference, so concurrent calls on one handle are legal; they must stay so."""
+    import threading
+    path, g = load_golden("t2d_o12")
+    b = gpu_lib.Baobzi(filename=path)
+    rng = np.random.default_rng(0)
+    xs = [np.ascontiguousarray(g["x"][rng.permutation(len(g["x"]))]) for _ in range(8)]
+    t = ref.OracleTree(path)
+    outs = [None] * 8
+
+    def work(i):
+        for _ in range(20):
+            outs[i] = b(xs[i])
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(8)]
+    [t_.start() for t_ in th]
+    [t_.join() for t_ in th]
+    for i in range(8):
+        assert ulp(ref, outs[i], t.eval_multi(xs[i], ref.ARITH_AVX2)) == 0
+    b.free()
