@@ -55,10 +55,11 @@ bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__res
 }
 
 // ------------------------------------------------------------------------------------------ K2
-// Single CTA.  count[] in: histogram; out: zero (reused as cursor by K3).
+// Single CTA.  count[] in: histogram; out: zero (ready for the next chunk's K1).  cursor[] out: zero (for K3).
 template <int TILE>
 __global__ void __launch_bounds__(1024)
-bin_scan_kernel(uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__restrict__ start,
+bin_scan_kernel(uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__restrict__ cursor,
+                uint32_t *__restrict__ start,
                 uint32_t *__restrict__ tile_leaf, uint32_t *__restrict__ perm, uint32_t *__restrict__ n_tiles) {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry_s;
@@ -97,6 +98,7 @@ bin_scan_kernel(uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__res
         if (l < n_leaves) {
             start[l] = excl;
             count[l] = 0;
+            cursor[l] = 0;
             for (uint32_t s = excl + cnt; s < excl + padded; ++s)
                 perm[s] = kInvalidSlot;
             for (uint32_t t = excl / TILE; t < (excl + padded) / TILE; ++t)
@@ -239,6 +241,8 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     if (e == cudaSuccess)
         e = cudaMalloc((void **)&ws.count, sizeof(uint32_t) * (nl + 1));
     if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.cursor, sizeof(uint32_t) * (nl + 1));
+    if (e == cudaSuccess)
         e = cudaMalloc((void **)&ws.start, sizeof(uint32_t) * (nl + 1));
     if (e == cudaSuccess)
         e = cudaMalloc((void **)&ws.tile_leaf, sizeof(uint32_t) * ws.tile_capacity);
@@ -258,6 +262,7 @@ void free_workspace(BinWorkspace &ws) {
     cudaFree(ws.key);
     cudaFree(ws.perm);
     cudaFree(ws.count);
+    cudaFree(ws.cursor);
     cudaFree(ws.start);
     cudaFree(ws.tile_leaf);
     cudaFree(ws.n_tiles);
@@ -283,10 +288,10 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
     bin_lookup_kernel<3><<<g1, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.key, ws.count, n);
     if (pf)
         cudaEventRecord(ev[1], st);
-    bin_scan_kernel<TILE><<<1, 1024, 0, st>>>(tv.n_leaves, ws.count, ws.start, ws.tile_leaf, ws.perm, ws.n_tiles);
+    bin_scan_kernel<TILE><<<1, 1024, 0, st>>>(tv.n_leaves, ws.count, ws.cursor, ws.start, ws.tile_leaf, ws.perm, ws.n_tiles);
     if (pf)
         cudaEventRecord(ev[2], st);
-    bin_scatter_kernel<<<g1, kBinThreads, 0, st>>>(ws.key, ws.start, ws.count, ws.perm, n);
+    bin_scatter_kernel<<<g1, kBinThreads, 0, st>>>(ws.key, ws.start, ws.cursor, ws.perm, n);
     if (pf)
         cudaEventRecord(ev[3], st);
     // persistent grid: 2 CTAs of 8 warps per SM, each CTA walks 8 consecutive tiles (same leaf, L1 reuse)

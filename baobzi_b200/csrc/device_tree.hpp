@@ -75,7 +75,8 @@ struct BinWorkspace {
     int64_t chunk_capacity = 0; // points
     uint32_t *key = nullptr;    // [chunk]            leaf rank per point (kNotLeaf = outside the domain)
     uint32_t *perm = nullptr;   // [chunk + padding]  point index (within the chunk) per sorted slot
-    uint32_t *count = nullptr;  // [n_leaves + 1]     histogram, then cursor
+    uint32_t *count = nullptr;  // [n_leaves + 1]     histogram (zero between chunks: the scan clears it)
+    uint32_t *cursor = nullptr; // [n_leaves + 1]     per-leaf fill cursor of the scatter (cleared by the scan)
     uint32_t *start = nullptr;  // [n_leaves + 1]     padded exclusive scan
     uint32_t *tile_leaf = nullptr; // [max_tiles]     leaf rank of each warp tile
     uint32_t *n_tiles = nullptr;   // [1]

@@ -1,0 +1,224 @@
+#!/usr/bin/env python
+"""bench.py -- FP64 evals/s of the batched evaluation path (baobzi_eval_multi) on B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C1..C5] [--points P]
+  torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...      (one rank per GPU, NCCL only for the barrier)
+
+A "step" is one pass of the hot path over the whole batch of synthetic uniform points of the workload
+(default C3 = BASELINE.json configs[2]: 3D order 8 smooth function, 1e9 points per GPU, the configuration the
+north_star target "1e10 evals/s for a 3D order-8 tree on one B200" is quoted on).  Rank 0 prints ONE JSON line.
+
+  value     whole-job evals/s, points and results resident in HBM, CUDA-event timed on the launching stream
+  e2e       the same through the reference-facing C ABI call baobzi_eval_multi with HOST (pinned) buffers:
+            H2D of the points and D2H of the results inside the timed region
+  roofline  for the dominant kernel, from per-launch CUDA events inside the timed region (baobzi_profile_*)
+  cpu_baseline  the reference's CPU path (oracle/_ref when built, else the oracle port) on a bounded sample
+  --impl reference  times only that CPU path, on all host cores, and prints the same line shape
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# BASELINE.json configs.  flops/eval = the reference formulation's count (FMA = 2).
+WORKLOADS = {
+    "C1": dict(desc="2D order 8, testfun_2d tol 1e-10 (baobzi_timing.c:176-191)", func="bench_fun_2d", dim=2, order=8,
+               tol=1e-10, center=[1.5, 3.0], hl=[1.0, 1.0], data=1.5, points=1_000_000),
+    "C2": dict(desc="1D order 16, 1.5*log(x) on [1,3]", func="bench_fun_1d", dim=1, order=16, tol=1e-10,
+               center=[2.0], hl=[1.0], data=1.5, points=100_000_000),
+    "C3": dict(desc="3D order 8, testfun_3d tol 1e-12 (baobzi_timing.c:195-208)", func="bench_fun_3d", dim=3, order=8,
+               tol=1e-12, center=[1.5, 3.0, 1.5], hl=[1.0, 1.0, 1.0], data=None, points=1_000_000_000),
+    "C4": dict(desc="2D order 6 oscillatory 2+sin(20x)cos(20y), tol 1e-10, coefficients > L2", func="bench_fun_2d_osc",
+               dim=2, order=6, tol=1e-10, center=[0.0, 0.0], hl=[1.0, 1.0], data=20.0, points=1_000_000_000),
+    "C5": dict(desc="3D order 12, testfun_3d tol 1e-12", func="bench_fun_3d", dim=3, order=12, tol=1e-12,
+               center=[1.5, 3.0, 1.5], hl=[1.0, 1.0, 1.0], data=None, points=1_000_000_000),
+}
+METRIC = "FP64 evals/sec for baobzi_eval_multi"
+
+
+def flops_per_eval(dim, o):
+    if dim == 1:
+        return 3 * o
+    if dim == 2:
+        return 2 * o * o + 2 * o + 4 * (o - 2) + 6
+    return 2 * o ** 3 + 2 * o * o + 2 * o + 6 * (o - 2) + 9
+
+
+def bytes_per_eval(dim):
+    return 8 * (dim + 1)
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        busy = sorted(sm)[len(sm) // 4:]  # drop the idle samples at the edges
+        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU side
+def cpu_reference_rate(tree_path, cfg, threads, pts_per_thread, repeats=1):
+    """The reference's CPU-dispatched baobzi_eval_multi (oracle/_ref, unmodified reference) -- or the oracle port
+    when the reference could not be built -- on `threads` contiguous slices from `threads` host threads (legal:
+    eval is const in the reference).  Returns (evals/s, info dict).  Only executed for cpu_baseline / --impl reference."""
+    from oracle import ref
+    dim = cfg["dim"]
+    rng = np.random.default_rng(1)
+    n = threads * pts_per_thread
+    x = np.array(cfg["center"]) + (rng.random((n, dim)) * 2 - 1) * np.array(cfg["hl"])
+    res = np.empty(n)
+    if ref.have_ref():
+        kind = "reference"
+        h = ref.ref_restore(tree_path, arch=None)  # default CPU dispatch (get_iset, src/baobzi.cpp:27-59)
+        lib = ref.ref_lib()
+
+        def work(k):
+            s = slice(k * pts_per_thread, (k + 1) * pts_per_thread)
+            xs, rs = x[s], res[s]
+            lib.baobzi_eval_multi(h.ptr, ref.dptr(xs), ref.dptr(rs), pts_per_thread)
+    else:
+        kind = "port"
+        if not os.path.exists(ref.ORACLE_SO):
+            subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"], check=True, stdout=subprocess.DEVNULL)
+        t = ref.OracleTree(tree_path)
+        lib = ref.oracle_lib()
+
+        def work(k):
+            s = slice(k * pts_per_thread, (k + 1) * pts_per_thread)
+            xs, rs = x[s], res[s]
+            lib.oracle_eval_multi(t.ptr, ref.dptr(xs), ref.dptr(rs), pts_per_thread, ref.ARITH_AVX2)
+
+    best = None
+    for _ in range(repeats + 1):  # first pass warms caches / page-faults the buffers
+        th = [threading.Thread(target=work, args=(k,)) for k in range(threads)]
+        t0 = time.perf_counter()
+        [t_.start() for t_ in th]
+        [t_.join() for t_ in th]
+        dt = time.perf_counter() - t0
+        best = dt if best is None or _ == 0 else min(best, dt)
+        if _ == 0:
+            best = None
+    isa = "n/a"
+    try:
+        flags = open("/proc/cpuinfo").read()
+        isa = "avx512" if " avx512f" in flags else ("avx2" if " avx2" in flags else "generic")
+    except OSError:
+        pass
+    info = {"kind": kind, "cores": threads, "sample": "%d threads x %d uniform points, same saved tree, %s dispatch"
+            % (threads, pts_per_thread, isa), "seconds": best}
+    return n / best, info
+
+
+def cpu_sample_size(cfg, threads):
+    # ~10-30 s of CPU work in total: the reference runs ~2e6 (3D o8) .. 1e8 (1D) evals/s per core
+    per_core_rate = {1: 8e7, 2: 5e6, 3: 1.5e6}[cfg["dim"]] * (8.0 / cfg["order"]) ** cfg["dim"]
+    return int(max(2e5, min(2e7, per_core_rate * 0.6)))
+
+
+def fit_tree_to_file(cfg, path):
+    """Fit the workload's tree with OUR host fitter (baobzi_init) and save it; needs the GPU library loaded."""
+    import baobzi_b200
+    funcs = C.CDLL(os.path.join(ROOT, "baobzi_b200", "lib", "libbenchfuncs.so"))
+    fptr = C.cast(getattr(funcs, cfg["func"]), C.c_void_p).value
+    b = baobzi_b200.Baobzi(fin=fptr, dim=cfg["dim"], order=cfg["order"], center=np.array(cfg["center"]),
+                           half_length=np.array(cfg["hl"]), tol=cfg["tol"], data=cfg["data"])
+    b.save(path)
+    return b
+
+
+def run_reference_arm(args, cfg, rank, world):
+    """--impl reference: rank 0 alone times the reference's CPU path with every host core it can use."""
+    if rank != 0:
+        return
+    from oracle import ref
+    threads = host_cores()
+    pts = cpu_sample_size(cfg, threads)
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "tree.baobzi")
+        if ref.have_ref():  # the reference fits its own tree through its own baobzi_init
+            subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"], check=True, stdout=subprocess.DEVNULL)
+            name = {"bench_fun_1d": "testfun_1d", "bench_fun_2d": "testfun_2d", "bench_fun_3d": "testfun_3d",
+                    "bench_fun_2d_osc": "testfun_2d_osc"}[cfg["func"]]
+            inp = ref.make_input(name, cfg["dim"], cfg["order"], cfg["tol"], data=cfg["data"])
+            ref.ref_init(inp, cfg["center"], cfg["hl"]).save(path)
+        else:
+            import baobzi_b200  # noqa: F401  (fitting needs our library; evaluation below is the oracle port)
+            fit_tree_to_file(cfg, path).free()
+        rates = []
+        for step in range(args.warmup + args.steps):
+            r, info = cpu_reference_rate(path, cfg, threads, pts, repeats=1)
+            if step >= args.warmup:
+                rates.append(r)
+    value = float(np.mean(rates))
+    line = {"metric": METRIC, "value": value, "unit": "evals/s", "impl": "reference", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * threads * pts / value,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "%s: %s" % (args.workload, cfg["desc"]), "points_per_step": threads * pts,
+                       "timing": "host wall clock; bounded sample of the workload"},
+            "cpu_baseline": {"value": value, "unit": "evals/s", "cores": info["cores"], "kind": info["kind"],
+                             "sample": info["sample"]},
+            "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)

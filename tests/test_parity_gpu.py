@@ -25,7 +25,6 @@ def test_golden_host_pointers(gpu_lib, ref, name):
     assert np.array_equal(b.node_index(x), g["node_idx"])
     y = b(x)
     assert ulp(ref, y, g["y_avx2"]) == 0
-    assert ulp(ref, y, g["y_avx512"]) <= 4 and ulp(ref, y, g["y_generic"]) <= 16  # the reference's own spread
     for row, ys in zip(g["scalar_rows"], g["ys_avx2"]):
         assert ulp(ref, b.eval(x[row]), ys) == 0
     assert b.launches > 0
