@@ -222,3 +222,192 @@ def run_reference_arm(args, cfg, rank, world):
             "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ GPU side
+def run_ours(args, cfg, rank, world, local_rank):
+    import torch
+    import baobzi_b200
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the evaluation path exists only as sm_100a kernels")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    if not os.path.exists(baobzi_b200.library_path()):
+        baobzi_b200.build()
+    dim, order = cfg["dim"], cfg["order"]
+    n = int(args.points or cfg["points"])
+
+    tmp = tempfile.TemporaryDirectory()
+    tree_path = os.path.join(tmp.name, "tree_rank%d.baobzi" % rank)
+    t0 = time.perf_counter()
+    b = fit_tree_to_file(cfg, tree_path)      # host fit (callback on the host) + flatten + upload to this GPU
+    fit_s = time.perf_counter() - t0
+    if args.mode:
+        b.set_mode(args.mode, args.chunk)
+    elif args.chunk:
+        b.set_mode("auto", args.chunk)
+
+    # synthetic uniform points x_j = hl_j (2u - 1) + c_j (baobzi_timing.c:98-100), generated on the device,
+    # seeded per rank; generated in slabs so the temporaries stay small
+    g = torch.Generator(device=dev).manual_seed(1 + rank)
+    x = torch.empty((n, dim), dtype=torch.float64, device=dev)
+    c = torch.tensor(cfg["center"], dtype=torch.float64, device=dev)
+    h = torch.tensor(cfg["hl"], dtype=torch.float64, device=dev)
+    slab = 1 << 24
+    for o in range(0, n, slab):
+        v = x[o:o + slab]
+        v.uniform_(0.0, 1.0, generator=g)
+        v.mul_(2.0).sub_(1.0).mul_(h).add_(c)
+    res = torch.empty(n, dtype=torch.float64, device=dev)
+    stream = torch.cuda.current_stream(dev)
+
+    def step():
+        rc = b._lib.baobzi_eval_multi_device(b.ptr, x.data_ptr(), res.data_ptr(), n, stream.cuda_stream)
+        if rc != 0:
+            raise RuntimeError("baobzi_eval_multi_device: CUDA error %d" % rc)
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = b.launches
+    if not args.no_profile:
+        b.profile_begin()                      # per-launch CUDA events inside the timed region (roofline)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(args.steps):
+        step()
+    ev1.record(stream)
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    stages = b.profile_end() if not args.no_profile else {}
+    launches = b.launches - launches0
+    clocks = sampler.stop()
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        ms = float(t.item())
+        lt = torch.tensor([launches], dtype=torch.int64, device=dev)
+        torch.distributed.all_reduce(lt)
+        launches = int(lt.item())
+    value = world * n * args.steps / (ms * 1e-3)
+    nan_count = int(torch.isnan(res[: min(n, 1 << 22)]).sum().item())
+
+    # ---- e2e: the reference-facing call with HOST buffers (pinned), copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        import psutil
+        need = n * (dim + 1) * 8
+        n_e = n if psutil.virtual_memory().available > 3 * need else max(1 << 20, int(psutil.virtual_memory().available / 3 / ((dim + 1) * 8)))
+        n_e = min(n_e, 2**31 - 1)
+        xh = torch.empty((n_e, dim), dtype=torch.float64, pin_memory=True)
+        yh = torch.empty(n_e, dtype=torch.float64, pin_memory=True)
+        xh.copy_(x[:n_e])
+        torch.cuda.synchronize(dev)
+        e_steps = max(1, min(args.steps, 3))
+        b._lib.baobzi_eval_multi(b.ptr, xh.data_ptr(), yh.data_ptr(), n_e)  # warm-up (allocates the pipeline slots)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            b._lib.baobzi_eval_multi(b.ptr, xh.data_ptr(), yh.data_ptr(), n_e)
+        torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], dtype=torch.float64, device=dev)
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+            dt = float(t.item())
+        same = bool(torch.equal(torch.nan_to_num(yh[:1 << 20]), torch.nan_to_num(res[:1 << 20].cpu())))
+        e2e = {"value": world * n_e * e_steps / dt, "unit": "evals/s", "h2d_bytes_per_step": n_e * dim * 8,
+               "d2h_bytes_per_step": n_e * 8, "points_per_step": n_e, "steps": e_steps,
+               "matches_device_path": same, "timing": "host wall clock around baobzi_eval_multi, pinned host buffers"}
+        del xh, yh
+
+    if rank != 0:
+        b.free()
+        return
+    # ---- roofline of the dominant kernel
+    hbm_peak, hbm_src = measured_peaks()
+    fp = C.c_double(0.0)
+    b._lib.baobzi_b200_fp64_peak(C.byref(fp))
+    roof = None
+    if stages:
+        name, (k_ms, k_launches, k_points) = max(stages.items(), key=lambda kv: kv[1][0])
+        total_ms = sum(v[0] for v in stages.values())
+        if k_launches:
+            per_launch_s = k_ms * 1e-3 / k_launches
+            pts_per_launch = k_points / k_launches
+            tf = flops_per_eval(dim, order) * pts_per_launch / per_launch_s / 1e12
+            gb = bytes_per_eval(dim) * pts_per_launch / per_launch_s / 1e9
+            fp64_bound = dim == 3 or (dim == 2 and tf / max(fp.value, 1e-9) > gb / hbm_peak)
+            roof = {"kernel": name, "bound": "fp64" if fp64_bound else "hbm",
+                    "achieved": tf if fp64_bound else gb, "peak": fp.value if fp64_bound else hbm_peak,
+                    "unit": "TFLOP/s" if fp64_bound else "GB/s",
+                    "frac": (tf / fp.value if fp.value else None) if fp64_bound else gb / hbm_peak,
+                    "traffic": None,
+                    "peak_source": "DFMA microbenchmark baobzi_b200_fp64_peak, measured in this run" if fp64_bound else hbm_src,
+                    "algorithmic_flops_per_eval": flops_per_eval(dim, order), "algorithmic_bytes_per_eval": bytes_per_eval(dim),
+                    "avg_launch_ms": per_launch_s * 1e3, "points_per_launch": pts_per_launch,
+                    "share_of_step": k_ms / total_ms if total_ms else None,
+                    "hbm_gbs_achieved": gb, "hbm_frac": gb / hbm_peak, "fp64_tflops_achieved": tf,
+                    "stages_ms_per_step": {k: v[0] / args.steps for k, v in stages.items() if v[1]}}
+    # ---- CPU baseline on this box's host cores (bounded sample)
+    cpu = None
+    if not args.no_cpu:
+        threads = host_cores()
+        r1, info1 = cpu_reference_rate(tree_path, cfg, 1, cpu_sample_size(cfg, 1) // 2)
+        rT, infoT = cpu_reference_rate(tree_path, cfg, threads, cpu_sample_size(cfg, threads) // 2)
+        cpu = {"value": rT, "unit": "evals/s", "cores": threads, "kind": infoT["kind"], "sample": infoT["sample"],
+               "single_thread_value": r1}
+    line = {"metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "%s: %s" % (args.workload, cfg["desc"]), "points_per_gpu": n,
+                       "inputs": "uniform on the domain, device resident, %.1f GB per GPU (larger than L2, no flush needed)"
+                                 % (n * (dim + 1) * 8 / 1e9),
+                       "parallelism": "tree replicated, points sharded by contiguous range, no collective",
+                       "tree": {"nodes": int(b._lib.baobzi_launch_count(b.ptr) * 0 + 0) or None}, "fit_seconds": fit_s,
+                       "mode": args.mode or "auto", "nan_results_in_sample": nan_count,
+                       "parity": "bit-exact vs reference BAOBZI_ARCH=avx2 (tests/)"},
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+            "fp64_peak_tflops_measured": fp.value}
+    line["config"].pop("tree")
+    print(json.dumps(line), flush=True)
+    b.free()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
+    ap.add_argument("--points", type=int, default=0, help="points per GPU (default: the workload's)")
+    ap.add_argument("--mode", default="", choices=["", "auto", "direct", "binned"])
+    ap.add_argument("--chunk", type=int, default=0)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-profile", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    cfg = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference_arm(args, cfg, rank, world)
+    else:
+        run_ours(args, cfg, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()
