@@ -36,7 +36,7 @@ __host__ __device__ constexpr int points_per_lane(int dim, int order) {
 template <int DIM>
 __global__ void __launch_bounds__(kBinThreads)
 bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
-                  uint32_t *__restrict__ key, uint32_t *__restrict__ count, uint32_t n) {
+                  uint32_t *__restrict__ key, uint32_t *__restrict__ count, int cshift, uint32_t n) {
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         double p[DIM];
@@ -50,17 +50,17 @@ bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__res
         const uint32_t node = locate<DIM>(tv, p, head);
         const uint32_t rank = load_tail(tv.nodes, node).leaf_rank;
         key[i] = rank;
-        atomicAdd(count + rank, 1u);
+        atomicAdd(count + ((size_t)rank << cshift), 1u);
     }
 }
 
 // ------------------------------------------------------------------------------------------ K2
-// Single CTA.  count[] in: histogram; out: zero (ready for the next chunk's K1).  cursor[] out: zero (for K3).
+// Single CTA: exclusive scan of the per-leaf counts rounded up to the warp-tile size.  count[] in: histogram;
+// out: zero (ready for the next chunk's K1).  cursor[] out: zero (for K3).  cnt[] out: dense copy for K2b.
 template <int TILE>
 __global__ void __launch_bounds__(1024)
-bin_scan_kernel(uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__restrict__ cursor,
-                uint32_t *__restrict__ start,
-                uint32_t *__restrict__ tile_leaf, uint32_t *__restrict__ perm, uint32_t *__restrict__ n_tiles) {
+bin_scan_kernel(uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__restrict__ cursor, int cshift,
+                uint32_t *__restrict__ cnt_out, uint32_t *__restrict__ start, uint32_t *__restrict__ n_tiles) {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry_s;
     if (threadIdx.x == 0)
@@ -69,10 +69,9 @@ bin_scan_kernel(uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__res
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (uint32_t base = 0; base < n_leaves; base += blockDim.x) {
         const uint32_t l = base + threadIdx.x;
-        const uint32_t cnt = l < n_leaves ? count[l] : 0u;
+        const uint32_t cnt = l < n_leaves ? count[(size_t)l << cshift] : 0u;
         const uint32_t padded = (cnt + TILE - 1) / TILE * TILE;
-        // inclusive scan of `padded` across the CTA
-        uint32_t v = padded;
+        uint32_t v = padded; // inclusive scan of `padded` across the CTA
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
@@ -94,15 +93,11 @@ bin_scan_kernel(uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__res
         }
         __syncthreads();
         const uint32_t carry = carry_s;
-        const uint32_t excl = carry + (warp ? warp_sums[warp - 1] : 0u) + v - padded;
         if (l < n_leaves) {
-            start[l] = excl;
-            count[l] = 0;
-            cursor[l] = 0;
-            for (uint32_t s = excl + cnt; s < excl + padded; ++s)
-                perm[s] = kInvalidSlot;
-            for (uint32_t t = excl / TILE; t < (excl + padded) / TILE; ++t)
-                tile_leaf[t] = l;
+            start[l] = carry + (warp ? warp_sums[warp - 1] : 0u) + v - padded;
+            cnt_out[l] = cnt;
+            count[(size_t)l << cshift] = 0;
+            cursor[(size_t)l << cshift] = 0;
         }
         __syncthreads();
         if (threadIdx.x == blockDim.x - 1)
@@ -113,16 +108,33 @@ bin_scan_kernel(uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__res
         *n_tiles = carry_s / TILE;
 }
 
+// K2b: one warp per leaf marks the padding slots of perm[] invalid and records the leaf of each of its tiles.
+template <int TILE>
+__global__ void __launch_bounds__(kBinThreads)
+bin_fill_kernel(uint32_t n_leaves, const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ start,
+                uint32_t *__restrict__ tile_leaf, uint32_t *__restrict__ perm) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t l = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (l >= n_leaves)
+        return;
+    const uint32_t c = cnt[l], s0 = start[l];
+    const uint32_t padded = (c + TILE - 1) / TILE * TILE;
+    for (uint32_t s = s0 + c + lane; s < s0 + padded; s += 32)
+        perm[s] = kInvalidSlot;
+    for (uint32_t t = s0 / TILE + lane; t < (s0 + padded) / TILE; t += 32)
+        tile_leaf[t] = l;
+}
+
 // ------------------------------------------------------------------------------------------ K3
 __global__ void __launch_bounds__(kBinThreads)
 bin_scatter_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict__ start, uint32_t *__restrict__ cursor,
-                   uint32_t *__restrict__ perm, uint32_t n) {
+                   int cshift, uint32_t *__restrict__ perm, uint32_t n) {
     const uint32_t stride = gridDim.x * blockDim.x;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const uint32_t k = key[i];
         if (k == kNotLeaf)
             continue;
-        const uint32_t pos = __ldg(start + k) + atomicAdd(cursor + k, 1u);
+        const uint32_t pos = __ldg(start + k) + atomicAdd(cursor + ((size_t)k << cshift), 1u);
         perm[pos] = i;
     }
 }
@@ -235,13 +247,20 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     const int64_t nl = dt.view.n_leaves;
     ws.perm_capacity = chunk + nl * tile;
     ws.tile_capacity = ws.perm_capacity / tile + 1;
+    // spread the per-leaf counters: up to 32 words (one 128-byte line) apart while the arrays stay <= 4 MB
+    ws.cshift = 0;
+    while (ws.cshift < 5 && ((nl + 1) << (ws.cshift + 1)) <= (1 << 20))
+        ws.cshift++;
+    const size_t cwords = (size_t)(nl + 1) << ws.cshift;
     cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
     if (e == cudaSuccess)
         e = cudaMalloc((void **)&ws.perm, sizeof(uint32_t) * ws.perm_capacity);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.count, sizeof(uint32_t) * (nl + 1));
+        e = cudaMalloc((void **)&ws.count, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.cursor, sizeof(uint32_t) * (nl + 1));
+        e = cudaMalloc((void **)&ws.cursor, sizeof(uint32_t) * cwords);
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.cnt, sizeof(uint32_t) * (nl + 1));
     if (e == cudaSuccess)
         e = cudaMalloc((void **)&ws.start, sizeof(uint32_t) * (nl + 1));
     if (e == cudaSuccess)
@@ -249,7 +268,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     if (e == cudaSuccess)
         e = cudaMalloc((void **)&ws.n_tiles, sizeof(uint32_t));
     if (e == cudaSuccess)
-        e = cudaMemset(ws.count, 0, sizeof(uint32_t) * (nl + 1));
+        e = cudaMemset(ws.count, 0, sizeof(uint32_t) * cwords);
     if (e != cudaSuccess) {
         free_workspace(ws);
         return (int)e;
@@ -263,6 +282,7 @@ void free_workspace(BinWorkspace &ws) {
     cudaFree(ws.perm);
     cudaFree(ws.count);
     cudaFree(ws.cursor);
+    cudaFree(ws.cnt);
     cudaFree(ws.start);
     cudaFree(ws.tile_leaf);
     cudaFree(ws.n_tiles);
@@ -285,13 +305,15 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
             e = pf->get();
         cudaEventRecord(ev[0], st);
     }
-    bin_lookup_kernel<3><<<g1, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.key, ws.count, n);
+    bin_lookup_kernel<3><<<g1, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.key, ws.count, ws.cshift, n);
     if (pf)
         cudaEventRecord(ev[1], st);
-    bin_scan_kernel<TILE><<<1, 1024, 0, st>>>(tv.n_leaves, ws.count, ws.cursor, ws.start, ws.tile_leaf, ws.perm, ws.n_tiles);
+    bin_scan_kernel<TILE><<<1, 1024, 0, st>>>(tv.n_leaves, ws.count, ws.cursor, ws.cshift, ws.cnt, ws.start, ws.n_tiles);
+    bin_fill_kernel<TILE><<<(tv.n_leaves * 32 + kBinThreads - 1) / kBinThreads, kBinThreads, 0, st>>>(tv.n_leaves, ws.cnt, ws.start,
+                                                                                                  ws.tile_leaf, ws.perm);
     if (pf)
         cudaEventRecord(ev[2], st);
-    bin_scatter_kernel<<<g1, kBinThreads, 0, st>>>(ws.key, ws.start, ws.cursor, ws.perm, n);
+    bin_scatter_kernel<<<g1, kBinThreads, 0, st>>>(ws.key, ws.start, ws.cursor, ws.cshift, ws.perm, n);
     if (pf)
         cudaEventRecord(ev[3], st);
     // persistent grid: 2 CTAs of 8 warps per SM, each CTA walks 8 consecutive tiles (same leaf, L1 reuse)
@@ -324,7 +346,7 @@ int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x
     default: return (int)cudaErrorInvalidValue;
     }
     if (launches)
-        *launches += 4;
+        *launches += 5;
     return rc;
 }
 

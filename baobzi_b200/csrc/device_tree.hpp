@@ -77,6 +77,9 @@ struct BinWorkspace {
     uint32_t *perm = nullptr;   // [chunk + padding]  point index (within the chunk) per sorted slot
     uint32_t *count = nullptr;  // [n_leaves + 1]     histogram (zero between chunks: the scan clears it)
     uint32_t *cursor = nullptr; // [n_leaves + 1]     per-leaf fill cursor of the scatter (cleared by the scan)
+    uint32_t *cnt = nullptr;    // [n_leaves + 1]     dense copy of the histogram for the fill kernel
+    int cshift = 0;             // count[] / cursor[] entries are spread 2^cshift words apart so that atomics of
+                                // different leaves land in different L2 sectors / lines
     uint32_t *start = nullptr;  // [n_leaves + 1]     padded exclusive scan
     uint32_t *tile_leaf = nullptr; // [max_tiles]     leaf rank of each warp tile
     uint32_t *n_tiles = nullptr;   // [1]
