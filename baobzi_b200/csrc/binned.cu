@@ -16,10 +16,10 @@
 //   K3 bin_scatter  thread per point: perm[start[key] + cursor[key]++] = i
 //   K4 bin_eval     warp per tile (32*P consecutive slots of one leaf): gather the P points per lane,
 //                   evaluate with register-blocked, reference-ordered arithmetic, scatter the results
-#include "cheb.cuh"
 #include "device_tree.hpp"
 
 #include <cstdio>
+#include <cstdlib>
 
 #include "lookup.cuh"
 
@@ -28,9 +28,10 @@ namespace bz {
 constexpr uint32_t kInvalidSlot = 0xFFFFFFFFu;
 constexpr int kBinThreads = 256;
 
-__host__ __device__ constexpr int points_per_lane(int dim, int order) {
-    return (dim == 3 && order <= 10) ? 2 : 1;
-}
+int bin_eval_default_P(int order);
+bool bin_eval_default_smem(int order);
+bool bin_eval_variant_exists(int order, int P, bool smem);
+int launch_bin_eval3d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------------ K1
 template <int DIM>
@@ -57,9 +58,8 @@ bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__res
 // ------------------------------------------------------------------------------------------ K2
 // Single CTA: exclusive scan of the per-leaf counts rounded up to the warp-tile size.  count[] in: histogram;
 // out: zero (ready for the next chunk's K1).  cursor[] out: zero (for K3).  cnt[] out: dense copy for K2b.
-template <int TILE>
 __global__ void __launch_bounds__(1024)
-bin_scan_kernel(uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__restrict__ cursor, int cshift,
+bin_scan_kernel(uint32_t TILE, uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__restrict__ cursor, int cshift,
                 uint32_t *__restrict__ cnt_out, uint32_t *__restrict__ start, uint32_t *__restrict__ n_tiles) {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry_s;
@@ -109,9 +109,8 @@ bin_scan_kernel(uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__res
 }
 
 // K2b: one warp per leaf marks the padding slots of perm[] invalid and records the leaf of each of its tiles.
-template <int TILE>
 __global__ void __launch_bounds__(kBinThreads)
-bin_fill_kernel(uint32_t n_leaves, const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ start,
+bin_fill_kernel(uint32_t TILE, uint32_t n_leaves, const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ start,
                 uint32_t *__restrict__ tile_leaf, uint32_t *__restrict__ perm) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t l = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -139,101 +138,6 @@ bin_scatter_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict_
     }
 }
 
-// ------------------------------------------------------------------------------------------ K4
-// P points per lane, all in the same leaf: coefficient loads are warp-uniform.
-template <int O, int P>
-__device__ __forceinline__ void gemv_block_multi(const double *__restrict__ C, const double (&v)[P][O],
-                                                 double (&acc)[P][O]) {
-    const double2 *c2 = reinterpret_cast<const double2 *>(C);
-#pragma unroll
-    for (int r = 0; r < O; r += 2) {
-        const double2 c = __ldg(c2 + r / 2);
-#pragma unroll
-        for (int p = 0; p < P; ++p) {
-            acc[p][r] = __dmul_rn(c.x, v[p][0]);
-            acc[p][r + 1] = __dmul_rn(c.y, v[p][0]);
-        }
-    }
-#pragma unroll
-    for (int k = 1; k < O; ++k) {
-#pragma unroll
-        for (int r = 0; r < O; r += 2) {
-            const double2 c = __ldg(c2 + (k * O + r) / 2);
-#pragma unroll
-            for (int p = 0; p < P; ++p) {
-                acc[p][r] = __fma_rn(c.x, v[p][k], acc[p][r]);
-                acc[p][r + 1] = __fma_rn(c.y, v[p][k], acc[p][r + 1]);
-            }
-        }
-    }
-}
-
-template <int ORDER, int P>
-__global__ void __launch_bounds__(kBinThreads)
-bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
-                  const uint32_t *__restrict__ perm, const uint32_t *__restrict__ tile_leaf,
-                  const uint32_t *__restrict__ n_tiles_p) {
-    constexpr int O = ORDER;
-    constexpr int TILE = 32 * P;
-    const uint32_t n_tiles = __ldg(n_tiles_p);
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t warps_per_cta = blockDim.x >> 5;
-    for (uint32_t t = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); t < n_tiles; t += gridDim.x * warps_per_cta) {
-        const uint32_t leaf = __ldg(tile_leaf + t);
-        const uint32_t node = __ldg(tv.leaf_node + leaf);
-        const NodeHead head = load_head(tv.nodes, node);
-        const NodeTail tail = load_tail(tv.nodes, node);
-        const double *C = tv.coeffs + 2ull * head.coeff16;
-
-        uint32_t idx[P];
-        double Ty[P][O], Tz[P][O], acc[P][O];
-        double x2[P], tx[P], tx_prev[P], val[P];
-#pragma unroll
-        for (int p = 0; p < P; ++p) {
-            idx[p] = __ldg(perm + (size_t)t * TILE + p * 32 + lane);
-            double px = head.c0, py = head.c1, pz = head.c2; // padding lanes evaluate the leaf centre
-            if (idx[p] != kInvalidSlot) {
-                const double *q = x + 3ull * idx[p];
-                px = __ldg(q);
-                py = __ldg(q + 1);
-                pz = __ldg(q + 2);
-            }
-            const double u = __dmul_rn(__dsub_rn(px, head.c0), tail.ih0);
-            const double v = __dmul_rn(__dsub_rn(py, head.c1), tail.ih1);
-            const double w = __dmul_rn(__dsub_rn(pz, head.c2), tail.ih2);
-            cheb_T<O>(v, Ty[p]);
-            cheb_T<O>(w, Tz[p]);
-            x2[p] = __dadd_rn(u, u);
-            tx_prev[p] = 1.0;
-            tx[p] = u; // becomes T_1 at i == 1
-            val[p] = 0.0;
-        }
-#pragma unroll 1
-        for (int i = 0; i < O; ++i) {
-            gemv_block_multi<O, P>(C + i * O * O, Tz, acc);
-#pragma unroll
-            for (int p = 0; p < P; ++p) {
-                const double d = dot_packets<O>(Ty[p], acc[p]);
-                double ti;
-                if (i == 0) {
-                    ti = 1.0;
-                } else if (i == 1) {
-                    ti = tx[p];
-                } else {
-                    ti = __fma_rn(x2[p], tx[p], -tx_prev[p]);
-                    tx_prev[p] = tx[p];
-                    tx[p] = ti;
-                }
-                val[p] = __fma_rn(ti, d, val[p]);
-            }
-        }
-#pragma unroll
-        for (int p = 0; p < P; ++p)
-            if (idx[p] != kInvalidSlot)
-                res[idx[p]] = val[p];
-    }
-}
-
 // ------------------------------------------------------------------------------------------ host side
 bool binned_supported(int dim, int order) { return dim == 3 && order >= 6 && order <= 16 && order % 2 == 0; }
 
@@ -242,7 +146,16 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         chunk = 1;
     if (chunk > 0x7FFFFFFFll)
         chunk = 0x7FFFFFFFll;
-    const int P = points_per_lane(dt.view.dim, dt.view.order);
+    int P = bin_eval_default_P(dt.view.order);
+    bool smem = bin_eval_default_smem(dt.view.order);
+    if (const char *e = std::getenv("BAOBZI_B200_P")) // tuning overrides (benchmarks)
+        if (bin_eval_variant_exists(dt.view.order, std::atoi(e), smem))
+            P = std::atoi(e);
+    if (const char *e = std::getenv("BAOBZI_B200_SMEM"))
+        if (bin_eval_variant_exists(dt.view.order, P, std::atoi(e) != 0))
+            smem = std::atoi(e) != 0;
+    ws.P = P;
+    ws.smem_coeffs = smem;
     const int64_t tile = 32 * P;
     const int64_t nl = dt.view.n_leaves;
     ws.perm_capacity = chunk + nl * tile;
@@ -289,11 +202,9 @@ void free_workspace(BinWorkspace &ws) {
     ws = BinWorkspace();
 }
 
-template <int O>
 static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, uint32_t n,
                            cudaStream_t st) {
-    constexpr int P = points_per_lane(3, O);
-    constexpr int TILE = 32 * P;
+    const uint32_t TILE = 32u * (uint32_t)ws.P;
     const TreeView &tv = dt.view;
     const unsigned cap = (unsigned)dt.sm_count * 16;
     unsigned g1 = (n + kBinThreads - 1) / kBinThreads;
@@ -308,17 +219,15 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
     bin_lookup_kernel<3><<<g1, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.key, ws.count, ws.cshift, n);
     if (pf)
         cudaEventRecord(ev[1], st);
-    bin_scan_kernel<TILE><<<1, 1024, 0, st>>>(tv.n_leaves, ws.count, ws.cursor, ws.cshift, ws.cnt, ws.start, ws.n_tiles);
-    bin_fill_kernel<TILE><<<(tv.n_leaves * 32 + kBinThreads - 1) / kBinThreads, kBinThreads, 0, st>>>(tv.n_leaves, ws.cnt, ws.start,
-                                                                                                  ws.tile_leaf, ws.perm);
+    bin_scan_kernel<<<1, 1024, 0, st>>>(TILE, tv.n_leaves, ws.count, ws.cursor, ws.cshift, ws.cnt, ws.start, ws.n_tiles);
+    bin_fill_kernel<<<(tv.n_leaves * 32 + kBinThreads - 1) / kBinThreads, kBinThreads, 0, st>>>(TILE, tv.n_leaves, ws.cnt,
+                                                                                            ws.start, ws.tile_leaf, ws.perm);
     if (pf)
         cudaEventRecord(ev[2], st);
     bin_scatter_kernel<<<g1, kBinThreads, 0, st>>>(ws.key, ws.start, ws.cursor, ws.cshift, ws.perm, n);
     if (pf)
         cudaEventRecord(ev[3], st);
-    // persistent grid: 2 CTAs of 8 warps per SM, each CTA walks 8 consecutive tiles (same leaf, L1 reuse)
-    const unsigned g4 = (unsigned)dt.sm_count * 2;
-    bin_eval3d_kernel<O, P><<<g4, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.perm, ws.tile_leaf, ws.n_tiles);
+    int rc = launch_bin_eval3d(dt, ws, d_x, d_res, st);
     if (pf) {
         cudaEventRecord(ev[4], st);
         pf->spans.push_back({kStageLookup, ev[0], ev[1], (int64_t)n});
@@ -326,7 +235,7 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         pf->spans.push_back({kStageScatter, ev[2], ev[3], (int64_t)n});
         pf->spans.push_back({kStageEval, ev[3], ev[4], (int64_t)n});
     }
-    return (int)cudaGetLastError();
+    return rc ? rc : (int)cudaGetLastError();
 }
 
 int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
@@ -335,16 +244,7 @@ int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x
         return 0;
     if (dt.view.dim != 3 || n > ws.chunk_capacity)
         return (int)cudaErrorInvalidValue;
-    int rc;
-    switch (dt.view.order) {
-    case 6: rc = launch_chunk_3d<6>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
-    case 8: rc = launch_chunk_3d<8>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
-    case 10: rc = launch_chunk_3d<10>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
-    case 12: rc = launch_chunk_3d<12>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
-    case 14: rc = launch_chunk_3d<14>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
-    case 16: rc = launch_chunk_3d<16>(dt, ws, d_x, d_res, (uint32_t)n, stream); break;
-    default: return (int)cudaErrorInvalidValue;
-    }
+    int rc = launch_chunk_3d(dt, ws, d_x, d_res, (uint32_t)n, stream);
     if (launches)
         *launches += 5;
     return rc;

@@ -78,6 +78,8 @@ struct BinWorkspace {
     uint32_t *count = nullptr;  // [n_leaves + 1]     histogram (zero between chunks: the scan clears it)
     uint32_t *cursor = nullptr; // [n_leaves + 1]     per-leaf fill cursor of the scatter (cleared by the scan)
     uint32_t *cnt = nullptr;    // [n_leaves + 1]     dense copy of the histogram for the fill kernel
+    int P = 2;                  // points per lane of the evaluation kernel (tile = 32 * P slots)
+    bool smem_coeffs = false;   // stage each tile's coefficient block in shared memory
     int cshift = 0;             // count[] / cursor[] entries are spread 2^cshift words apart so that atomics of
                                 // different leaves land in different L2 sectors / lines
     uint32_t *start = nullptr;  // [n_leaves + 1]     padded exclusive scan
