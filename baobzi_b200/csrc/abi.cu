@@ -83,13 +83,17 @@ bool report(cudaError_t e, const char *what) {
     return true;
 }
 
-int64_t default_chunk() {
+// Points per binned chunk.  Large enough that every leaf fills many warp tiles (padding waste ~ tile / points
+// per leaf), small enough that the chunk's keys / slots mostly stay in L2: 2048 points per leaf, clamped.
+int64_t default_chunk(const DeviceTree &dt) {
     if (const char *s = std::getenv("BAOBZI_B200_CHUNK")) {
         long long v = std::atoll(s);
         if (v > 0)
             return v;
     }
-    return int64_t(1) << 21; // 2 Mi points: x + keys + perm + res of a chunk stay L2 resident
+    int64_t c = (int64_t)dt.view.n_leaves * 2048;
+    const int64_t lo = int64_t(1) << 21, hi = int64_t(1) << 24;
+    return c < lo ? lo : (c > hi ? hi : c);
 }
 
 int env_mode() {
@@ -176,7 +180,7 @@ int eval_device(Function *f, Replica *r, BinWorkspace &ws, const double *d_x, do
     StageProfile *prof = f->profile.get();
     ws.prof = prof;
     if (use_binned(f, r->dt, n)) {
-        int64_t step = f->chunk > 0 ? f->chunk : default_chunk();
+        int64_t step = f->chunk > 0 ? f->chunk : default_chunk(r->dt);
         if (step > n)
             step = n;
         if (ws.chunk_capacity < step) {
