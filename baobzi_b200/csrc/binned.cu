@@ -31,6 +31,7 @@ constexpr int kBinThreads = 256;
 int bin_eval_default_P(int order);
 bool bin_eval_default_smem(int order);
 bool bin_eval_variant_exists(int order, int P, bool smem);
+bool bin_eval_pipe_exists(int order, int P);
 int launch_bin_eval3d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------------ K1
@@ -110,8 +111,9 @@ bin_scan_kernel(uint32_t TILE, uint32_t n_leaves, uint32_t *__restrict__ count, 
 
 // K2b: one warp per leaf marks the padding slots of perm[] invalid and records the leaf of each of its tiles.
 __global__ void __launch_bounds__(kBinThreads)
-bin_fill_kernel(uint32_t TILE, uint32_t n_leaves, const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ start,
-                uint32_t *__restrict__ tile_leaf, uint32_t *__restrict__ perm) {
+bin_fill_kernel(const TreeView tv, uint32_t TILE, uint32_t n_leaves, const uint32_t *__restrict__ cnt,
+                const uint32_t *__restrict__ start, uint32_t *__restrict__ tile_leaf, uint2 *__restrict__ tile_info,
+                uint32_t *__restrict__ perm) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t l = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (l >= n_leaves)
@@ -120,8 +122,12 @@ bin_fill_kernel(uint32_t TILE, uint32_t n_leaves, const uint32_t *__restrict__ c
     const uint32_t padded = (c + TILE - 1) / TILE * TILE;
     for (uint32_t s = s0 + c + lane; s < s0 + padded; s += 32)
         perm[s] = kInvalidSlot;
-    for (uint32_t t = s0 / TILE + lane; t < (s0 + padded) / TILE; t += 32)
+    const uint32_t node = __ldg(tv.leaf_node + l);
+    const uint2 info = make_uint2(node, load_head(tv.nodes, node).coeff16);
+    for (uint32_t t = s0 / TILE + lane; t < (s0 + padded) / TILE; t += 32) {
         tile_leaf[t] = l;
+        tile_info[t] = info;
+    }
 }
 
 // ------------------------------------------------------------------------------------------ K3
@@ -156,6 +162,9 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             smem = std::atoi(e) != 0;
     ws.P = P;
     ws.smem_coeffs = smem;
+    ws.pipelined = bin_eval_pipe_exists(dt.view.order, P);
+    if (const char *e = std::getenv("BAOBZI_B200_PIPE"))
+        ws.pipelined = ws.pipelined && std::atoi(e) != 0;
     const int64_t tile = 32 * P;
     const int64_t nl = dt.view.n_leaves;
     ws.perm_capacity = chunk + nl * tile;
@@ -181,6 +190,8 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     if (e == cudaSuccess)
         e = cudaMalloc((void **)&ws.n_tiles, sizeof(uint32_t));
     if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.tile_info, sizeof(uint2) * ws.tile_capacity);
+    if (e == cudaSuccess)
         e = cudaMemset(ws.count, 0, sizeof(uint32_t) * cwords);
     if (e != cudaSuccess) {
         free_workspace(ws);
@@ -199,6 +210,7 @@ void free_workspace(BinWorkspace &ws) {
     cudaFree(ws.start);
     cudaFree(ws.tile_leaf);
     cudaFree(ws.n_tiles);
+    cudaFree(ws.tile_info);
     ws = BinWorkspace();
 }
 
@@ -220,8 +232,8 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
     if (pf)
         cudaEventRecord(ev[1], st);
     bin_scan_kernel<<<1, 1024, 0, st>>>(TILE, tv.n_leaves, ws.count, ws.cursor, ws.cshift, ws.cnt, ws.start, ws.n_tiles);
-    bin_fill_kernel<<<(tv.n_leaves * 32 + kBinThreads - 1) / kBinThreads, kBinThreads, 0, st>>>(TILE, tv.n_leaves, ws.cnt,
-                                                                                            ws.start, ws.tile_leaf, ws.perm);
+    bin_fill_kernel<<<(tv.n_leaves * 32 + kBinThreads - 1) / kBinThreads, kBinThreads, 0, st>>>(
+        tv, TILE, tv.n_leaves, ws.cnt, ws.start, ws.tile_leaf, ws.tile_info, ws.perm);
     if (pf)
         cudaEventRecord(ev[2], st);
     bin_scatter_kernel<<<g1, kBinThreads, 0, st>>>(ws.key, ws.start, ws.cursor, ws.cshift, ws.perm, n);

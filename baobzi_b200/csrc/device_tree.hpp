@@ -80,6 +80,8 @@ struct BinWorkspace {
     uint32_t *cnt = nullptr;    // [n_leaves + 1]     dense copy of the histogram for the fill kernel
     int P = 2;                  // points per lane of the evaluation kernel (tile = 32 * P slots)
     bool smem_coeffs = false;   // stage each tile's coefficient block in shared memory
+    bool pipelined = false;     // K4 variant with cp.async double buffering (bin_eval.cu)
+    uint2 *tile_info = nullptr; // [max_tiles] {node, coefficient offset / 16 B} of each tile's leaf
     int cshift = 0;             // count[] / cursor[] entries are spread 2^cshift words apart so that atomics of
                                 // different leaves land in different L2 sectors / lines
     uint32_t *start = nullptr;  // [n_leaves + 1]     padded exclusive scan
