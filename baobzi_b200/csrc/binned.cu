@@ -56,6 +56,60 @@ bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__res
     }
 }
 
+// ------------------------------------------------------------------------------------------ K1/K3, privatised
+// Same job as K1/K3 with one shared-memory atomic per point instead of two global ones: every CTA owns a
+// contiguous range of the chunk, histograms it in shared memory (the atomic's return value is the point's rank
+// inside (CTA, leaf)), then reserves its share of every leaf with ONE global atomic per non-empty (CTA, leaf).
+// K3 becomes atomic-free: slot = start[leaf] + base[CTA][leaf] + rank.  Used when the histogram fits in smem.
+template <int DIM>
+__global__ void __launch_bounds__(kBinThreads)
+bin_lookup2_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                   uint32_t *__restrict__ key, uint32_t *__restrict__ rank, uint32_t *__restrict__ count, int cshift,
+                   uint32_t *__restrict__ cta_base, uint32_t n) {
+    extern __shared__ uint32_t hist[];
+    const uint32_t nl = tv.n_leaves;
+    for (uint32_t l = threadIdx.x; l < nl; l += blockDim.x)
+        hist[l] = 0;
+    __syncthreads();
+    const uint32_t lo = (uint32_t)(((uint64_t)blockIdx.x * n) / gridDim.x);
+    const uint32_t hi = (uint32_t)(((uint64_t)(blockIdx.x + 1) * n) / gridDim.x);
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        double p[DIM];
+        load_point_keep<DIM>(x, i, p);
+        if (outside<DIM>(tv, p)) {
+            res[i] = __longlong_as_double(0x7ff8000000000000ll);
+            key[i] = kNotLeaf;
+            continue;
+        }
+        NodeHead head;
+        const uint32_t node = locate<DIM>(tv, p, head);
+        const uint32_t leaf = load_tail(tv.nodes, node).leaf_rank;
+        key[i] = leaf;
+        rank[i] = atomicAdd(hist + leaf, 1u);
+    }
+    __syncthreads();
+    for (uint32_t l = threadIdx.x; l < nl; l += blockDim.x) {
+        const uint32_t h = hist[l];
+        if (h)
+            cta_base[(size_t)blockIdx.x * nl + l] = atomicAdd(count + ((size_t)l << cshift), h);
+    }
+}
+
+__global__ void __launch_bounds__(kBinThreads)
+bin_scatter2_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict__ rank,
+                    const uint32_t *__restrict__ start, const uint32_t *__restrict__ cta_base, uint32_t n_leaves,
+                    uint32_t *__restrict__ perm, uint32_t n) {
+    const uint32_t lo = (uint32_t)(((uint64_t)blockIdx.x * n) / gridDim.x);
+    const uint32_t hi = (uint32_t)(((uint64_t)(blockIdx.x + 1) * n) / gridDim.x);
+    const uint32_t *base = cta_base + (size_t)blockIdx.x * n_leaves;
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        const uint32_t k = __ldcs(key + i);
+        if (k == kNotLeaf)
+            continue;
+        perm[__ldg(start + k) + __ldg(base + k) + __ldcs(rank + i)] = i;
+    }
+}
+
 // ------------------------------------------------------------------------------------------ K2
 // Single CTA: exclusive scan of the per-leaf counts rounded up to the warp-tile size.  count[] in: histogram;
 // out: zero (ready for the next chunk's K1).  cursor[] out: zero (for K3).  cnt[] out: dense copy for K2b.
@@ -174,7 +228,15 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     while (ws.cshift < 5 && ((nl + 1) << (ws.cshift + 1)) <= (1 << 20))
         ws.cshift++;
     const size_t cwords = (size_t)(nl + 1) << ws.cshift;
+    ws.privatized = (size_t)nl * sizeof(uint32_t) <= 160 * 1024;
+    if (const char *e = std::getenv("BAOBZI_B200_PRIVATE"))
+        ws.privatized = ws.privatized && std::atoi(e) != 0;
+    ws.sort_ctas = dt.sm_count * 4;
     cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
+    if (e == cudaSuccess && ws.privatized)
+        e = cudaMalloc((void **)&ws.rank, sizeof(uint32_t) * chunk);
+    if (e == cudaSuccess && ws.privatized)
+        e = cudaMalloc((void **)&ws.cta_base, sizeof(uint32_t) * (size_t)ws.sort_ctas * (nl + 1));
     if (e == cudaSuccess)
         e = cudaMalloc((void **)&ws.perm, sizeof(uint32_t) * ws.perm_capacity);
     if (e == cudaSuccess)
@@ -210,6 +272,8 @@ void free_workspace(BinWorkspace &ws) {
     cudaFree(ws.start);
     cudaFree(ws.tile_leaf);
     cudaFree(ws.n_tiles);
+    cudaFree(ws.rank);
+    cudaFree(ws.cta_base);
     cudaFree(ws.tile_info);
     ws = BinWorkspace();
 }
@@ -228,7 +292,18 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
             e = pf->get();
         cudaEventRecord(ev[0], st);
     }
-    bin_lookup_kernel<3><<<g1, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.key, ws.count, ws.cshift, n);
+    const size_t hist_bytes = (size_t)tv.n_leaves * sizeof(uint32_t);
+    if (ws.privatized) {
+        static bool configured = false;
+        if (!configured && hist_bytes > 48 * 1024) {
+            cudaFuncSetAttribute(bin_lookup2_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+            configured = true;
+        }
+        bin_lookup2_kernel<3><<<ws.sort_ctas, kBinThreads, hist_bytes, st>>>(tv, d_x, d_res, ws.key, ws.rank, ws.count,
+                                                                           ws.cshift, ws.cta_base, n);
+    } else {
+        bin_lookup_kernel<3><<<g1, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.key, ws.count, ws.cshift, n);
+    }
     if (pf)
         cudaEventRecord(ev[1], st);
     bin_scan_kernel<<<1, 1024, 0, st>>>(TILE, tv.n_leaves, ws.count, ws.cursor, ws.cshift, ws.cnt, ws.start, ws.n_tiles);
@@ -236,7 +311,10 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         tv, TILE, tv.n_leaves, ws.cnt, ws.start, ws.tile_leaf, ws.tile_info, ws.perm);
     if (pf)
         cudaEventRecord(ev[2], st);
-    bin_scatter_kernel<<<g1, kBinThreads, 0, st>>>(ws.key, ws.start, ws.cursor, ws.cshift, ws.perm, n);
+    if (ws.privatized)
+        bin_scatter2_kernel<<<ws.sort_ctas, kBinThreads, 0, st>>>(ws.key, ws.rank, ws.start, ws.cta_base, tv.n_leaves, ws.perm, n);
+    else
+        bin_scatter_kernel<<<g1, kBinThreads, 0, st>>>(ws.key, ws.start, ws.cursor, ws.cshift, ws.perm, n);
     if (pf)
         cudaEventRecord(ev[3], st);
     int rc = launch_bin_eval3d(dt, ws, d_x, d_res, st);

@@ -81,6 +81,10 @@ struct BinWorkspace {
     int P = 2;                  // points per lane of the evaluation kernel (tile = 32 * P slots)
     bool smem_coeffs = false;   // stage each tile's coefficient block in shared memory
     bool pipelined = false;     // K4 variant with cp.async double buffering (bin_eval.cu)
+    bool privatized = false;    // K1/K3 with per-CTA shared-memory histograms (binned.cu)
+    int sort_ctas = 0;
+    uint32_t *rank = nullptr;     // [chunk] rank of a point inside its (CTA, leaf)
+    uint32_t *cta_base = nullptr; // [sort_ctas][n_leaves] first slot of (CTA, leaf) relative to start[leaf]
     uint2 *tile_info = nullptr; // [max_tiles] {node, coefficient offset / 16 B} of each tile's leaf
     int cshift = 0;             // count[] / cursor[] entries are spread 2^cshift words apart so that atomics of
                                 // different leaves land in different L2 sectors / lines
