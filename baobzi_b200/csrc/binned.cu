@@ -73,19 +73,32 @@ bin_lookup2_kernel(const TreeView tv, const double *__restrict__ x, double *__re
     __syncthreads();
     const uint32_t lo = (uint32_t)(((uint64_t)blockIdx.x * n) / gridDim.x);
     const uint32_t hi = (uint32_t)(((uint64_t)(blockIdx.x + 1) * n) / gridDim.x);
-    for (uint32_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-        double p[DIM];
-        load_point_keep<DIM>(x, i, p);
-        if (outside<DIM>(tv, p)) {
-            res[i] = __longlong_as_double(0x7ff8000000000000ll);
-            key[i] = kNotLeaf;
-            continue;
+    // two points per thread per trip: the lookup is a chain of dependent L2 loads, so independent chains are
+    // what keeps the memory system busy
+    for (uint32_t i0 = lo + threadIdx.x; i0 < hi; i0 += 2 * blockDim.x) {
+        const uint32_t i1 = i0 + blockDim.x;
+        const bool has1 = i1 < hi;
+        double p0[DIM], p1[DIM];
+        load_point_keep<DIM>(x, i0, p0);
+        load_point_keep<DIM>(x, has1 ? i1 : i0, p1);
+        const bool out0 = outside<DIM>(tv, p0), out1 = outside<DIM>(tv, p1) || !has1;
+        uint32_t leaf0 = kNotLeaf, leaf1 = kNotLeaf;
+        if (!out0)
+            leaf0 = locate_leaf<DIM>(tv, p0);
+        if (!out1)
+            leaf1 = locate_leaf<DIM>(tv, p1);
+        if (out0)
+            res[i0] = __longlong_as_double(0x7ff8000000000000ll);
+        else
+            rank[i0] = atomicAdd(hist + leaf0, 1u);
+        key[i0] = leaf0;
+        if (has1) {
+            if (outside<DIM>(tv, p1))
+                res[i1] = __longlong_as_double(0x7ff8000000000000ll);
+            else
+                rank[i1] = atomicAdd(hist + leaf1, 1u);
+            key[i1] = leaf1;
         }
-        NodeHead head;
-        const uint32_t node = locate<DIM>(tv, p, head);
-        const uint32_t leaf = load_tail(tv.nodes, node).leaf_rank;
-        key[i] = leaf;
-        rank[i] = atomicAdd(hist + leaf, 1u);
     }
     __syncthreads();
     for (uint32_t l = threadIdx.x; l < nl; l += blockDim.x) {
@@ -102,11 +115,18 @@ bin_scatter2_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict
     const uint32_t lo = (uint32_t)(((uint64_t)blockIdx.x * n) / gridDim.x);
     const uint32_t hi = (uint32_t)(((uint64_t)(blockIdx.x + 1) * n) / gridDim.x);
     const uint32_t *base = cta_base + (size_t)blockIdx.x * n_leaves;
-    for (uint32_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-        const uint32_t k = __ldcs(key + i);
-        if (k == kNotLeaf)
-            continue;
-        perm[__ldg(start + k) + __ldg(base + k) + __ldcs(rank + i)] = i;
+    for (uint32_t i0 = lo + threadIdx.x; i0 < hi; i0 += 4 * blockDim.x) {
+        uint32_t k[4], r[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t i = i0 + u * blockDim.x;
+            k[u] = i < hi ? __ldcs(key + i) : kNotLeaf;
+            r[u] = i < hi ? __ldcs(rank + i) : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (k[u] != kNotLeaf)
+                perm[__ldg(start + k[u]) + __ldg(base + k[u]) + r[u]] = i0 + u * blockDim.x;
     }
 }
 
@@ -231,7 +251,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     ws.privatized = (size_t)nl * sizeof(uint32_t) <= 160 * 1024;
     if (const char *e = std::getenv("BAOBZI_B200_PRIVATE"))
         ws.privatized = ws.privatized && std::atoi(e) != 0;
-    ws.sort_ctas = dt.sm_count * 4;
+    ws.sort_ctas = dt.sm_count * 8;
     cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
     if (e == cudaSuccess && ws.privatized)
         e = cudaMalloc((void **)&ws.rank, sizeof(uint32_t) * chunk);

@@ -84,6 +84,35 @@ __device__ __forceinline__ uint32_t locate(const TreeView &tv, const double (&x)
     return node;
 }
 
+// Same walk, but every step fetches the whole 64-byte record (both sectors of one line in a single round
+// trip) and only the dense leaf rank is returned: one dependent load fewer than locate() + load_tail().
+template <int DIM>
+__device__ __forceinline__ uint32_t locate_leaf(const TreeView &tv, const double (&x)[DIM]) {
+    int lin = 0, stride = 1;
+#pragma unroll
+    for (int j = 0; j < DIM; ++j) {
+        const double xb = __dsub_rn(x[j], tv.lower_left[j]);
+        int b = __double2int_rz(__dmul_rn(xb, tv.inv_bin_size[j]));
+        b = min(max(b, 0), tv.n_sub[j] - 1);
+        lin += stride * b;
+        stride *= tv.n_sub[j];
+    }
+    uint32_t node = __ldg(tv.bin_root + lin);
+    for (;;) {
+        const double2 *p = reinterpret_cast<const double2 *>(tv.nodes + node);
+        const double2 a = __ldg(p), b = __ldg(p + 1), d = __ldg(p + 3);
+        const uint32_t child0 = (uint32_t)(unsigned long long)__double_as_longlong(b.y);
+        if (child0 == kLeafMark)
+            return (uint32_t)((unsigned long long)__double_as_longlong(d.y) >> 32);
+        uint32_t bits = (uint32_t)(x[0] > a.x);
+        if (DIM > 1)
+            bits |= (uint32_t)(x[1] > a.y) << 1;
+        if (DIM > 2)
+            bits |= (uint32_t)(x[2] > b.x) << 2;
+        node = child0 + bits;
+    }
+}
+
 template <int DIM>
 __device__ __forceinline__ void load_point(const double *__restrict__ x, int64_t i, double (&p)[DIM]) {
     if constexpr (DIM == 2) {
