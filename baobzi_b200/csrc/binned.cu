@@ -251,7 +251,10 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     ws.privatized = (size_t)nl * sizeof(uint32_t) <= 160 * 1024;
     if (const char *e = std::getenv("BAOBZI_B200_PRIVATE"))
         ws.privatized = ws.privatized && std::atoi(e) != 0;
-    ws.sort_ctas = dt.sm_count * 8;
+    ws.sort_ctas = dt.sm_count * 4;
+    if (const char *e = std::getenv("BAOBZI_B200_SORT_CTAS"))
+        if (std::atoi(e) > 0)
+            ws.sort_ctas = dt.sm_count * std::atoi(e);
     cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
     if (e == cudaSuccess && ws.privatized)
         e = cudaMalloc((void **)&ws.rank, sizeof(uint32_t) * chunk);

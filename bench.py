@@ -83,39 +83,46 @@ class ClockSampler:
         self.idx, self.proc, self.lines = gpu_index, None, []
 
     def start(self):
+        """Start sampling (nvidia-smi needs a moment to come up, so call this before the warm-up steps)."""
+        def reader():
+            for ln in self.proc.stdout:
+                self.lines.append((time.perf_counter(), ln))
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True)
+            self.thread = threading.Thread(target=reader, daemon=True)
             self.thread.start()
         except Exception:
             self.proc = None
 
-    def stop(self):
+    def stop(self, t_begin, t_end):
+        """Summarise the samples that arrived inside the timed region [t_begin, t_end] (perf_counter times)."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
         self.thread.join(timeout=2)
-        sm, mx, reasons = [], [], set()
+        sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        inside = [ln for (ts, ln) in self.lines if t_begin <= ts <= t_end + 0.06]
+        for ln in inside:
             f = [t.strip() for t in ln.split(",")]
             if len(f) < 7:
                 continue
             try:
                 sm.append(float(f[0]))
                 mx.append(float(f[1]))
+                pw.append(float(f[2]))
             except ValueError:
                 continue
             for nm, v in zip(names, f[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(nm)
         if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        busy = sorted(sm)[len(sm) // 4:]  # drop the idle samples at the edges
-        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                "samples": len(sm)}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples inside the timed region"],
+                    "samples": 0, "samples_total": len(self.lines)}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(pw)}
 
 
 # ------------------------------------------------------------------------------------------------ CPU side
@@ -274,24 +281,26 @@ def run_ours(args, cfg, rank, world, local_rank):
             torch.distributed.barrier()
         torch.cuda.synchronize(dev)
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     for _ in range(args.warmup):
         step()
     barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     launches0 = b.launches
     if not args.no_profile:
         b.profile_begin()                      # per-launch CUDA events inside the timed region (roofline)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_begin = time.perf_counter()
     ev0.record(stream)
     for _ in range(args.steps):
         step()
     ev1.record(stream)
     barrier()
+    t_end = time.perf_counter()
     ms = ev0.elapsed_time(ev1)
     stages = b.profile_end() if not args.no_profile else {}
     launches = b.launches - launches0
-    clocks = sampler.stop()
+    clocks = sampler.stop(t_begin, t_end)
     if world > 1:
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
