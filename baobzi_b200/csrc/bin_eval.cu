@@ -1,132 +1,35 @@
-// bin_eval.cu -- K4 of the binned path: evaluation of leaf-grouped points (see binned.cu for K1-K3).
+// bin_eval.cu -- K4 of the binned path: evaluation of leaf-grouped points (see binned.cu for the sort).
 //
 // One warp per tile of 32*P consecutive slots of ONE leaf; lane l owns slots l, l+32, ... (P points, register
-// blocked).  Because the whole warp sits in one leaf, a coefficient pair is a warp-uniform 16-byte load whose
-// value feeds 2*P FMAs per lane.
+// blocked).  Because the whole warp sits in one leaf, a coefficient pair is a warp-uniform 16-byte shared-memory
+// load whose value feeds 2*P FMAs per lane.
 //
-// What bounds it (ncu, profiles/): the FP64 pipe issues one warp-wide DFMA per 2 cycles per SM sub-partition,
-// but a uniform 128-bit load still occupies the LSU data pipe for 4 wavefronts (512 B written back to the
-// register file at 128 B/clk per SM).  With P points per lane the ratio is 4 LSU cycles (shared by the 4
-// sub-partitions) per 2*P DFMAs = 4*P FP64 cycles of one sub-partition, so P = 2 is LSU-bound (4 x 4 > 8) and
-// P = 4 is balanced (16 = 16).  Hence P = 4 where the registers allow it (order <= 8), the T-vector of the
-// middle axis is rebuilt at the end of every slab instead of being kept live, and the coefficient block can be
-// staged per warp in shared memory (SMEM variant) so that loads have a short fixed latency and never miss.
+// What bounds it (ncu, profiles/): the FP64 pipe issues one warp-wide DFMA per 2 cycles per SM sub-partition.
+// A warp-uniform LDS costs one LSU wavefront per coefficient, so with P points per lane the four sub-partitions
+// together ask for 2/P wavefronts per cycle at full FP64 rate: P = 2 would be LSU bound, P = 3 needs 2/3 of the
+// LSU, P = 4 one half.  The other limit is latency hiding: P*O accumulators + P*O values of T(z) per lane put a
+// P = 4 warp at ~250 registers, i.e. 2 warps per scheduler, and two warps leave the pipe idle whenever both wait
+// (measured: 70 % busy).  Hence the knobs below: P, warps per CTA, T(z) either held in registers or advanced on
+// the fly in the k loop (3 live values per point instead of O), T(y) rebuilt per slab instead of kept live.
 //
-// Arithmetic: exactly cheb.cuh's order (bit-identical to the reference's AVX2+FMA build); only the interleaving
-// of independent row chains across the P points differs, which does not change any rounding.
+// Each warp runs a 2-stage software pipeline over its tiles: while tile j is evaluated out of shared memory,
+// tile j+1's inputs (the leaf's coefficient block, the node record, the gathered points and their indices) are
+// in flight as cp.async copies, and tile j+2's descriptor is being fetched into registers.
+//
+// Arithmetic: cheb.cuh's order (bit-identical to the reference's AVX2+FMA build).  Multiplications by
+// T_0 = 1.0 are not executed (x * 1.0 == x bit for bit): a row chain starts as fma(c_1, T_1, c_0), and the
+// T recurrences run from T_{-1} = T_1 = x so that every slab executes the same code (fma(2x, 1, -x) == x exactly).
 #include "cheb.cuh"
 #include "device_tree.hpp"
 #include "lookup.cuh"
+
+#include <cstdio>
+#include <cstdlib>
 
 namespace bz {
 
 constexpr uint32_t kInvalidSlotE = 0xFFFFFFFFu;
 
-template <int O, int P, bool SMEM, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, 1)
-bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
-                  const uint32_t *__restrict__ perm, const uint32_t *__restrict__ tile_leaf,
-                  const uint32_t *__restrict__ n_tiles_p) {
-    constexpr int TILE = 32 * P;
-    constexpr int BLK2 = O * O * O / 2; // double2 per leaf block
-    extern __shared__ double2 smem2[];
-    const uint32_t n_tiles = __ldg(n_tiles_p);
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double2 *wbuf = smem2 + (SMEM ? warp * BLK2 : 0);
-
-    for (uint32_t t = blockIdx.x * WARPS + warp; t < n_tiles; t += gridDim.x * WARPS) {
-        const uint32_t leaf = __ldg(tile_leaf + t);
-        const uint32_t node = __ldg(tv.leaf_node + leaf);
-        const NodeHead head = load_head(tv.nodes, node);
-        const NodeTail tail = load_tail(tv.nodes, node);
-        const double2 *Cg = reinterpret_cast<const double2 *>(tv.coeffs + 2ull * head.coeff16);
-
-        uint32_t idx[P];
-#pragma unroll
-        for (int p = 0; p < P; ++p)
-            idx[p] = __ldg(perm + (size_t)t * TILE + p * 32 + lane);
-        if (SMEM) { // stage this leaf's block: coalesced 16-byte loads, no reuse across warps needed
-            __syncwarp();
-#pragma unroll 4
-            for (int j = lane; j < BLK2; j += 32)
-                wbuf[j] = __ldg(Cg + j);
-        }
-        double Tz[P][O], acc[P][O];
-        double v[P], x2[P], tx[P], tx_prev[P], val[P];
-#pragma unroll
-        for (int p = 0; p < P; ++p) {
-            double px = head.c0, py = head.c1, pz = head.c2; // padding lanes evaluate the leaf centre
-            if (idx[p] != kInvalidSlotE) {
-                const double *q = x + 3ull * idx[p];
-                px = __ldg(q);
-                py = __ldg(q + 1);
-                pz = __ldg(q + 2);
-            }
-            const double u = __dmul_rn(__dsub_rn(px, head.c0), tail.ih0);
-            v[p] = __dmul_rn(__dsub_rn(py, head.c1), tail.ih1);
-            const double w = __dmul_rn(__dsub_rn(pz, head.c2), tail.ih2);
-            cheb_T<O>(w, Tz[p]);
-            x2[p] = __dadd_rn(u, u);
-            tx_prev[p] = 1.0;
-            tx[p] = u;
-            val[p] = 0.0;
-        }
-        if (SMEM)
-            __syncwarp();
-        const double2 *Cb = SMEM ? wbuf : Cg;
-
-#pragma unroll 1
-        for (int i = 0; i < O; ++i) {
-            const double2 *c2 = Cb + i * (O * O / 2);
-            // acc[p][r] = sum_k C_i(r,k) Tz[p][k]: row chains in k order, first term a plain product
-#pragma unroll
-            for (int k = 0; k < O; ++k) {
-#pragma unroll
-                for (int r = 0; r < O; r += 2) {
-                    const double2 c = SMEM ? c2[(k * O + r) / 2] : __ldg(c2 + (k * O + r) / 2);
-#pragma unroll
-                    for (int p = 0; p < P; ++p) {
-                        if (k == 0) {
-                            acc[p][r] = __dmul_rn(c.x, Tz[p][0]);
-                            acc[p][r + 1] = __dmul_rn(c.y, Tz[p][0]);
-                        } else {
-                            acc[p][r] = __fma_rn(c.x, Tz[p][k], acc[p][r]);
-                            acc[p][r + 1] = __fma_rn(c.y, Tz[p][k], acc[p][r + 1]);
-                        }
-                    }
-                }
-            }
-#pragma unroll
-            for (int p = 0; p < P; ++p) {
-                double Ty[O];
-                cheb_T<O>(v[p], Ty); // rebuilt per slab: O-2 FMAs instead of O live registers per point
-                const double d = dot_packets<O>(Ty, acc[p]);
-                double ti;
-                if (i == 0) {
-                    ti = 1.0;
-                } else if (i == 1) {
-                    ti = tx[p];
-                } else {
-                    ti = __fma_rn(x2[p], tx[p], -tx_prev[p]);
-                    tx_prev[p] = tx[p];
-                    tx[p] = ti;
-                }
-                val[p] = __fma_rn(ti, d, val[p]);
-            }
-        }
-#pragma unroll
-        for (int p = 0; p < P; ++p)
-            if (idx[p] != kInvalidSlotE)
-                res[idx[p]] = val[p];
-    }
-}
-
-// ------------------------------------------------------------------------------------------ pipelined K4
-// Same arithmetic, but each warp runs a 2-stage software pipeline over its tiles: while tile j is evaluated
-// out of shared memory, tile j+1's inputs (the leaf's coefficient block, the node record, the gathered points
-// and their indices) are already in flight as cp.async copies, and tile j+2's descriptor is being fetched into
-// registers.  The prologue latency (dependent L2/HBM loads: slot -> point) that left the FP64 pipe idle a third
-// of the time in the unpipelined kernel (profiles/r01_k4_P4_smem_ncu_summary.json: long_scoreboard) is hidden.
 __device__ __forceinline__ void cp_async8(void *smem, const void *gmem) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
 }
@@ -148,13 +51,48 @@ struct PipeStage { // per warp, per stage
     uint32_t idx[TILE];
 };
 
-template <int O, int P, int WARPS>
+// <Ty, acc> in Eigen's packet order (cheb.cuh dot_packets) with Ty[0] == 1.0 known: its product is acc[0] itself.
+template <int START, int LEN, int STRIDE, int LANE, int O>
+__device__ __forceinline__ double dot_tree_one(const double (&a)[O], const double (&b)[O]) {
+    constexpr int i0 = START * STRIDE + LANE;
+    if constexpr (i0 != 0) {
+        return dot_tree<START, LEN, STRIDE, LANE, O>(a, b);
+    } else if constexpr (LEN == 1) {
+        return b[0];
+    } else if constexpr (LEN == 2) {
+        return __fma_rn(a[STRIDE], b[STRIDE], b[0]);
+    } else if constexpr (LEN == 3) {
+        return __dadd_rn(b[0], dot_tree<START + 1, 2, STRIDE, LANE, O>(a, b)); // fma(1, b0, s) == b0 + s
+    } else {
+        constexpr int H = LEN / 2;
+        return __dadd_rn(dot_tree_one<START, H, STRIDE, LANE, O>(a, b), dot_tree<START + H, LEN - H, STRIDE, LANE, O>(a, b));
+    }
+}
+template <int O>
+__device__ __forceinline__ double dot_packets_one(const double (&a)[O], const double (&b)[O]) {
+    if constexpr (O % 4 == 0) {
+        const double l0 = dot_tree_one<0, O / 4, 4, 0, O>(a, b);
+        const double l1 = dot_tree<0, O / 4, 4, 1, O>(a, b);
+        const double l2 = dot_tree<0, O / 4, 4, 2, O>(a, b);
+        const double l3 = dot_tree<0, O / 4, 4, 3, O>(a, b);
+        return __dadd_rn(__dadd_rn(l0, l2), __dadd_rn(l1, l3));
+    } else {
+        const double l0 = dot_tree_one<0, O / 2, 2, 0, O>(a, b);
+        const double l1 = dot_tree<0, O / 2, 2, 1, O>(a, b);
+        return __dadd_rn(l0, l1);
+    }
+}
+
+// TZFLY: T_k(z) advanced inside the k loop (costs O-2 extra FMAs per point and slab, frees (O-3)*P doubles).
+// TYKEEP: T(y) computed once per tile and kept live (O*P doubles) instead of rebuilt after every slab.
+template <int O, int P, int WARPS, bool TZFLY, bool TYKEEP, int EXP = 0>
 __global__ void __launch_bounds__(WARPS * 32, 1)
-bin_eval3d_pipe_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
-                       const uint32_t *__restrict__ perm, const uint2 *__restrict__ tile_info,
-                       const uint32_t *__restrict__ n_tiles_p) {
+bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                  const uint32_t *__restrict__ perm, const uint2 *__restrict__ tile_info,
+                  const uint32_t *__restrict__ n_tiles_p) {
     constexpr int TILE = 32 * P;
     constexpr int BLK2 = O * O * O / 2;
+    constexpr int NTZ = TZFLY ? 1 : O;
     using Stage = PipeStage<O, P>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t n_tiles = __ldg(n_tiles_p);
@@ -178,7 +116,7 @@ bin_eval3d_pipe_kernel(const TreeView tv, const double *__restrict__ x, double *
         }
     };
     auto issue = [&](uint32_t tt, const uint2 &info, const uint32_t (&id)[P], Stage &st) {
-        if (tt < n_tiles) {
+        if (tt < n_tiles && !(EXP == 2 && tt >= blockIdx.x * WARPS + warp + 2 * stride)) {
             const double2 *Cg = reinterpret_cast<const double2 *>(tv.coeffs + 2ull * info.y);
 #pragma unroll 4
             for (int j = lane; j < BLK2; j += 32)
@@ -215,8 +153,8 @@ bin_eval3d_pipe_kernel(const TreeView tv, const double *__restrict__ x, double *
 
         const double2 n0 = st.node[0], n1 = st.node[1], n2 = st.node[2], n3 = st.node[3];
         const double c0 = n0.x, c1 = n0.y, c2c = n1.x, ih0 = n2.x, ih1 = n2.y, ih2 = n3.x;
-        double Tz[P][O], acc[P][O];
-        double v[P], x2[P], tx[P], tx_prev[P], val[P];
+        double Tz[P][NTZ], Tyk[P][TYKEEP ? O : 1], acc[P][O];
+        double v[P], w[P], x2[P], w2[P], tx[P], tx_prev[P], val[P];
 #pragma unroll
         for (int p = 0; p < P; ++p) {
             const bool ok = st.idx[p * 32 + lane] != kInvalidSlotE;
@@ -225,49 +163,83 @@ bin_eval3d_pipe_kernel(const TreeView tv, const double *__restrict__ x, double *
             const double pz = ok ? st.pts[2 * TILE + p * 32 + lane] : c2c;
             const double u = __dmul_rn(__dsub_rn(px, c0), ih0);
             v[p] = __dmul_rn(__dsub_rn(py, c1), ih1);
-            const double w = __dmul_rn(__dsub_rn(pz, c2c), ih2);
-            cheb_T<O>(w, Tz[p]);
+            w[p] = __dmul_rn(__dsub_rn(pz, c2c), ih2);
+            if constexpr (TZFLY)
+                w2[p] = __dadd_rn(w[p], w[p]);
+            else
+                cheb_T<O>(w[p], Tz[p]);
+            if constexpr (TYKEEP)
+                cheb_T<O>(v[p], Tyk[p]);
             x2[p] = __dadd_rn(u, u);
-            tx_prev[p] = 1.0;
-            tx[p] = u;
+            tx_prev[p] = u; // T_{-1} = T_1
+            tx[p] = 1.0;
             val[p] = 0.0;
         }
 #pragma unroll 1
         for (int i = 0; i < O; ++i) {
             const double2 *cc = st.coeff + i * (O * O / 2);
+            // acc[p][r] = sum_k C_i(r,k) Tz[p][k]: row chains in k order; the k = 0 product is C_i(r,0) itself
+            double tk[P], tkm[P];
 #pragma unroll
-            for (int k = 0; k < O; ++k) {
+            for (int k = 1; k < O; ++k) {
+#pragma unroll
+                for (int p = 0; p < P; ++p) {
+                    if constexpr (TZFLY) {
+                        if (k == 1) {
+                            tkm[p] = 1.0;
+                            tk[p] = w[p];
+                        } else {
+                            const double tn = __fma_rn(w2[p], tk[p], -tkm[p]);
+                            tkm[p] = tk[p];
+                            tk[p] = tn;
+                        }
+                    } else {
+                        tk[p] = Tz[p][k];
+                    }
+                }
 #pragma unroll
                 for (int r = 0; r < O; r += 2) {
-                    const double2 c = cc[(k * O + r) / 2];
+                    double2 c = cc[(k * O + r) / 2];
+                    if (EXP == 1) { // timing experiment: no shared-memory traffic in the slab loop
+                        c = make_double2(x2[0], x2[1]);
+                        asm volatile("" : "+d"(c.x), "+d"(c.y));
+                    }
+                    if (k == 1) {
+                        double2 cz = cc[r / 2];
+                        if (EXP == 1) {
+                            cz = make_double2(x2[1], x2[0]);
+                            asm volatile("" : "+d"(cz.x), "+d"(cz.y));
+                        }
 #pragma unroll
-                    for (int p = 0; p < P; ++p) {
-                        if (k == 0) {
-                            acc[p][r] = __dmul_rn(c.x, Tz[p][0]);
-                            acc[p][r + 1] = __dmul_rn(c.y, Tz[p][0]);
-                        } else {
-                            acc[p][r] = __fma_rn(c.x, Tz[p][k], acc[p][r]);
-                            acc[p][r + 1] = __fma_rn(c.y, Tz[p][k], acc[p][r + 1]);
+                        for (int p = 0; p < P; ++p) {
+                            acc[p][r] = __fma_rn(c.x, tk[p], cz.x);
+                            acc[p][r + 1] = __fma_rn(c.y, tk[p], cz.y);
+                        }
+                    } else {
+#pragma unroll
+                        for (int p = 0; p < P; ++p) {
+                            acc[p][r] = __fma_rn(c.x, tk[p], acc[p][r]);
+                            acc[p][r + 1] = __fma_rn(c.y, tk[p], acc[p][r + 1]);
                         }
                     }
                 }
             }
 #pragma unroll
             for (int p = 0; p < P; ++p) {
-                double Ty[O];
-                cheb_T<O>(v[p], Ty);
-                const double d = dot_packets<O>(Ty, acc[p]);
-                double ti;
-                if (i == 0) {
-                    ti = 1.0;
-                } else if (i == 1) {
-                    ti = tx[p];
+                double d;
+                if constexpr (TYKEEP) {
+                    d = dot_packets_one<O>(Tyk[p], acc[p]);
                 } else {
-                    ti = __fma_rn(x2[p], tx[p], -tx_prev[p]);
-                    tx_prev[p] = tx[p];
-                    tx[p] = ti;
+                    double vv = v[p];
+                    asm volatile("" : "+d"(vv)); // opaque per slab: T(y) is rebuilt here, not hoisted and kept live
+                    double Ty[O];
+                    cheb_T<O>(vv, Ty);
+                    d = dot_packets_one<O>(Ty, acc[p]);
                 }
-                val[p] = __fma_rn(ti, d, val[p]);
+                val[p] = __fma_rn(tx[p], d, val[p]);
+                const double tn = __fma_rn(x2[p], tx[p], -tx_prev[p]);
+                tx_prev[p] = tx[p];
+                tx[p] = tn;
             }
         }
 #pragma unroll
@@ -280,11 +252,19 @@ bin_eval3d_pipe_kernel(const TreeView tv, const double *__restrict__ x, double *
     cp_async_wait<0>();
 }
 
-template <int O, int P, int WARPS>
-static int launch_pipe(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
-    auto kern = bin_eval3d_pipe_kernel<O, P, WARPS>;
-    const size_t smem = sizeof(PipeStage<O, P>) * 2 * WARPS;
-    static bool configured = false;
+// ------------------------------------------------------------------------------------------ host side
+struct K4Variant {
+    int order, P, warps;
+    bool tzfly, tykeep;
+    int (*launch)(const DeviceTree &, const BinWorkspace &, const double *, double *, cudaStream_t);
+};
+
+template <int O, int P, int WARPS, bool TZFLY, bool TYKEEP, int EXP = 0>
+static int launch_k4(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
+    auto kern = bin_eval3d_kernel<O, P, WARPS, TZFLY, TYKEEP, EXP>;
+    constexpr size_t smem = sizeof(PipeStage<O, P>) * 2 * WARPS;
+    static_assert(smem <= 227 * 1024, "pipeline stages exceed the shared memory of an SM");
+    static bool configured = false; // per instantiation
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess)
@@ -295,70 +275,56 @@ static int launch_pipe(const DeviceTree &dt, const BinWorkspace &ws, const doubl
     return (int)cudaGetLastError();
 }
 
-template <int O, int P, bool SMEM, int WARPS>
-static int launch_variant(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res,
-                          cudaStream_t st) {
-    auto kern = bin_eval3d_kernel<O, P, SMEM, WARPS>;
-    const size_t smem = SMEM ? (size_t)WARPS * O * O * O * sizeof(double) : 0;
-    static bool configured = false; // per instantiation
-    if (!configured) {
-        if (smem > 48 * 1024) {
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-            if (e != cudaSuccess)
-                return (int)e;
-        }
-        configured = true;
-    }
-    int per_sm = 1;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS * 32, smem);
-    if (per_sm < 1)
-        per_sm = 1;
-    kern<<<dt.sm_count * per_sm, WARPS * 32, smem, st>>>(dt.view, d_x, d_res, ws.perm, ws.tile_leaf, ws.n_tiles);
-    return (int)cudaGetLastError();
+#define BZ_K4(O_, P_, W_, F_, Y_) {O_, P_, W_, F_, Y_, launch_k4<O_, P_, W_, F_, Y_>}
+// first entry of an order = its default
+static const K4Variant kVariants[] = {
+    BZ_K4(6, 4, 8, false, true),   BZ_K4(6, 4, 12, false, true),  BZ_K4(6, 4, 16, false, false),
+    BZ_K4(8, 4, 8, false, true),   BZ_K4(8, 4, 8, false, false),  BZ_K4(8, 3, 12, false, false),
+    BZ_K4(8, 3, 12, false, true),  BZ_K4(8, 4, 12, true, false),  BZ_K4(8, 2, 16, false, false),
+    BZ_K4(8, 2, 16, false, true),  BZ_K4(8, 3, 8, false, true),
+    BZ_K4(10, 2, 8, false, true),  BZ_K4(10, 3, 8, false, false), BZ_K4(10, 4, 8, true, false),
+    BZ_K4(12, 2, 4, false, true),  BZ_K4(12, 3, 4, false, false), BZ_K4(12, 4, 4, true, false),
+    BZ_K4(14, 2, 4, false, true),  BZ_K4(14, 3, 4, true, false),
+    BZ_K4(16, 2, 2, false, true),  BZ_K4(16, 2, 3, false, false),
+#ifdef BZ_EXPERIMENTS // timing experiments with WRONG results: P = 91 / 92 select them
+    {8, 91, 8, false, true, launch_k4<8, 4, 8, false, true, 1>}, {8, 92, 8, false, true, launch_k4<8, 4, 8, false, true, 2>},
+    {8, 91, 12, false, false, launch_k4<8, 3, 12, false, false, 1>}, {8, 92, 12, false, false, launch_k4<8, 3, 12, false, false, 2>},
+#endif
+};
+#undef BZ_K4
+
+static const K4Variant *find_variant(int order, int P, int warps, int tzfly, int tykeep) {
+    for (const K4Variant &v : kVariants)
+        if (v.order == order && (P < 0 || (v.P == P && v.warps == warps && v.tzfly == (tzfly != 0) && v.tykeep == (tykeep != 0))))
+            return &v;
+    return nullptr;
 }
 
-// Default points per lane for a 3D tree of this order (what the registers allow, see header comment).
-int bin_eval_default_P(int order) { return order <= 8 ? 4 : 2; }
-bool bin_eval_default_smem(int order) { return order <= 10; }
-
-// WARPS per CTA: the SMEM variant needs WARPS * 8 * O^3 bytes of shared memory (<= 227 KB)
-#define BZ_K4(O_, P_, S_, W_)                                                                                          \
-    if (order == O_ && P == P_ && smem == S_)                                                                          \
-        return launch_variant<O_, P_, S_, W_>(dt, ws, d_x, d_res, st);
+// Variant for a 3D tree of this order: the default, or BAOBZI_B200_K4="P,warps,tzfly,tykeep" (benchmarks).
+// Returns the points per lane (tile = 32 * P slots) and an opaque index for launch_bin_eval3d; -1 if unsupported.
+int bin_eval_select(int order, int *P) {
+    const K4Variant *v = find_variant(order, -1, 0, 0, 0);
+    if (const char *e = std::getenv("BAOBZI_B200_K4")) {
+        int p = 0, w = 0, f = 0, y = 0;
+        if (std::sscanf(e, "%d,%d,%d,%d", &p, &w, &f, &y) == 4) {
+            const K4Variant *o = find_variant(order, p, w, f, y);
+            if (o)
+                v = o;
+            else
+                std::fprintf(stderr, "baobzi: BAOBZI_B200_K4=%s is not built for order %d, using the default\n", e, order);
+        }
+    }
+    if (!v)
+        return -1;
+    *P = v->P > 90 ? (v->warps == 12 ? 3 : 4) : v->P;
+    return (int)(v - kVariants);
+}
 
 int launch_bin_eval3d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
-    const int order = dt.view.order, P = ws.P;
-    const bool smem = ws.smem_coeffs;
-    if (ws.pipelined) {
-        if (order == 6 && P == 4) return launch_pipe<6, 4, 8>(dt, ws, d_x, d_res, st);
-        if (order == 8 && P == 4) return launch_pipe<8, 4, 8>(dt, ws, d_x, d_res, st);
-        if (order == 8 && P == 2) return launch_pipe<8, 2, 8>(dt, ws, d_x, d_res, st);
-        if (order == 10 && P == 2) return launch_pipe<10, 2, 8>(dt, ws, d_x, d_res, st);
-        if (order == 12 && P == 2) return launch_pipe<12, 2, 4>(dt, ws, d_x, d_res, st);
-        if (order == 14 && P == 2) return launch_pipe<14, 2, 4>(dt, ws, d_x, d_res, st);
-        if (order == 16 && P == 2) return launch_pipe<16, 2, 2>(dt, ws, d_x, d_res, st);
-    }
-    BZ_K4(6, 4, true, 8) BZ_K4(6, 4, false, 8) BZ_K4(6, 2, true, 8) BZ_K4(6, 2, false, 8)
-    BZ_K4(8, 4, true, 8) BZ_K4(8, 4, false, 8) BZ_K4(8, 2, true, 8) BZ_K4(8, 2, false, 8)
-    BZ_K4(10, 2, true, 8) BZ_K4(10, 2, false, 8) BZ_K4(10, 4, false, 4)
-    BZ_K4(12, 2, true, 8) BZ_K4(12, 2, false, 8) BZ_K4(12, 1, false, 8)
-    BZ_K4(14, 2, true, 8) BZ_K4(14, 2, false, 8) BZ_K4(14, 1, false, 8)
-    BZ_K4(16, 2, true, 4) BZ_K4(16, 2, false, 8) BZ_K4(16, 1, false, 8)
-    return (int)cudaErrorInvalidValue;
-}
-
-bool bin_eval_pipe_exists(int order, int P) {
-    return (order == 6 && P == 4) || (order == 8 && (P == 4 || P == 2)) || (order >= 10 && order <= 16 && P == 2);
-}
-
-bool bin_eval_variant_exists(int order, int P, bool smem) {
-    static const int table[][3] = {{6, 4, 1}, {6, 4, 0}, {6, 2, 1}, {6, 2, 0}, {8, 4, 1}, {8, 4, 0}, {8, 2, 1}, {8, 2, 0},
-                                   {10, 2, 1}, {10, 2, 0}, {10, 4, 0}, {12, 2, 1}, {12, 2, 0}, {12, 1, 0}, {14, 2, 1},
-                                   {14, 2, 0}, {14, 1, 0}, {16, 2, 1}, {16, 2, 0}, {16, 1, 0}};
-    for (auto &e : table)
-        if (e[0] == order && e[1] == P && (e[2] != 0) == smem)
-            return true;
-    return false;
+    if (ws.variant < 0 || ws.variant >= (int)(sizeof(kVariants) / sizeof(kVariants[0])) ||
+        kVariants[ws.variant].order != dt.view.order)
+        return (int)cudaErrorInvalidValue;
+    return kVariants[ws.variant].launch(dt, ws, d_x, d_res, st);
 }
 
 } // namespace bz

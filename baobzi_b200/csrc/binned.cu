@@ -23,15 +23,14 @@
 
 #include "lookup.cuh"
 
+#include <cooperative_groups.h>
+
 namespace bz {
 
 constexpr uint32_t kInvalidSlot = 0xFFFFFFFFu;
 constexpr int kBinThreads = 256;
 
-int bin_eval_default_P(int order);
-bool bin_eval_default_smem(int order);
-bool bin_eval_variant_exists(int order, int P, bool smem);
-bool bin_eval_pipe_exists(int order, int P);
+int bin_eval_select(int order, int *P);
 int launch_bin_eval3d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------------ K1
@@ -56,77 +55,136 @@ bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__res
     }
 }
 
-// ------------------------------------------------------------------------------------------ K1/K3, privatised
-// Same job as K1/K3 with one shared-memory atomic per point instead of two global ones: every CTA owns a
-// contiguous range of the chunk, histograms it in shared memory (the atomic's return value is the point's rank
-// inside (CTA, leaf)), then reserves its share of every leaf with ONE global atomic per non-empty (CTA, leaf).
-// K3 becomes atomic-free: slot = start[leaf] + base[CTA][leaf] + rank.  Used when the histogram fits in smem.
-template <int DIM>
-__global__ void __launch_bounds__(kBinThreads)
-bin_lookup2_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
-                   uint32_t *__restrict__ key, uint32_t *__restrict__ rank, uint32_t *__restrict__ count, int cshift,
-                   uint32_t *__restrict__ cta_base, uint32_t n) {
-    extern __shared__ uint32_t hist[];
-    const uint32_t nl = tv.n_leaves;
-    for (uint32_t l = threadIdx.x; l < nl; l += blockDim.x)
-        hist[l] = 0;
-    __syncthreads();
-    const uint32_t lo = (uint32_t)(((uint64_t)blockIdx.x * n) / gridDim.x);
-    const uint32_t hi = (uint32_t)(((uint64_t)(blockIdx.x + 1) * n) / gridDim.x);
-    // two points per thread per trip: the lookup is a chain of dependent L2 loads, so independent chains are
-    // what keeps the memory system busy
-    for (uint32_t i0 = lo + threadIdx.x; i0 < hi; i0 += 2 * blockDim.x) {
-        const uint32_t i1 = i0 + blockDim.x;
-        const bool has1 = i1 < hi;
-        double p0[DIM], p1[DIM];
-        load_point_keep<DIM>(x, i0, p0);
-        load_point_keep<DIM>(x, has1 ? i1 : i0, p1);
-        const bool out0 = outside<DIM>(tv, p0), out1 = outside<DIM>(tv, p1) || !has1;
-        uint32_t leaf0 = kNotLeaf, leaf1 = kNotLeaf;
-        if (!out0)
-            leaf0 = locate_leaf<DIM>(tv, p0);
-        if (!out1)
-            leaf1 = locate_leaf<DIM>(tv, p1);
-        if (out0)
-            res[i0] = __longlong_as_double(0x7ff8000000000000ll);
-        else
-            rank[i0] = atomicAdd(hist + leaf0, 1u);
-        key[i0] = leaf0;
-        if (has1) {
-            if (outside<DIM>(tv, p1))
-                res[i1] = __longlong_as_double(0x7ff8000000000000ll);
-            else
-                rank[i1] = atomicAdd(hist + leaf1, 1u);
-            key[i1] = leaf1;
-        }
-    }
-    __syncthreads();
-    for (uint32_t l = threadIdx.x; l < nl; l += blockDim.x) {
-        const uint32_t h = hist[l];
-        if (h)
-            cta_base[(size_t)blockIdx.x * nl + l] = atomicAdd(count + ((size_t)l << cshift), h);
-    }
-}
+// ------------------------------------------------------------------------------------------ fused sort
+// K1 + K2 + K2b + K3 as ONE cooperative kernel (used whenever the per-leaf histogram fits in shared memory).
+// Every CTA owns a contiguous range of the chunk.
+//   phase A  lookup: leaf rank per point, histogram of the range in shared memory, key[i] = leaf; then one global
+//            atomic per non-empty (CTA, leaf) reserves the CTA's share of the leaf: base = atomicAdd(count[leaf], h)
+//   -- grid barrier --
+//   phase B  every CTA scans the (now complete) histogram itself -- a few thousand counters out of L2, cheaper than
+//            a single-CTA scan kernel plus a launch; the leaves are dealt round-robin to the CTAs for the padding
+//            slots and the tile descriptors.  tbl[leaf] = start[leaf] + base[leaf], and the scatter is
+//            perm[tbl[leaf]++] = i with a shared-memory atomic: no rank array, no global atomics, no table gathers.
+// HBM traffic: the points once (8*DIM B) + perm (4 B); key[] (4 B written, 4 B read) lives in L2.
+constexpr int kSortThreads = 512;
+constexpr size_t kFusedSortMaxSmem = 160 * 1024;
+constexpr int kSortPts = 4; // independent lookups in flight per thread (the lookup is latency bound, not issue bound)
 
-__global__ void __launch_bounds__(kBinThreads)
-bin_scatter2_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict__ rank,
-                    const uint32_t *__restrict__ start, const uint32_t *__restrict__ cta_base, uint32_t n_leaves,
-                    uint32_t *__restrict__ perm, uint32_t n) {
+template <int DIM>
+__global__ void __launch_bounds__(kSortThreads)
+bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                      uint32_t *__restrict__ key, uint32_t *__restrict__ count, uint32_t *__restrict__ count_next,
+                      int cshift, uint32_t TILE, uint32_t *__restrict__ perm, uint32_t *__restrict__ tile_leaf,
+                      uint2 *__restrict__ tile_info, uint32_t *__restrict__ n_tiles, uint32_t n) {
+    extern __shared__ uint32_t tbl[]; // [n_leaves] histogram -> base -> next free slot
+    __shared__ uint32_t warp_sums[kSortThreads / 32];
+    const uint32_t nl = tv.n_leaves;
+    const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+    for (uint32_t l = tid; l < nl; l += nthr)
+        tbl[l] = 0;
+    __syncthreads();
     const uint32_t lo = (uint32_t)(((uint64_t)blockIdx.x * n) / gridDim.x);
     const uint32_t hi = (uint32_t)(((uint64_t)(blockIdx.x + 1) * n) / gridDim.x);
-    const uint32_t *base = cta_base + (size_t)blockIdx.x * n_leaves;
-    for (uint32_t i0 = lo + threadIdx.x; i0 < hi; i0 += 4 * blockDim.x) {
-        uint32_t k[4], r[4];
+
+    // ---- phase A
+    for (uint32_t i0 = lo + tid; i0 < hi; i0 += kSortPts * nthr) {
+        double p[kSortPts][DIM];
+        bool have[kSortPts];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const uint32_t i = i0 + u * blockDim.x;
+        for (int u = 0; u < kSortPts; ++u) {
+            const uint32_t i = i0 + u * nthr;
+            have[u] = i < hi;
+            load_point_keep<DIM>(x, have[u] ? i : i0, p[u]); // default cache policy: K4 gathers these again
+        }
+        uint32_t leaf[kSortPts];
+#pragma unroll
+        for (int u = 0; u < kSortPts; ++u)
+            leaf[u] = (!have[u] || outside<DIM>(tv, p[u])) ? kNotLeaf : locate_leaf<DIM>(tv, p[u]);
+#pragma unroll
+        for (int u = 0; u < kSortPts; ++u) {
+            if (!have[u])
+                continue;
+            const uint32_t i = i0 + u * nthr;
+            key[i] = leaf[u];
+            if (leaf[u] == kNotLeaf)
+                res[i] = __longlong_as_double(0x7ff8000000000000ll);
+            else
+                atomicAdd(tbl + leaf[u], 1u);
+        }
+    }
+    __syncthreads();
+    for (uint32_t l = tid; l < nl; l += nthr) {
+        const uint32_t h = tbl[l];
+        tbl[l] = h ? atomicAdd(count + ((size_t)l << cshift), h) : 0u;
+    }
+    __threadfence();
+    cooperative_groups::this_grid().sync();
+
+    // ---- phase B: padded exclusive scan of the global histogram, thread t owns leaves [t*per, (t+1)*per)
+    const uint32_t per = (nl + nthr - 1) / nthr;
+    const uint32_t l0 = min(tid * per, nl), l1 = min(l0 + per, nl);
+    uint32_t mine = 0;
+    for (uint32_t l = l0; l < l1; ++l) {
+        const uint32_t c = __ldcg(count + ((size_t)l << cshift));
+        mine += (c + TILE - 1) / TILE * TILE;
+    }
+    const uint32_t lane = tid & 31, warp = tid >> 5;
+    uint32_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o)
+            incl += t;
+    }
+    if (lane == 31)
+        warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = lane < kSortThreads / 32 ? warp_sums[lane] : 0u;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o)
+                w += t;
+        }
+        if (lane < kSortThreads / 32)
+            warp_sums[lane] = w;
+    }
+    __syncthreads();
+    uint32_t start = (warp ? warp_sums[warp - 1] : 0u) + incl - mine;
+    for (uint32_t l = l0; l < l1; ++l) {
+        const uint32_t c = __ldcg(count + ((size_t)l << cshift));
+        const uint32_t padded = (c + TILE - 1) / TILE * TILE;
+        if (l % gridDim.x == blockIdx.x) { // this CTA's leaves: padding slots, tile descriptors, counter reset
+            for (uint32_t s = start + c; s < start + padded; ++s)
+                perm[s] = kInvalidSlot;
+            const uint32_t node = __ldg(tv.leaf_node + l);
+            const uint2 info = make_uint2(node, load_head(tv.nodes, node).coeff16);
+            for (uint32_t t = start / TILE; t < (start + padded) / TILE; ++t) {
+                tile_leaf[t] = l;
+                tile_info[t] = info;
+            }
+            count_next[(size_t)l << cshift] = 0; // the buffer the NEXT chunk histograms into
+        }
+        tbl[l] += start;
+        start += padded;
+    }
+    if (blockIdx.x == 0 && tid == nthr - 1)
+        *n_tiles = (warp_sums[kSortThreads / 32 - 1]) / TILE;
+    __syncthreads();
+
+    // ---- scatter
+    for (uint32_t i0 = lo + tid; i0 < hi; i0 += kSortPts * nthr) {
+        uint32_t k[kSortPts];
+#pragma unroll
+        for (int u = 0; u < kSortPts; ++u) {
+            const uint32_t i = i0 + u * nthr;
             k[u] = i < hi ? __ldcs(key + i) : kNotLeaf;
-            r[u] = i < hi ? __ldcs(rank + i) : 0u;
         }
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < kSortPts; ++u)
             if (k[u] != kNotLeaf)
-                perm[__ldg(start + k[u]) + __ldg(base + k[u]) + r[u]] = i0 + u * blockDim.x;
+                perm[atomicAdd(tbl + k[u], 1u)] = i0 + u * nthr;
     }
 }
 
@@ -226,19 +284,11 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         chunk = 1;
     if (chunk > 0x7FFFFFFFll)
         chunk = 0x7FFFFFFFll;
-    int P = bin_eval_default_P(dt.view.order);
-    bool smem = bin_eval_default_smem(dt.view.order);
-    if (const char *e = std::getenv("BAOBZI_B200_P")) // tuning overrides (benchmarks)
-        if (bin_eval_variant_exists(dt.view.order, std::atoi(e), smem))
-            P = std::atoi(e);
-    if (const char *e = std::getenv("BAOBZI_B200_SMEM"))
-        if (bin_eval_variant_exists(dt.view.order, P, std::atoi(e) != 0))
-            smem = std::atoi(e) != 0;
+    int P = 0;
+    ws.variant = bin_eval_select(dt.view.order, &P);
+    if (ws.variant < 0)
+        return (int)cudaErrorInvalidValue;
     ws.P = P;
-    ws.smem_coeffs = smem;
-    ws.pipelined = bin_eval_pipe_exists(dt.view.order, P);
-    if (const char *e = std::getenv("BAOBZI_B200_PIPE"))
-        ws.pipelined = ws.pipelined && std::atoi(e) != 0;
     const int64_t tile = 32 * P;
     const int64_t nl = dt.view.n_leaves;
     ws.perm_capacity = chunk + nl * tile;
@@ -248,18 +298,24 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     while (ws.cshift < 5 && ((nl + 1) << (ws.cshift + 1)) <= (1 << 20))
         ws.cshift++;
     const size_t cwords = (size_t)(nl + 1) << ws.cshift;
-    ws.privatized = (size_t)nl * sizeof(uint32_t) <= 160 * 1024;
-    if (const char *e = std::getenv("BAOBZI_B200_PRIVATE"))
-        ws.privatized = ws.privatized && std::atoi(e) != 0;
-    ws.sort_ctas = dt.sm_count * 4;
-    if (const char *e = std::getenv("BAOBZI_B200_SORT_CTAS"))
-        if (std::atoi(e) > 0)
-            ws.sort_ctas = dt.sm_count * std::atoi(e);
+    ws.fused = (size_t)nl * sizeof(uint32_t) <= kFusedSortMaxSmem;
+    if (const char *e = std::getenv("BAOBZI_B200_FUSED_SORT"))
+        ws.fused = ws.fused && std::atoi(e) != 0;
+    ws.sort_ctas = 0;
+    if (ws.fused) { // cooperative launch: the grid is what is co-resident
+        const size_t smem = (size_t)nl * sizeof(uint32_t);
+        cudaFuncSetAttribute(bin_sort_fused_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
+        int per_sm = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<3>, kSortThreads, smem);
+        int want = 4;
+        if (const char *e = std::getenv("BAOBZI_B200_SORT_CTAS"))
+            if (std::atoi(e) > 0)
+                want = std::atoi(e);
+        per_sm = per_sm < want ? per_sm : want;
+        ws.sort_ctas = dt.sm_count * per_sm;
+        ws.fused = per_sm >= 1;
+    }
     cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
-    if (e == cudaSuccess && ws.privatized)
-        e = cudaMalloc((void **)&ws.rank, sizeof(uint32_t) * chunk);
-    if (e == cudaSuccess && ws.privatized)
-        e = cudaMalloc((void **)&ws.cta_base, sizeof(uint32_t) * (size_t)ws.sort_ctas * (nl + 1));
     if (e == cudaSuccess)
         e = cudaMalloc((void **)&ws.perm, sizeof(uint32_t) * ws.perm_capacity);
     if (e == cudaSuccess)
@@ -278,6 +334,8 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         e = cudaMalloc((void **)&ws.tile_info, sizeof(uint2) * ws.tile_capacity);
     if (e == cudaSuccess)
         e = cudaMemset(ws.count, 0, sizeof(uint32_t) * cwords);
+    if (e == cudaSuccess)
+        e = cudaMemset(ws.cursor, 0, sizeof(uint32_t) * cwords);
     if (e != cudaSuccess) {
         free_workspace(ws);
         return (int)e;
@@ -295,8 +353,6 @@ void free_workspace(BinWorkspace &ws) {
     cudaFree(ws.start);
     cudaFree(ws.tile_leaf);
     cudaFree(ws.n_tiles);
-    cudaFree(ws.rank);
-    cudaFree(ws.cta_base);
     cudaFree(ws.tile_info);
     ws = BinWorkspace();
 }
@@ -315,31 +371,38 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
             e = pf->get();
         cudaEventRecord(ev[0], st);
     }
-    const size_t hist_bytes = (size_t)tv.n_leaves * sizeof(uint32_t);
-    if (ws.privatized) {
-        static bool configured = false;
-        if (!configured && hist_bytes > 48 * 1024) {
-            cudaFuncSetAttribute(bin_lookup2_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-            configured = true;
+    int rc_sort = 0;
+    if (ws.fused) {
+        uint32_t grid = (uint32_t)ws.sort_ctas;
+        const uint32_t useful = (n + kSortThreads * kSortPts - 1) / (kSortThreads * kSortPts);
+        grid = grid < useful ? grid : (useful ? useful : 1u);
+        uint32_t *cur = ws.flip ? ws.cursor : ws.count, *next = ws.flip ? ws.count : ws.cursor;
+        ws.flip = !ws.flip;
+        TreeView tvv = tv;
+        int cshift = ws.cshift;
+        uint32_t tile = TILE, nn = n;
+        void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
+                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn};
+        rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3>, dim3(grid), dim3(kSortThreads), args,
+                                                   (size_t)tv.n_leaves * sizeof(uint32_t), st);
+        if (pf) { // the three classic stages are one launch here: all of it is booked under "lookup"
+            cudaEventRecord(ev[1], st);
+            cudaEventRecord(ev[2], st);
+            cudaEventRecord(ev[3], st);
         }
-        bin_lookup2_kernel<3><<<ws.sort_ctas, kBinThreads, hist_bytes, st>>>(tv, d_x, d_res, ws.key, ws.rank, ws.count,
-                                                                           ws.cshift, ws.cta_base, n);
     } else {
         bin_lookup_kernel<3><<<g1, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.key, ws.count, ws.cshift, n);
-    }
-    if (pf)
-        cudaEventRecord(ev[1], st);
-    bin_scan_kernel<<<1, 1024, 0, st>>>(TILE, tv.n_leaves, ws.count, ws.cursor, ws.cshift, ws.cnt, ws.start, ws.n_tiles);
-    bin_fill_kernel<<<(tv.n_leaves * 32 + kBinThreads - 1) / kBinThreads, kBinThreads, 0, st>>>(
-        tv, TILE, tv.n_leaves, ws.cnt, ws.start, ws.tile_leaf, ws.tile_info, ws.perm);
-    if (pf)
-        cudaEventRecord(ev[2], st);
-    if (ws.privatized)
-        bin_scatter2_kernel<<<ws.sort_ctas, kBinThreads, 0, st>>>(ws.key, ws.rank, ws.start, ws.cta_base, tv.n_leaves, ws.perm, n);
-    else
+        if (pf)
+            cudaEventRecord(ev[1], st);
+        bin_scan_kernel<<<1, 1024, 0, st>>>(TILE, tv.n_leaves, ws.count, ws.cursor, ws.cshift, ws.cnt, ws.start, ws.n_tiles);
+        bin_fill_kernel<<<(tv.n_leaves * 32 + kBinThreads - 1) / kBinThreads, kBinThreads, 0, st>>>(
+            tv, TILE, tv.n_leaves, ws.cnt, ws.start, ws.tile_leaf, ws.tile_info, ws.perm);
+        if (pf)
+            cudaEventRecord(ev[2], st);
         bin_scatter_kernel<<<g1, kBinThreads, 0, st>>>(ws.key, ws.start, ws.cursor, ws.cshift, ws.perm, n);
-    if (pf)
-        cudaEventRecord(ev[3], st);
+        if (pf)
+            cudaEventRecord(ev[3], st);
+    }
     int rc = launch_bin_eval3d(dt, ws, d_x, d_res, st);
     if (pf) {
         cudaEventRecord(ev[4], st);
@@ -348,7 +411,7 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         pf->spans.push_back({kStageScatter, ev[2], ev[3], (int64_t)n});
         pf->spans.push_back({kStageEval, ev[3], ev[4], (int64_t)n});
     }
-    return rc ? rc : (int)cudaGetLastError();
+    return rc_sort ? rc_sort : rc ? rc : (int)cudaGetLastError();
 }
 
 int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
@@ -359,7 +422,7 @@ int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x
         return (int)cudaErrorInvalidValue;
     int rc = launch_chunk_3d(dt, ws, d_x, d_res, (uint32_t)n, stream);
     if (launches)
-        *launches += 5;
+        *launches += ws.fused ? 2 : 5;
     return rc;
 }
 

@@ -55,7 +55,7 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
 
     std::vector<NodeRec> recs(nn);
     std::vector<uint32_t> leaf_node;
-    std::vector<uint32_t> bin_root(nb);
+    std::vector<uint32_t> bin_root(nb), bin_leaf(nb, kNotLeaf);
     for (size_t s = 0; s < nb; ++s) {
         const uint32_t b = h.subtree_begin[s], e = h.subtree_begin[s + 1];
         bin_root[s] = b;
@@ -72,6 +72,8 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
                 const uint64_t off = aligned ? h.coeff_offset[g] : new_off[g];
                 r.coeff16 = (uint32_t)(off / 2);
                 r.leaf_rank = (uint32_t)leaf_node.size();
+                if (g == b)
+                    bin_leaf[s] = r.leaf_rank; // undivided grid cell: the lookup ends at the bin table
                 leaf_node.push_back(g);
             } else {
                 r.child0 = b + h.first_child[g]; // subtree-local -> global
@@ -81,11 +83,12 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
         }
     }
 
-    // one allocation, 256-byte aligned sections: nodes | bin_root | leaf_node | coeffs (+ 32 KB of zero slack so
-    // that vector loads near the end of the last block never leave the allocation)
+    // one allocation, 256-byte aligned sections: nodes | bin_root | bin_leaf | leaf_node | coeffs (+ 32 KB of zero
+    // slack so that vector loads near the end of the last block never leave the allocation)
     const size_t off_nodes = 0;
     const size_t off_bins = align_up(off_nodes + nn * sizeof(NodeRec), 256);
-    const size_t off_leaf = align_up(off_bins + nb * sizeof(uint32_t), 256);
+    const size_t off_binl = align_up(off_bins + nb * sizeof(uint32_t), 256);
+    const size_t off_leaf = align_up(off_binl + nb * sizeof(uint32_t), 256);
     const size_t off_coef = align_up(off_leaf + leaf_node.size() * sizeof(uint32_t), 256);
     const size_t total = align_up(off_coef + coeffs->size() * sizeof(double) + 32768, 256);
 
@@ -103,6 +106,8 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
         e = cudaMemcpy(base + off_nodes, recs.data(), nn * sizeof(NodeRec), cudaMemcpyHostToDevice);
     if (e == cudaSuccess)
         e = cudaMemcpy(base + off_bins, bin_root.data(), nb * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess)
+        e = cudaMemcpy(base + off_binl, bin_leaf.data(), nb * sizeof(uint32_t), cudaMemcpyHostToDevice);
     if (e == cudaSuccess && !leaf_node.empty())
         e = cudaMemcpy(base + off_leaf, leaf_node.data(), leaf_node.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
     if (e == cudaSuccess && !coeffs->empty())
@@ -132,6 +137,7 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
     v.out_dim = h.output_dim;
     v.nodes = reinterpret_cast<const NodeRec *>(base + off_nodes);
     v.bin_root = reinterpret_cast<const uint32_t *>(base + off_bins);
+    v.bin_leaf = reinterpret_cast<const uint32_t *>(base + off_binl);
     v.leaf_node = reinterpret_cast<const uint32_t *>(base + off_leaf);
     v.coeffs = reinterpret_cast<const double *>(base + off_coef);
     return 0;

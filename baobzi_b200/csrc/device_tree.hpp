@@ -13,6 +13,8 @@
 //                            request, an internal-node visit one 32-byte sector.
 //   coeffs   [n_coeffs] f64  the reference's coeffs_ (template.hpp:558), blocks 16-byte aligned, layout
 //                            per leaf unchanged
+//   bin_leaf [n_bins]  u32   dense leaf rank of an undivided grid cell (its root is a leaf), kNotLeaf otherwise:
+//                            for such cells the binned path's lookup is the floor transform plus ONE 4-byte load
 //   leaf_rank[n_nodes] u32   dense rank of a leaf among leaves in node order (kNotLeaf for internal
 //                            nodes) -- bin key of the binned path
 //   leaf_node[n_leaves] u32  inverse of leaf_rank
@@ -46,6 +48,7 @@ struct TreeView {
     int dim, order;
     uint32_t n_bins, n_nodes, n_leaves, out_dim;
     const uint32_t *bin_root;
+    const uint32_t *bin_leaf; // [n_bins] dense leaf rank when the cell's root is itself a leaf, else kNotLeaf
     const NodeRec *nodes;
     const double *coeffs;
     const uint32_t *leaf_node;
@@ -79,12 +82,11 @@ struct BinWorkspace {
     uint32_t *cursor = nullptr; // [n_leaves + 1]     per-leaf fill cursor of the scatter (cleared by the scan)
     uint32_t *cnt = nullptr;    // [n_leaves + 1]     dense copy of the histogram for the fill kernel
     int P = 2;                  // points per lane of the evaluation kernel (tile = 32 * P slots)
-    bool smem_coeffs = false;   // stage each tile's coefficient block in shared memory
-    bool pipelined = false;     // K4 variant with cp.async double buffering (bin_eval.cu)
-    bool privatized = false;    // K1/K3 with per-CTA shared-memory histograms (binned.cu)
-    int sort_ctas = 0;
-    uint32_t *rank = nullptr;     // [chunk] rank of a point inside its (CTA, leaf)
-    uint32_t *cta_base = nullptr; // [sort_ctas][n_leaves] first slot of (CTA, leaf) relative to start[leaf]
+    int variant = -1;           // which instantiation of the evaluation kernel (bin_eval.cu: bin_eval_select)
+    bool fused = false;         // lookup + scan + scatter as one cooperative kernel (binned.cu); count / cursor
+                                // are then the two histogram buffers used by alternate chunks
+    bool flip = false;          // which of the two the next chunk histograms into
+    int sort_ctas = 0;          // grid of the cooperative kernel (all CTAs co-resident)
     uint2 *tile_info = nullptr; // [max_tiles] {node, coefficient offset / 16 B} of each tile's leaf
     int cshift = 0;             // count[] / cursor[] entries are spread 2^cshift words apart so that atomics of
                                 // different leaves land in different L2 sectors / lines

@@ -84,8 +84,10 @@ __device__ __forceinline__ uint32_t locate(const TreeView &tv, const double (&x)
     return node;
 }
 
-// Same walk, but every step fetches the whole 64-byte record (both sectors of one line in a single round
-// trip) and only the dense leaf rank is returned: one dependent load fewer than locate() + load_tail().
+// Same walk, but only the dense leaf rank is returned.  Undivided grid cells (every cell of a tree whose fit
+// never refined past the grid, e.g. the 3D benchmark trees) are answered by the bin_leaf table alone; otherwise
+// every step fetches the whole 64-byte record (both sectors of one line in a single round trip): one dependent
+// load fewer than locate() + load_tail().
 template <int DIM>
 __device__ __forceinline__ uint32_t locate_leaf(const TreeView &tv, const double (&x)[DIM]) {
     int lin = 0, stride = 1;
@@ -97,6 +99,9 @@ __device__ __forceinline__ uint32_t locate_leaf(const TreeView &tv, const double
         lin += stride * b;
         stride *= tv.n_sub[j];
     }
+    const uint32_t direct = __ldg(tv.bin_leaf + lin); // undivided cell: done after one 4-byte load
+    if (direct != kNotLeaf)
+        return direct;
     uint32_t node = __ldg(tv.bin_root + lin);
     for (;;) {
         const double2 *p = reinterpret_cast<const double2 *>(tv.nodes + node);

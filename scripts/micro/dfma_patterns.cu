@@ -1,0 +1,182 @@
+// Microbenchmark: FP64 pipe throughput on sm_100a for the operand patterns the evaluation kernel can use.
+// build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o dfma_patterns dfma_patterns.cu
+#include <cstdio>
+#include <cuda_runtime.h>
+
+#define ITERS 4096
+
+// A: one fresh register operand (peak): v = fma(v, a, b), a from the uniform datapath, b reused
+template <int W>
+__global__ void __launch_bounds__(W * 32, 1) pat_a(double *out, double a, double b) {
+    double v[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) v[k] = threadIdx.x * 1e-3 + k;
+    for (int i = 0; i < ITERS; ++i) {
+#pragma unroll
+        for (int k = 0; k < 32; ++k) v[k] = __fma_rn(v[k], a, b);
+    }
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) s += v[k];
+    if (s == 1.2345) out[0] = s;
+}
+
+// B: acc[p][r] = fma(c[r], t[p], acc[p][r]), p innermost (c reused over p); c and t live in registers
+// MODE 0: p inner; 1: r inner (t reused); 2: c is warp-uniform from kernel parameters (uniform datapath)
+template <int W, int P, int MODE>
+__global__ void __launch_bounds__(W * 32, 1) pat_b(double *out, const double *in, double u0, double u1, double u2,
+                                                   double u3, double u4, double u5, double u6, double u7) {
+    double acc[P][8], c[8], t[P];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) c[r] = in[r] + (MODE == 2 ? 0.0 : threadIdx.x * 1e-9);
+    const double uu[8] = {u0, u1, u2, u3, u4, u5, u6, u7};
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+        t[p] = in[8 + p] + threadIdx.x * 1e-6;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) acc[p][r] = p + r;
+    }
+    for (int i = 0; i < ITERS; ++i) {
+        if (MODE == 1) {
+#pragma unroll
+            for (int p = 0; p < P; ++p)
+#pragma unroll
+                for (int r = 0; r < 8; ++r) acc[p][r] = __fma_rn(c[r], t[p], acc[p][r]);
+        } else {
+#pragma unroll
+            for (int r = 0; r < 8; ++r)
+#pragma unroll
+                for (int p = 0; p < P; ++p) acc[p][r] = __fma_rn(MODE == 2 ? uu[r] : c[r], t[p], acc[p][r]);
+        }
+    }
+    double s = 0;
+#pragma unroll
+    for (int p = 0; p < P; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) s += acc[p][r];
+    if (s == 1.2345) out[0] = s;
+}
+
+// F: the evaluation kernel's slab loop: coefficients are warp-uniform LDS.128 pairs out of shared memory.
+// MODE 0: used as loaded (vector register, reused over p); MODE 1: moved to the uniform datapath by REDUX.OR
+__device__ __forceinline__ double to_uniform(double c) {
+    unsigned lo = __double2loint(c), hi = __double2hiint(c);
+    lo = __reduce_or_sync(0xffffffffu, lo);
+    hi = __reduce_or_sync(0xffffffffu, hi);
+    return __hiloint2double(hi, lo);
+}
+template <int W, int P, int MODE>
+__global__ void __launch_bounds__(W * 32, 1) pat_f(double *out, const double *in) {
+    __shared__ double2 sm[256 * 2];
+    for (int i = threadIdx.x; i < 512; i += blockDim.x) sm[i] = make_double2(in[i & 63], in[(i + 7) & 63]);
+    __syncthreads();
+    double acc[P][8], t[P][8];
+#pragma unroll
+    for (int p = 0; p < P; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) { acc[p][r] = p + r; t[p][r] = in[8 + p + r] + threadIdx.x * 1e-6; }
+    for (int i = 0; i < ITERS / 8; ++i) {
+        const double2 *cc = sm + (i & 1) * 256 + (threadIdx.x >> 5 & 1) * 0; // one "slab": 8 k x 8 r
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+#pragma unroll
+            for (int r = 0; r < 8; r += 2) {
+                double2 c = cc[(k * 8 + r) / 2];
+                if (MODE == 1) { c.x = to_uniform(c.x); c.y = to_uniform(c.y); }
+#pragma unroll
+                for (int p = 0; p < P; ++p) {
+                    acc[p][r] = __fma_rn(c.x, t[p][k], acc[p][r]);
+                    acc[p][r + 1] = __fma_rn(c.y, t[p][k], acc[p][r + 1]);
+                }
+            }
+    }
+    double s = 0;
+#pragma unroll
+    for (int p = 0; p < P; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) s += acc[p][r];
+    if (s == 1.2345) out[0] = s;
+}
+
+// E: DMMA m8n8k4 chains (8 independent accumulator fragments per warp)
+template <int W>
+__global__ void __launch_bounds__(W * 32, 1) pat_dmma(double *out, const double *in) {
+    double a = in[threadIdx.x & 31], b = in[32 + (threadIdx.x & 31)];
+    double c[8][2];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) c[j][0] = c[j][1] = j;
+    for (int i = 0; i < ITERS; ++i) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                         : "+d"(c[j][0]), "+d"(c[j][1]) : "d"(a), "d"(b));
+    }
+    double s = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += c[j][0] + c[j][1];
+    if (s == 1.2345) out[0] = s;
+}
+
+// DMMA rounding probe: D = A*B + C with A row 0 = (a0..a3), B col 0 = (b0..b3): which FMA order reproduces it?
+__global__ void dmma_probe(double *out, const double *av, const double *bv, double c0) {
+    const int lane = threadIdx.x, g = lane >> 2, t = lane & 3;
+    double a = g == 0 ? av[t] : 0.0, b = g == 0 ? bv[t] : 0.0; // A[g][t], B[t][g]
+    double d0 = (lane == 0) ? c0 : 0.0, d1 = 0.0;
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+    if (lane == 0) out[0] = d0;
+}
+
+template <class F>
+static double time_ms(F launch) {
+    cudaEvent_t b, e;
+    cudaEventCreate(&b); cudaEventCreate(&e);
+    launch();
+    cudaDeviceSynchronize();
+    float best = 1e30f;
+    for (int r = 0; r < 5; ++r) {
+        cudaEventRecord(b); launch(); cudaEventRecord(e); cudaEventSynchronize(e);
+        float ms; cudaEventElapsedTime(&ms, b, e);
+        if (ms < best) best = ms;
+    }
+    return best;
+}
+
+int main() {
+    int sms; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
+    int khz; cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, 0);
+    double *d, *in; cudaMalloc(&d, 64); cudaMalloc(&in, 1024);
+    double h[128]; for (int i = 0; i < 128; ++i) h[i] = 0.5 + 1e-3 * i;
+    cudaMemcpy(in, h, sizeof h, cudaMemcpyHostToDevice);
+    auto report = [&](const char *name, double fma_per_thread, int warps, double ms) {
+        const double fl = 2.0 * fma_per_thread * warps * 32 * sms;
+        printf("%-28s warps/SM=%2d  %.3f ms  %.2f TFLOP/s  (%.1f%% of %d SMs x 64 FMA/clk x %.3f GHz)\n", name, warps, ms,
+               fl / ms / 1e9, 100.0 * fl / ms / 1e9 / (sms * 64.0 * 2 * khz * 1e-6), sms, khz * 1e-6);
+    };
+#define RUN_A(W) report("A 1 fresh operand", 32.0 * ITERS, W, time_ms([&] { pat_a<W><<<sms, W * 32>>>(d, 0.999999, 1e-9); }))
+    RUN_A(4); RUN_A(8); RUN_A(16);
+#define RUN_B(W, P, M, name) report(name, 8.0 * P * ITERS, W, time_ms([&] { pat_b<W, P, M><<<sms, W * 32>>>(d, in, .1, .2, .3, .4, .5, .6, .7, .8); }))
+    RUN_B(8, 4, 0, "B P=4 c reused (p inner)"); RUN_B(8, 4, 1, "B P=4 t reused (r inner)"); RUN_B(8, 4, 2, "B P=4 c uniform");
+    RUN_B(12, 3, 0, "B P=3 c reused (p inner)"); RUN_B(12, 3, 1, "B P=3 t reused (r inner)"); RUN_B(12, 3, 2, "B P=3 c uniform");
+    RUN_B(16, 2, 0, "B P=2 c reused (p inner)"); RUN_B(16, 2, 1, "B P=2 t reused (r inner)"); RUN_B(16, 2, 2, "B P=2 c uniform");
+    RUN_B(4, 4, 0, "B P=4 c reused (p inner)"); RUN_B(4, 4, 2, "B P=4 c uniform");
+#define RUN_F(W, P, M, name) report(name, 64.0 * P * (ITERS / 8), W, time_ms([&] { pat_f<W, P, M><<<sms, W * 32>>>(d, in); }))
+    RUN_F(8, 4, 0, "F P=4 LDS coef, vector"); RUN_F(8, 4, 1, "F P=4 LDS coef, REDUX->UR");
+    RUN_F(12, 3, 0, "F P=3 LDS coef, vector"); RUN_F(12, 3, 1, "F P=3 LDS coef, REDUX->UR");
+    RUN_F(16, 2, 0, "F P=2 LDS coef, vector"); RUN_F(16, 2, 1, "F P=2 LDS coef, REDUX->UR");
+#define RUN_E(W) report("E DMMA m8n8k4", 8.0 * 8 * ITERS /* 256 FMA per warp-instr = 8 per lane */, W, time_ms([&] { pat_dmma<W><<<sms, W * 32>>>(d, in); }))
+    RUN_E(4); RUN_E(8); RUN_E(16);
+    // rounding probe
+    double ha[4] = {1.0 + 0x1p-30, 1.0 + 0x1p-31, 1.0 - 0x1p-29, 1.0 + 0x1p-33}, hb[4] = {1.0 + 0x1p-28, 1.0 - 0x1p-27, 1.0 + 0x1p-30, 1.0 - 0x1p-31};
+    double *da, *db; cudaMalloc(&da, 32); cudaMalloc(&db, 32);
+    cudaMemcpy(da, ha, 32, cudaMemcpyHostToDevice); cudaMemcpy(db, hb, 32, cudaMemcpyHostToDevice);
+    const double c0 = -4.0 + 0x1p-40;
+    dmma_probe<<<1, 32>>>(d, da, db, c0);
+    double got; cudaMemcpy(&got, d, 8, cudaMemcpyDeviceToHost);
+    double fwd = c0, rev = c0;
+    for (int k = 0; k < 4; ++k) fwd = __builtin_fma(ha[k], hb[k], fwd);
+    for (int k = 3; k >= 0; --k) rev = __builtin_fma(ha[k], hb[k], rev);
+    printf("DMMA probe: got %a  fma chain k=0..3 %a  k=3..0 %a\n", got, fwd, rev);
+    printf("%s\n", cudaGetErrorString(cudaGetLastError()));
+    return 0;
+}
