@@ -188,10 +188,10 @@ int eval_device(Function *f, Replica *r, BinWorkspace &ws, const double *d_x, do
             free_workspace(ws);
             rc = alloc_workspace(r->dt, step, ws);
         }
-        for (int64_t o = 0; o < n && rc == 0; o += step) {
-            const int64_t m = n - o < step ? n - o : step;
-            rc = launch_eval_binned(r->dt, ws, d_x + o * r->dt.view.dim, d_res + o, m, stream, &launches);
-        }
+        ws.chunk_limit = step;
+        ws.prof = prof; // (re)attach: a reallocation starts from a fresh workspace
+        if (rc == 0)
+            rc = launch_eval_binned(r->dt, ws, d_x, d_res, n, stream, &launches); // chunks of ws.chunk_capacity
     } else {
         rc = launch_eval_direct(r->dt, d_x, d_res, nullptr, n, stream, &launches, prof);
     }

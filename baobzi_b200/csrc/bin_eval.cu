@@ -252,11 +252,208 @@ bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__res
     cp_async_wait<0>();
 }
 
+// ------------------------------------------------------------------------------------------ K4, FP64 tensor cores
+// Order 8 on the DMMA path.  Measured on B200 (scripts/micro/): a DFMA stream with two fresh register operands per
+// instruction (the register-blocked loop above) tops out at ~77 % of the FP64 peak once its coefficients come from
+// shared memory; mma.sync.m8n8k4.f64 runs at the same peak as DFMA (36.9 TFLOP/s), reads a quarter of the registers
+// per FMA and takes 1/8 of the issue slots -- and it rounds exactly like the chain it replaces: for every output,
+//     d = c;  d = fma(a[m][k], b[k][n], d)  for k = 0, 1, 2, 3          (scripts/micro/dmma_order.cu: 0 of 12.8 M
+// outputs differ, signed zeros and heavy cancellation included).  That is the reference's row chain
+// acc[r] = fma(C_i(r,k), Tz[k], acc[r]), so the result stays bit-identical.
+//
+// Mapping (slab i of the leaf, a group of 8 points):  D[point][n] = sum_k Tz[point][k] * C_i(row(n), k), two chained
+// MMAs (k = 0..3, 4..7) starting from C = -0.0 (fma(1, c, -0) == c: the reference's c * T_0).
+//   A fragment  lane (g, t) holds Tz[point g][k = t (+4)]            -- registers, constant over the slabs
+//   B fragment  lane (g, t) holds C_i(row(g), k = t (+4))            -- the WHOLE leaf block is 16 doubles per lane,
+//               loaded once per leaf with coalesced 256-byte requests and kept in registers: a warp walks a
+//               contiguous run of tiles, and tiles of one leaf are adjacent, so no shared-memory coefficient traffic
+//   D fragment  lane (g, t) holds columns 2t, 2t+1; the column -> row map is row(2t) = t, row(2t+1) = t + 4, which
+//               are exactly the two rows the reference's packet reduction pairs first:
+//               l_t = fma(Ty[t+4], acc[t+4], Ty[t] * acc[t]) is lane local, then d = (l0 + l2) + (l1 + l3) takes two
+//               quad shuffles.  Four groups (32 points) are reduced together so that every lane ends up owning one point.
+struct MmaStage { // per warp, per stage
+    double pts[3 * 128]; // [coordinate][slot]
+    uint32_t idx[128];
+};
+
+__device__ __forceinline__ void dmma8(double &d0, double &d1, double a, double b) {
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+// T[t] and T[t + 4] for t = lane & 3
+__device__ __forceinline__ void pick_t(const double (&T)[8], uint32_t t, double &lo, double &hi) {
+    const bool b0 = t & 1, b1 = t & 2;
+    const double l01 = b0 ? T[1] : T[0], l23 = b0 ? T[3] : T[2];
+    const double h01 = b0 ? T[5] : T[4], h23 = b0 ? T[7] : T[6];
+    lo = b1 ? l23 : l01;
+    hi = b1 ? h23 : h01;
+}
+__device__ __forceinline__ double shfl_xor_d(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+
+template <int WARPS, int EXP = 0, bool ROLLED = false>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+bin_eval3d_mma8_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                       const uint32_t *__restrict__ perm, const uint2 *__restrict__ tile_info,
+                       const uint32_t *__restrict__ n_tiles_p) {
+    constexpr int TILE = 128;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t n_tiles = __ldg(n_tiles_p);
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    MmaStage *stages = reinterpret_cast<MmaStage *>(smem_raw) + 2 * warp;
+    // ROLLED: the B fragments live in shared memory ([slab][kb][lane], conflict-free 256-byte rows) and the slab loop
+    // is not unrolled, so that every slab is one uninterrupted run of 8 DMMAs followed by its reduction
+    double *sB = reinterpret_cast<double *>(smem_raw + sizeof(MmaStage) * 2 * WARPS) + 512 * warp;
+    // contiguous run of tiles per warp: a leaf's tiles are adjacent, so its coefficients are fetched once per run
+    const uint32_t nw = gridDim.x * WARPS, wid = blockIdx.x * WARPS + warp;
+    const uint32_t t_begin = (uint32_t)(((uint64_t)n_tiles * wid) / nw), t_end = (uint32_t)(((uint64_t)n_tiles * (wid + 1)) / nw);
+
+    auto load_meta = [&](uint32_t tt, uint32_t (&id)[4]) {
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+            id[p] = tt < t_end ? __ldg(perm + (size_t)tt * TILE + p * 32 + lane) : kInvalidSlotE;
+    };
+    auto issue = [&](const uint32_t (&id)[4], MmaStage &st) {
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            st.idx[p * 32 + lane] = id[p];
+            if (id[p] != kInvalidSlotE) {
+                const double *q = x + 3ull * id[p];
+                cp_async8(&st.pts[0 * TILE + p * 32 + lane], q);
+                cp_async8(&st.pts[1 * TILE + p * 32 + lane], q + 1);
+                cp_async8(&st.pts[2 * TILE + p * 32 + lane], q + 2);
+            }
+        }
+        cp_async_commit();
+    };
+
+    uint32_t idx_n[4];
+    load_meta(t_begin, idx_n);
+    issue(idx_n, stages[0]);
+    load_meta(t_begin + 1, idx_n);
+    uint32_t cur_node = 0xFFFFFFFFu;
+    double breg[8][2]; // B fragments of the current leaf
+    double c0 = 0, c1 = 0, c2 = 0, ih0 = 0, ih1 = 0, ih2 = 0;
+    const uint32_t brow = (g >> 1) + 4 * (g & 1); // row(n = g)
+    int cur = 0;
+    for (uint32_t tt = t_begin; tt < t_end; ++tt, cur ^= 1) {
+        __syncwarp(); // every lane is done reading stage cur^1
+        if (EXP != 3 || tt < t_begin + 2) {
+            issue(idx_n, stages[cur ^ 1]);
+            load_meta(tt + 2, idx_n);
+        }
+        const uint2 info = EXP == 3 && tt > t_begin ? make_uint2(cur_node, 0) : __ldg(tile_info + tt);
+        if (info.x != cur_node) { // warp uniform
+            cur_node = info.x;
+            const double *C = tv.coeffs + 2ull * info.y;
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int kb = 0; kb < 2; ++kb)
+                    breg[i][kb] = __ldg(C + i * 64 + (4 * kb + t) * 8 + brow);
+            if (ROLLED) {
+                __syncwarp();
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+#pragma unroll
+                    for (int kb = 0; kb < 2; ++kb)
+                        sB[(i * 2 + kb) * 32 + lane] = breg[i][kb];
+                __syncwarp();
+            }
+            const NodeHead head = load_head(tv.nodes, info.x);
+            const NodeTail tail = load_tail(tv.nodes, info.x);
+            c0 = head.c0, c1 = head.c1, c2 = head.c2;
+            ih0 = tail.ih0, ih1 = tail.ih1, ih2 = tail.ih2;
+        }
+        cp_async_wait<1>();
+        __syncwarp();
+        const MmaStage &st = stages[cur];
+#pragma unroll 1
+        for (int s = 0; s < 4; ++s) {
+            const int base = s * 32;
+            double a0[4], a1[4], ya[4], yb[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { // the four points (group j, row g) this lane's fragments belong to
+                const int q = base + 8 * j + g;
+                const double v = __dmul_rn(__dsub_rn(st.pts[1 * TILE + q], c1), ih1);
+                const double w = __dmul_rn(__dsub_rn(st.pts[2 * TILE + q], c2), ih2);
+                if (EXP == 2) { // timing experiment: no recurrences
+                    a0[j] = w, a1[j] = v, ya[j] = w, yb[j] = v;
+                } else {
+                double T[8];
+                cheb_T<8>(w, T);
+                pick_t(T, t, a0[j], a1[j]);
+                cheb_T<8>(v, T);
+                pick_t(T, t, ya[j], yb[j]);
+                }
+            }
+            const int own = base + 8 * t + g; // this lane's own point: group t
+            const double u = __dmul_rn(__dsub_rn(st.pts[0 * TILE + own], c0), ih0);
+            const double x2 = __dadd_rn(u, u);
+            double tx = 1.0, tx_prev = u, val = 0.0;
+            const bool low = t < 2, odd = t & 1;
+#pragma unroll ROLLED ? 1 : 8
+            for (int i = 0; i < 8; ++i) {
+                double l[4];
+                const double b0 = ROLLED ? sB[(i * 2 + 0) * 32 + lane] : breg[i][0];
+                const double b1 = ROLLED ? sB[(i * 2 + 1) * 32 + lane] : breg[i][1];
+                double d0[4], d1[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    d0[j] = d1[j] = -0.0;
+                    dmma8(d0[j], d1[j], a0[j], b0);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    dmma8(d0[j], d1[j], a1[j], b1);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    l[j] = __dmul_rn(ya[j], d0[j]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    l[j] = __fma_rn(yb[j], d1[j], l[j]); // rows t and t + 4 of point (j, g)
+                // (l0 + l2) + (l1 + l3) over the quad; groups 0,1 are finished on lanes t < 2, groups 2,3 on t >= 2
+                double d;
+                if (EXP == 1) { // timing experiment: no shuffles / selects
+                    d = __dadd_rn(__dadd_rn(l[0], l[2]), __dadd_rn(l[1], l[3]));
+                } else {
+                const double r0 = shfl_xor_d(low ? l[2] : l[0], 2), r1 = shfl_xor_d(low ? l[3] : l[1], 2);
+                const double s0 = __dadd_rn(low ? l[0] : l[2], r0), s1 = __dadd_rn(low ? l[1] : l[3], r1);
+                d = __dadd_rn(odd ? s1 : s0, shfl_xor_d(odd ? s0 : s1, 1)); // lane t: point (t, g)
+                }
+                val = __fma_rn(tx, d, val);
+                const double tn = __fma_rn(x2, tx, -tx_prev);
+                tx_prev = tx;
+                tx = tn;
+            }
+            const uint32_t id = st.idx[own];
+            if (id != kInvalidSlotE)
+                res[id] = val;
+        }
+    }
+    cp_async_wait<0>();
+}
+
+template <int WARPS, int EXP = 0, bool ROLLED = false>
+static int launch_k4_mma8(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
+    auto kern = bin_eval3d_mma8_kernel<WARPS, EXP, ROLLED>;
+    constexpr size_t smem = sizeof(MmaStage) * 2 * WARPS + (ROLLED ? 4096 * WARPS : 0);
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess)
+            return (int)e;
+        configured = true;
+    }
+    kern<<<dt.sm_count, WARPS * 32, smem, st>>>(dt.view, d_x, d_res, ws.perm, ws.tile_info, ws.n_tiles);
+    return (int)cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------------------ host side
 struct K4Variant {
     int order, P, warps;
     bool tzfly, tykeep;
     int (*launch)(const DeviceTree &, const BinWorkspace &, const double *, double *, cudaStream_t);
+    const void *func; // for cudaFuncGetAttributes
+    size_t smem;
 };
 
 template <int O, int P, int WARPS, bool TZFLY, bool TYKEEP, int EXP = 0>
@@ -275,11 +472,15 @@ static int launch_k4(const DeviceTree &dt, const BinWorkspace &ws, const double 
     return (int)cudaGetLastError();
 }
 
-#define BZ_K4(O_, P_, W_, F_, Y_) {O_, P_, W_, F_, Y_, launch_k4<O_, P_, W_, F_, Y_>}
+#define BZ_K4(O_, P_, W_, F_, Y_)                                                                                      \
+    {O_, P_, W_, F_, Y_, launch_k4<O_, P_, W_, F_, Y_>, (const void *)bin_eval3d_kernel<O_, P_, W_, F_, Y_>,           \
+     sizeof(PipeStage<O_, P_>) * 2 * W_}
+#define BZ_K4M(W_) {8, 4, W_, true, true, launch_k4_mma8<W_>, (const void *)bin_eval3d_mma8_kernel<W_>, sizeof(MmaStage) * 2 * W_}
 // first entry of an order = its default
 static const K4Variant kVariants[] = {
     BZ_K4(6, 4, 8, false, true),   BZ_K4(6, 4, 12, false, true),  BZ_K4(6, 4, 16, false, false),
-    BZ_K4(8, 4, 8, false, true),   BZ_K4(8, 4, 8, false, false),  BZ_K4(8, 3, 12, false, false),
+    BZ_K4(8, 4, 8, false, true),   BZ_K4(8, 4, 8, false, false),
+    BZ_K4M(16), BZ_K4M(12), BZ_K4M(8), // tzfly && tykeep together = the DMMA kernel  BZ_K4(8, 3, 12, false, false),
     BZ_K4(8, 3, 12, false, true),  BZ_K4(8, 4, 12, true, false),  BZ_K4(8, 2, 16, false, false),
     BZ_K4(8, 2, 16, false, true),  BZ_K4(8, 3, 8, false, true),
     BZ_K4(10, 2, 8, false, true),  BZ_K4(10, 3, 8, false, false), BZ_K4(10, 4, 8, true, false),
@@ -287,11 +488,15 @@ static const K4Variant kVariants[] = {
     BZ_K4(14, 2, 4, false, true),  BZ_K4(14, 3, 4, true, false),
     BZ_K4(16, 2, 2, false, true),  BZ_K4(16, 2, 3, false, false),
 #ifdef BZ_EXPERIMENTS // timing experiments with WRONG results: P = 91 / 92 select them
-    {8, 91, 8, false, true, launch_k4<8, 4, 8, false, true, 1>}, {8, 92, 8, false, true, launch_k4<8, 4, 8, false, true, 2>},
-    {8, 91, 12, false, false, launch_k4<8, 3, 12, false, false, 1>}, {8, 92, 12, false, false, launch_k4<8, 3, 12, false, false, 2>},
+    {8, 96, 16, true, true, launch_k4_mma8<16, 0, true>, nullptr, 0}, {8, 97, 12, true, true, launch_k4_mma8<12, 0, true>, nullptr, 0},
+    {8, 98, 8, true, true, launch_k4_mma8<8, 0, true>, nullptr, 0},
+    {8, 93, 16, true, true, launch_k4_mma8<16, 1>, nullptr, 0}, {8, 94, 16, true, true, launch_k4_mma8<16, 2>, nullptr, 0}, {8, 95, 16, true, true, launch_k4_mma8<16, 3>, nullptr, 0},
+    {8, 91, 8, false, true, launch_k4<8, 4, 8, false, true, 1>, nullptr, 0}, {8, 92, 8, false, true, launch_k4<8, 4, 8, false, true, 2>, nullptr, 0},
+    {8, 91, 12, false, false, launch_k4<8, 3, 12, false, false, 1>, nullptr, 0}, {8, 92, 12, false, false, launch_k4<8, 3, 12, false, false, 2>, nullptr, 0},
 #endif
 };
 #undef BZ_K4
+#undef BZ_K4M
 
 static const K4Variant *find_variant(int order, int P, int warps, int tzfly, int tykeep) {
     for (const K4Variant &v : kVariants)
@@ -316,8 +521,22 @@ int bin_eval_select(int order, int *P) {
     }
     if (!v)
         return -1;
-    *P = v->P > 90 ? (v->warps == 12 ? 3 : 4) : v->P;
+    *P = v->P > 90 ? (v->warps == 12 && v->P < 93 ? 3 : 4) : v->P;
     return (int)(v - kVariants);
+}
+
+// Registers (whole CTA) and shared memory the selected kernel holds on an SM: what is left is the room a
+// concurrently running sort CTA may use.  Returns false when unknown.
+bool bin_eval_footprint(int variant, int *cta_regs, size_t *cta_smem) {
+    if (variant < 0 || variant >= (int)(sizeof(kVariants) / sizeof(kVariants[0])) || !kVariants[variant].func)
+        return false;
+    cudaFuncAttributes a;
+    if (cudaFuncGetAttributes(&a, kVariants[variant].func) != cudaSuccess)
+        return false;
+    const int per_warp = (a.numRegs * 32 + 511) / 512 * 512; // allocation granularity: 512 registers per warp
+    *cta_regs = per_warp * kVariants[variant].warps;
+    *cta_smem = kVariants[variant].smem + a.sharedSizeBytes + 1024;
+    return true;
 }
 
 int launch_bin_eval3d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {

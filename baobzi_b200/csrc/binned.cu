@@ -20,6 +20,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <utility>
 
 #include "lookup.cuh"
 
@@ -31,6 +32,7 @@ constexpr uint32_t kInvalidSlot = 0xFFFFFFFFu;
 constexpr int kBinThreads = 256;
 
 int bin_eval_select(int order, int *P);
+bool bin_eval_footprint(int variant, int *cta_regs, size_t *cta_smem);
 int launch_bin_eval3d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st);
 
 // ------------------------------------------------------------------------------------------ K1
@@ -75,16 +77,20 @@ __global__ void __launch_bounds__(kSortThreads)
 bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
                       uint32_t *__restrict__ key, uint32_t *__restrict__ count, uint32_t *__restrict__ count_next,
                       int cshift, uint32_t TILE, uint32_t *__restrict__ perm, uint32_t *__restrict__ tile_leaf,
-                      uint2 *__restrict__ tile_info, uint32_t *__restrict__ n_tiles, uint32_t n) {
+                      uint2 *__restrict__ tile_info, uint32_t *__restrict__ n_tiles, uint32_t n, uint32_t skey_cap) {
     extern __shared__ uint32_t tbl[]; // [n_leaves] histogram -> base -> next free slot
-    __shared__ uint32_t warp_sums[kSortThreads / 32];
+    __shared__ uint32_t warp_sums[32];
     const uint32_t nl = tv.n_leaves;
+    // keys of the CTA's own range as 16-bit leaf ranks in shared memory when they fit (skey_cap entries follow
+    // tbl[]): the scatter then never goes back to global memory for them
+    uint16_t *skey = reinterpret_cast<uint16_t *>(tbl + nl);
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     for (uint32_t l = tid; l < nl; l += nthr)
         tbl[l] = 0;
     __syncthreads();
     const uint32_t lo = (uint32_t)(((uint64_t)blockIdx.x * n) / gridDim.x);
     const uint32_t hi = (uint32_t)(((uint64_t)(blockIdx.x + 1) * n) / gridDim.x);
+    const bool use_skey = hi - lo <= skey_cap; // CTA uniform
 
     // ---- phase A
     for (uint32_t i0 = lo + tid; i0 < hi; i0 += kSortPts * nthr) {
@@ -105,7 +111,10 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
             if (!have[u])
                 continue;
             const uint32_t i = i0 + u * nthr;
-            key[i] = leaf[u];
+            if (use_skey)
+                skey[i - lo] = (uint16_t)leaf[u]; // kNotLeaf -> 0xFFFF (n_leaves < 0xFFFF when skey_cap > 0)
+            else
+                key[i] = leaf[u];
             if (leaf[u] == kNotLeaf)
                 res[i] = __longlong_as_double(0x7ff8000000000000ll);
             else
@@ -140,14 +149,14 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         warp_sums[warp] = incl;
     __syncthreads();
     if (warp == 0) {
-        uint32_t w = lane < kSortThreads / 32 ? warp_sums[lane] : 0u;
+        uint32_t w = lane < nthr / 32 ? warp_sums[lane] : 0u;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
             if (lane >= o)
                 w += t;
         }
-        if (lane < kSortThreads / 32)
+        if (lane < nthr / 32)
             warp_sums[lane] = w;
     }
     __syncthreads();
@@ -170,7 +179,7 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         start += padded;
     }
     if (blockIdx.x == 0 && tid == nthr - 1)
-        *n_tiles = (warp_sums[kSortThreads / 32 - 1]) / TILE;
+        *n_tiles = (warp_sums[nthr / 32 - 1]) / TILE;
     __syncthreads();
 
     // ---- scatter
@@ -179,12 +188,27 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u) {
             const uint32_t i = i0 + u * nthr;
-            k[u] = i < hi ? __ldcs(key + i) : kNotLeaf;
+            if (use_skey) {
+                const uint32_t v = i < hi ? skey[i - lo] : 0xFFFFu;
+                k[u] = v == 0xFFFFu ? kNotLeaf : v;
+            } else {
+                k[u] = i < hi ? __ldcs(key + i) : kNotLeaf;
+            }
         }
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u)
             if (k[u] != kNotLeaf)
+            {
+#if defined(BZ_SORT_EXP) && BZ_SORT_EXP == 1 // timing experiment: no scattered stores
+                const uint32_t slot = atomicAdd(tbl + k[u], 1u);
+                if (slot == 0xFFFFFFF0u)
+                    perm[slot] = i0 + u * nthr;
+#elif defined(BZ_SORT_EXP) && BZ_SORT_EXP == 2 // timing experiment: no shared atomics in the scatter
+                perm[tbl[k[u]] + (i0 & 7)] = i0 + u * nthr;
+#else
                 perm[atomicAdd(tbl + k[u], 1u)] = i0 + u * nthr;
+#endif
+            }
     }
 }
 
@@ -303,17 +327,68 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         ws.fused = ws.fused && std::atoi(e) != 0;
     ws.sort_ctas = 0;
     if (ws.fused) { // cooperative launch: the grid is what is co-resident
-        const size_t smem = (size_t)nl * sizeof(uint32_t);
+        const size_t hist = (size_t)nl * sizeof(uint32_t);
         cudaFuncSetAttribute(bin_sort_fused_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
-        int per_sm = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<3>, kSortThreads, smem);
-        int want = 4;
+        int want = 2;
         if (const char *e = std::getenv("BAOBZI_B200_SORT_CTAS"))
             if (std::atoi(e) > 0)
                 want = std::atoi(e);
-        per_sm = per_sm < want ? per_sm : want;
+        // preferred: `want` CTAs per SM, each keeping the 16-bit keys of its range in shared memory
+        ws.sort_skey = 0;
+        ws.sort_smem = hist;
+        int per_sm = 0;
+        if (nl < 0xFFFFu && !(std::getenv("BAOBZI_B200_SORT_SKEY") && std::atoi(std::getenv("BAOBZI_B200_SORT_SKEY")) == 0)) {
+            const int64_t range = (chunk + (int64_t)dt.sm_count * want - 1) / ((int64_t)dt.sm_count * want);
+            int64_t cap = range > kSortThreads * kSortPts ? range : kSortThreads * kSortPts; // small launches use fewer CTAs
+            cap = (cap + 7) / 8 * 8;
+            const size_t smem = hist + (size_t)cap * sizeof(uint16_t);
+            if (smem <= kFusedSortMaxSmem) {
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<3>, kSortThreads, smem);
+                if (per_sm >= want) {
+                    per_sm = want;
+                    ws.sort_skey = (uint32_t)cap;
+                    ws.sort_smem = smem;
+                }
+            }
+        }
+        if (!ws.sort_skey) {
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<3>, kSortThreads, hist);
+            per_sm = per_sm < want ? per_sm : want;
+        }
         ws.sort_ctas = dt.sm_count * per_sm;
+        ws.sort_threads = kSortThreads;
         ws.fused = per_sm >= 1;
+        // Overlap: can one sort CTA per SM live beside the evaluation kernel's CTA?  Then the sort of the next chunk
+        // runs concurrently with the evaluation of this one (different streams); the sort is sized to what is left.
+        ws.sort_overlap_ok = false;
+        int k4_regs = 0;
+        size_t k4_smem = 0;
+        cudaFuncAttributes sa;
+        const char *ov = std::getenv("BAOBZI_B200_OVERLAP");
+        // Measured on B200 (C3): beside the evaluation kernel the sort is left 6 warps per SM and takes 3.3x as long, and
+        // its L2 traffic slows the evaluation by a third -- 18.1 ms per 2e8 points against 13.6 ms back to back.
+        // Off by default; BAOBZI_B200_OVERLAP=1 enables it.
+        if (ws.fused && ov && std::atoi(ov) != 0 && bin_eval_footprint(ws.variant, &k4_regs, &k4_smem) &&
+            cudaFuncGetAttributes(&sa, bin_sort_fused_kernel<3>) == cudaSuccess) {
+            const int per_warp = (sa.numRegs * 32 + 511) / 512 * 512;
+            int warps = (65536 - k4_regs) / per_warp;
+            warps = warps > kSortThreads / 32 ? kSortThreads / 32 : warps;
+            warps = warps >= 8 ? warps / 4 * 4 : warps; // keep the sub-partitions even
+            const size_t smem_left = 227 * 1024 > k4_smem ? 227 * 1024 - k4_smem : 0;
+            if (warps >= 4 && hist + sa.sharedSizeBytes + 1024 <= smem_left) {
+                ws.sort_overlap_ok = true;
+                ws.sort_threads = warps * 32;
+                ws.sort_ctas = dt.sm_count;
+                ws.sort_skey = 0;
+                ws.sort_smem = hist;
+            }
+        }
+        if (std::getenv("BAOBZI_B200_DEBUG"))
+            std::fprintf(stderr, "baobzi: overlap %d: sort CTA %d threads beside %d K4 registers / %zu B smem\n",
+                         (int)ws.sort_overlap_ok, ws.sort_threads, k4_regs, k4_smem);
+        if (std::getenv("BAOBZI_B200_DEBUG"))
+            std::fprintf(stderr, "baobzi: fused sort: %d CTAs/SM, %zu B smem, %u shared keys per CTA, chunk %lld\n", per_sm,
+                         ws.sort_smem, ws.sort_skey, (long long)chunk);
     }
     cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
     if (e == cudaSuccess)
@@ -336,6 +411,27 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         e = cudaMemset(ws.count, 0, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)
         e = cudaMemset(ws.cursor, 0, sizeof(uint32_t) * cwords);
+    ws.overlap = ws.fused && ws.sort_overlap_ok;
+    if (e == cudaSuccess && ws.overlap) {
+        e = cudaMalloc((void **)&ws.alt_key, sizeof(uint32_t) * chunk);
+        if (e == cudaSuccess)
+            e = cudaMalloc((void **)&ws.alt_perm, sizeof(uint32_t) * ws.perm_capacity);
+        if (e == cudaSuccess)
+            e = cudaMalloc((void **)&ws.alt_tile_leaf, sizeof(uint32_t) * ws.tile_capacity);
+        if (e == cudaSuccess)
+            e = cudaMalloc((void **)&ws.alt_tile_info, sizeof(uint2) * ws.tile_capacity);
+        if (e == cudaSuccess)
+            e = cudaMalloc((void **)&ws.alt_n_tiles, sizeof(uint32_t));
+        if (e == cudaSuccess)
+            e = cudaStreamCreateWithFlags(&ws.sort_stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess)
+            e = cudaEventCreateWithFlags(&ws.ev_begin, cudaEventDisableTiming);
+        for (int h = 0; h < 2 && e == cudaSuccess; ++h) {
+            e = cudaEventCreateWithFlags(&ws.ev_sorted[h], cudaEventDisableTiming);
+            if (e == cudaSuccess)
+                e = cudaEventCreateWithFlags(&ws.ev_evaluated[h], cudaEventDisableTiming);
+        }
+    }
     if (e != cudaSuccess) {
         free_workspace(ws);
         return (int)e;
@@ -354,6 +450,21 @@ void free_workspace(BinWorkspace &ws) {
     cudaFree(ws.tile_leaf);
     cudaFree(ws.n_tiles);
     cudaFree(ws.tile_info);
+    cudaFree(ws.alt_key);
+    cudaFree(ws.alt_perm);
+    cudaFree(ws.alt_tile_leaf);
+    cudaFree(ws.alt_tile_info);
+    cudaFree(ws.alt_n_tiles);
+    if (ws.sort_stream)
+        cudaStreamDestroy(ws.sort_stream);
+    if (ws.ev_begin)
+        cudaEventDestroy(ws.ev_begin);
+    for (int h = 0; h < 2; ++h) {
+        if (ws.ev_sorted[h])
+            cudaEventDestroy(ws.ev_sorted[h]);
+        if (ws.ev_evaluated[h])
+            cudaEventDestroy(ws.ev_evaluated[h]);
+    }
     ws = BinWorkspace();
 }
 
@@ -372,19 +483,68 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         cudaEventRecord(ev[0], st);
     }
     int rc_sort = 0;
-    if (ws.fused) {
+    if (ws.fused && ws.overlap) {
+        // sort(c) goes to the side stream into buffer set `half`; it waits only for the call's inputs (ev_begin) and
+        // for the evaluation that last read this set (chunk c-2), so it runs beside the evaluation of chunk c-1.
+        const int h = ws.half;
+        cudaStream_t ss = ws.sort_stream;
+        if (ws.evaluated_valid[h])
+            cudaStreamWaitEvent(ss, ws.ev_evaluated[h], 0);
+        if (pf) {
+            cudaEventRecord(ev[0], ss);
+        }
         uint32_t grid = (uint32_t)ws.sort_ctas;
-        const uint32_t useful = (n + kSortThreads * kSortPts - 1) / (kSortThreads * kSortPts);
+        const uint32_t per_cta = (uint32_t)ws.sort_threads * kSortPts;
+        const uint32_t useful = (n + per_cta - 1) / per_cta;
         grid = grid < useful ? grid : (useful ? useful : 1u);
         uint32_t *cur = ws.flip ? ws.cursor : ws.count, *next = ws.flip ? ws.count : ws.cursor;
         ws.flip = !ws.flip;
         TreeView tvv = tv;
         int cshift = ws.cshift;
-        uint32_t tile = TILE, nn = n;
+        uint32_t tile = TILE, nn = n, skey = 0;
         void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
-                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn};
-        rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3>, dim3(grid), dim3(kSortThreads), args,
-                                                   (size_t)tv.n_leaves * sizeof(uint32_t), st);
+                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey};
+        rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3>, dim3(grid), dim3(ws.sort_threads), args,
+                                                   ws.sort_smem, ss);
+        if (pf) {
+            cudaEventRecord(ev[1], ss);
+            pf->spans.push_back({kStageLookup, ev[0], ev[1], (int64_t)n});
+        }
+        cudaEventRecord(ws.ev_sorted[h], ss);
+        cudaStreamWaitEvent(st, ws.ev_sorted[h], 0);
+        if (pf)
+            cudaEventRecord(ev[3], st);
+        int rc = launch_bin_eval3d(dt, ws, d_x, d_res, st);
+        if (pf) {
+            cudaEventRecord(ev[4], st);
+            pf->spans.push_back({kStageEval, ev[3], ev[4], (int64_t)n});
+            pf->pool.push_back(ev[2]);
+        }
+        cudaEventRecord(ws.ev_evaluated[h], st);
+        ws.evaluated_valid[h] = true;
+        // the next chunk uses the other buffer set
+        std::swap(ws.key, ws.alt_key);
+        std::swap(ws.perm, ws.alt_perm);
+        std::swap(ws.tile_leaf, ws.alt_tile_leaf);
+        std::swap(ws.tile_info, ws.alt_tile_info);
+        std::swap(ws.n_tiles, ws.alt_n_tiles);
+        ws.half ^= 1;
+        return rc_sort ? rc_sort : rc ? rc : (int)cudaGetLastError();
+    }
+    if (ws.fused) {
+        uint32_t grid = (uint32_t)ws.sort_ctas;
+        const uint32_t per_cta = (uint32_t)ws.sort_threads * kSortPts;
+        const uint32_t useful = (n + per_cta - 1) / per_cta;
+        grid = grid < useful ? grid : (useful ? useful : 1u);
+        uint32_t *cur = ws.flip ? ws.cursor : ws.count, *next = ws.flip ? ws.count : ws.cursor;
+        ws.flip = !ws.flip;
+        TreeView tvv = tv;
+        int cshift = ws.cshift;
+        uint32_t tile = TILE, nn = n, skey = ws.sort_skey;
+        void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
+                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey};
+        rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3>, dim3(grid), dim3(ws.sort_threads), args,
+                                                   ws.sort_smem, st);
         if (pf) { // the three classic stages are one launch here: all of it is booked under "lookup"
             cudaEventRecord(ev[1], st);
             cudaEventRecord(ev[2], st);
@@ -418,12 +578,21 @@ int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x
                        cudaStream_t stream, int64_t *launches) {
     if (n <= 0)
         return 0;
-    if (dt.view.dim != 3 || n > ws.chunk_capacity)
+    if (dt.view.dim != 3 || ws.chunk_capacity <= 0)
         return (int)cudaErrorInvalidValue;
-    int rc = launch_chunk_3d(dt, ws, d_x, d_res, (uint32_t)n, stream);
-    if (launches)
-        *launches += ws.fused ? 2 : 5;
-    return rc;
+    if (ws.overlap) { // fork: the side stream may start once everything queued before this call is done
+        cudaEventRecord(ws.ev_begin, stream);
+        cudaStreamWaitEvent(ws.sort_stream, ws.ev_begin, 0);
+    }
+    int rc = 0;
+    const int64_t step = ws.chunk_limit > 0 && ws.chunk_limit < ws.chunk_capacity ? ws.chunk_limit : ws.chunk_capacity;
+    for (int64_t o = 0; o < n && rc == 0; o += step) {
+        const int64_t m = n - o < step ? n - o : step;
+        rc = launch_chunk_3d(dt, ws, d_x + 3 * o, d_res + o, (uint32_t)m, stream);
+        if (launches)
+            *launches += ws.fused ? 2 : 5;
+    }
+    return rc; // every side-stream launch is an ancestor of the last evaluation on `stream`: the join is implicit
 }
 
 } // namespace bz

@@ -76,6 +76,7 @@ struct StageProfile {
 // stays resident in L2).
 struct BinWorkspace {
     int64_t chunk_capacity = 0; // points
+    int64_t chunk_limit = 0;    // points per chunk wanted by this call (<= capacity; 0: capacity)
     uint32_t *key = nullptr;    // [chunk]            leaf rank per point (kNotLeaf = outside the domain)
     uint32_t *perm = nullptr;   // [chunk + padding]  point index (within the chunk) per sorted slot
     uint32_t *count = nullptr;  // [n_leaves + 1]     histogram (zero between chunks: the scan clears it)
@@ -87,6 +88,8 @@ struct BinWorkspace {
                                 // are then the two histogram buffers used by alternate chunks
     bool flip = false;          // which of the two the next chunk histograms into
     int sort_ctas = 0;          // grid of the cooperative kernel (all CTAs co-resident)
+    uint32_t sort_skey = 0;     // per-CTA capacity of the shared-memory key array (0: keys go through key[])
+    size_t sort_smem = 0;       // dynamic shared memory of the cooperative kernel
     uint2 *tile_info = nullptr; // [max_tiles] {node, coefficient offset / 16 B} of each tile's leaf
     int cshift = 0;             // count[] / cursor[] entries are spread 2^cshift words apart so that atomics of
                                 // different leaves land in different L2 sectors / lines
@@ -95,6 +98,17 @@ struct BinWorkspace {
     uint32_t *n_tiles = nullptr;   // [1]
     int64_t perm_capacity = 0, tile_capacity = 0;
     StageProfile *prof = nullptr; // not owned
+    // Overlap of the (memory / latency bound) sort of chunk c+1 with the (FP64 bound) evaluation of chunk c: the
+    // sort runs on its own stream into the second set of buffers below, sized to be co-resident with the
+    // evaluation kernel's CTAs (binned.cu: launch_eval_binned).
+    bool overlap = false, sort_overlap_ok = false;
+    int sort_threads = 0;
+    cudaStream_t sort_stream = nullptr;
+    cudaEvent_t ev_begin = nullptr, ev_sorted[2] = {nullptr, nullptr}, ev_evaluated[2] = {nullptr, nullptr};
+    bool evaluated_valid[2] = {false, false};
+    int half = 0;
+    uint32_t *alt_key = nullptr, *alt_perm = nullptr, *alt_tile_leaf = nullptr, *alt_n_tiles = nullptr;
+    uint2 *alt_tile_info = nullptr;
 };
 
 struct DeviceTree {
@@ -121,7 +135,7 @@ int launch_eval_direct(const DeviceTree &dt, const double *d_x, double *d_res, i
 int measure_fp64_peak(double *tflops, int repeats);
 // Scalar twin: x[dim] -> y[out_dim] (reference Function::eval(x, res), template.hpp:851-860).
 int launch_eval_scalar(const DeviceTree &dt, const double *d_x, double *d_y, cudaStream_t stream, int64_t *launches);
-// Binned path over one chunk (n <= ws.chunk_capacity): lookup+histogram, padded scan, scatter, evaluation.
+// Binned path over n points in chunks of ws.chunk_capacity: sort by leaf (lookup+histogram, padded scan, scatter), evaluation.
 int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
                        cudaStream_t stream, int64_t *launches);
 // true when the binned path is implemented for this (dim, order)

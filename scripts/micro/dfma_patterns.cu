@@ -117,6 +117,161 @@ __global__ void __launch_bounds__(W * 32, 1) pat_dmma(double *out, const double 
     if (s == 1.2345) out[0] = s;
 }
 
+// G: DMMA and DFMA mixed in the ratio of the tensor-core evaluation kernel (8 DMMA : NF DFMA per step)
+template <int W, int NF>
+__global__ void __launch_bounds__(W * 32, 1) pat_mix(double *out, const double *in) {
+    double a = in[threadIdx.x & 31], b = in[32 + (threadIdx.x & 31)];
+    double c[4][2], v[16];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) c[j][0] = c[j][1] = j;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = threadIdx.x * 1e-3 + k;
+    for (int i = 0; i < ITERS; ++i) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                         : "+d"(c[j][0]), "+d"(c[j][1]) : "d"(a), "d"(b));
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                         : "+d"(c[j][0]), "+d"(c[j][1]) : "d"(b), "d"(a));
+        }
+#pragma unroll
+        for (int k = 0; k < NF; ++k) v[k % 16] = __fma_rn(v[k % 16], a, b);
+    }
+    double s = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) s += c[j][0] + c[j][1];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) s += v[k];
+    if (s == 1.2345) out[0] = s;
+}
+
+// G2: same mix, but the DFMAs are spread singly between the DMMAs (SPREAD) instead of issued as one run
+template <int W, int SPREAD>
+__global__ void __launch_bounds__(W * 32, 1) pat_mix2(double *out, const double *in) {
+    double a = in[threadIdx.x & 31], b = in[32 + (threadIdx.x & 31)];
+    double c[8][2], v[16];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) c[j][0] = c[j][1] = j;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = threadIdx.x * 1e-3 + k;
+    for (int i = 0; i < ITERS; ++i) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                         : "+d"(c[j][0]), "+d"(c[j][1]) : "d"(a), "d"(b));
+            if (SPREAD) {
+                asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(v[2 * j]) : "d"(a), "d"(b));
+                asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(v[2 * j + 1]) : "d"(a), "d"(b));
+            }
+        }
+        if (!SPREAD) {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(v[k]) : "d"(a), "d"(b));
+        }
+    }
+    double s = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += c[j][0] + c[j][1];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) s += v[k];
+    if (s == 1.2345) out[0] = s;
+}
+
+// E2: DMMA with distinct A / B registers per instruction; RESTART: every pair starts from C = -0.0 like the kernel
+template <int W, int RESTART>
+__global__ void __launch_bounds__(W * 32, 1) pat_dmma2(double *out, const double *in) {
+    double a[8], b[16], c[4][2], acc = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = in[(threadIdx.x + j) & 31];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) b[j] = in[32 + ((threadIdx.x + j) & 31)];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) c[j][0] = c[j][1] = j;
+    for (int i = 0; i < ITERS / 8; ++i) {
+#pragma unroll
+        for (int sl = 0; sl < 8; ++sl) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (RESTART) c[j][0] = c[j][1] = -0.0;
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                             : "+d"(c[j][0]), "+d"(c[j][1]) : "d"(a[2 * j]), "d"(b[2 * sl]));
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                             : "+d"(c[j][0]), "+d"(c[j][1]) : "d"(a[2 * j + 1]), "d"(b[2 * sl + 1]));
+            }
+            if (RESTART) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc = __fma_rn(c[j][0], c[j][1], acc);
+            }
+        }
+    }
+    double s = acc;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) s += c[j][0] + c[j][1];
+    if (s == 1.2345) out[0] = s;
+}
+
+// G3: 8 DMMA + 13 DFMA per step where the DFMAs form CH dependent chains (CH = 13: independent; 1: one chain)
+template <int W, int CH>
+__global__ void __launch_bounds__(W * 32, 1) pat_mix3(double *out, const double *in) {
+    double a = in[threadIdx.x & 31], b = in[32 + (threadIdx.x & 31)];
+    double c[8][2], v[13];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) c[j][0] = c[j][1] = j;
+#pragma unroll
+    for (int k = 0; k < 13; ++k) v[k] = threadIdx.x * 1e-3 + k;
+    for (int i = 0; i < ITERS; ++i) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                         : "+d"(c[j][0]), "+d"(c[j][1]) : "d"(a), "d"(b));
+#pragma unroll
+        for (int k = 0; k < 13; ++k) v[k % CH] = __fma_rn(v[k % CH], a, b);
+    }
+    double s = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += c[j][0] + c[j][1];
+#pragma unroll
+    for (int k = 0; k < 13; ++k) s += v[k];
+    if (s == 1.2345) out[0] = s;
+}
+
+// H: warps of two kinds share each SM sub-partition: even warps issue only DMMA, odd warps only DFMA (independent
+// chains), sized so that each kind alone needs the same pipe time.  No compiler interleaving is possible across
+// warps, so elapsed / (sum of pipe cycles) shows what the hardware loses when DMMA and DFMA alternate on the pipe.
+template <int W, int KIND> // KIND 0: both, 1: only DMMA warps work, 2: only DFMA warps work
+__global__ void __launch_bounds__(W * 32, 1) pat_h(double *out, const double *in) {
+    const int warp = threadIdx.x >> 5;
+    const bool mma_warp = ((warp >> 2) & 1) == 0; // warps 0-3 -> one per sub-partition, 4-7 -> the other kind, ...
+    double a = in[threadIdx.x & 31], b = in[32 + (threadIdx.x & 31)];
+    double s = 0;
+    if (mma_warp) {
+        if (KIND == 2) return;
+        double c[8][2];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) c[j][0] = c[j][1] = j;
+        for (int i = 0; i < ITERS; ++i) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                             : "+d"(c[j][0]), "+d"(c[j][1]) : "d"(a), "d"(b));
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += c[j][0] + c[j][1];
+    } else {
+        if (KIND == 1) return;
+        double v[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = threadIdx.x * 1e-3 + k;
+        for (int i = 0; i < ITERS * 4; ++i) { // 4 x 16 DFMA x 2 cycles = 8 DMMA x 16 cycles
+#pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] = __fma_rn(v[k], a, b);
+        }
+#pragma unroll
+        for (int k = 0; k < 16; ++k) s += v[k];
+    }
+    if (s == 1.2345) out[0] = s;
+}
+
 // DMMA rounding probe: D = A*B + C with A row 0 = (a0..a3), B col 0 = (b0..b3): which FMA order reproduces it?
 __global__ void dmma_probe(double *out, const double *av, const double *bv, double c0) {
     const int lane = threadIdx.x, g = lane >> 2, t = lane & 3;
@@ -166,6 +321,24 @@ int main() {
     RUN_F(16, 2, 0, "F P=2 LDS coef, vector"); RUN_F(16, 2, 1, "F P=2 LDS coef, REDUX->UR");
 #define RUN_E(W) report("E DMMA m8n8k4", 8.0 * 8 * ITERS /* 256 FMA per warp-instr = 8 per lane */, W, time_ms([&] { pat_dmma<W><<<sms, W * 32>>>(d, in); }))
     RUN_E(4); RUN_E(8); RUN_E(16);
+#define RUN_G(W, NF) { double ms = time_ms([&] { pat_mix<W, NF><<<sms, W * 32>>>(d, in); }); \
+        printf("G 8 DMMA + %2d DFMA  warps/SM=%2d  %.3f ms  pipe cycles needed/elapsed = %.3f\n", NF, W, ms, \
+               (8 * 16.0 + NF * 2.0) * ITERS * (W / 4.0) / (ms * 1e-3 * khz * 1e3)); }
+    RUN_G(16, 0); RUN_G(16, 13); RUN_G(16, 32); RUN_G(8, 13); RUN_G(4, 13); RUN_G(16, 64);
+#define RUN_G2(W, S) { double ms = time_ms([&] { pat_mix2<W, S><<<sms, W * 32>>>(d, in); }); \
+        printf("G2 8 DMMA + 16 DFMA %s warps/SM=%2d  %.3f ms  pipe cycles needed/elapsed = %.3f\n", S ? "spread " : "grouped", W, ms, \
+               (8 * 16.0 + 16 * 2.0) * ITERS * (W / 4.0) / (ms * 1e-3 * khz * 1e3)); }
+    RUN_G2(16, 0); RUN_G2(16, 1); RUN_G2(8, 0); RUN_G2(8, 1); RUN_G2(4, 0); RUN_G2(4, 1);
+#define RUN_E2(W, R) report(R ? "E2 DMMA distinct regs, restart" : "E2 DMMA distinct regs", 8.0 * 8 * ITERS, W, time_ms([&] { pat_dmma2<W, R><<<sms, W * 32>>>(d, in); }))
+    RUN_E2(16, 0); RUN_E2(16, 1); RUN_E2(8, 0); RUN_E2(8, 1);
+#define RUN_G3(W, CH) { double ms = time_ms([&] { pat_mix3<W, CH><<<sms, W * 32>>>(d, in); }); \
+        printf("G3 8 DMMA + 13 DFMA in %2d chains warps/SM=%2d  %.3f ms  pipe cycles needed/elapsed = %.3f\n", CH, W, ms, \
+               (8 * 16.0 + 13 * 2.0) * ITERS * (W / 4.0) / (ms * 1e-3 * khz * 1e3)); }
+    RUN_G3(16, 13); RUN_G3(16, 4); RUN_G3(16, 2); RUN_G3(16, 1); RUN_G3(8, 1); RUN_G3(12, 1);
+#define RUN_H(W, K) { double ms = time_ms([&] { pat_h<W, K><<<sms, W * 32>>>(d, in); }); \
+        printf("H warps/SM=%2d %-22s %.3f ms  pipe cycles needed/elapsed = %.3f\n", W, K == 0 ? "DMMA warps + DFMA warps" : K == 1 ? "DMMA warps only" : "DFMA warps only", ms, \
+               (K == 0 ? 2.0 : 1.0) * 8 * 16.0 * ITERS * (W / 8.0) / (ms * 1e-3 * khz * 1e3)); }
+    RUN_H(8, 1); RUN_H(8, 2); RUN_H(8, 0); RUN_H(16, 1); RUN_H(16, 2); RUN_H(16, 0);
     // rounding probe
     double ha[4] = {1.0 + 0x1p-30, 1.0 + 0x1p-31, 1.0 - 0x1p-29, 1.0 + 0x1p-33}, hb[4] = {1.0 + 0x1p-28, 1.0 - 0x1p-27, 1.0 + 0x1p-30, 1.0 - 0x1p-31};
     double *da, *db; cudaMalloc(&da, 32); cudaMalloc(&db, 32);
