@@ -64,7 +64,7 @@ ABI = {
     "baobzi_b200_version": (C.c_char_p, []),
 }
 DATA_SYMBOLS = ["baobzi_input_default"]
-MODES = {"auto": 0, "direct": 1, "binned": 2}
+MODES = {"auto": 0, "direct": 1, "binned": 2, "bucketed": 3}
 
 
 def library_path():
@@ -243,7 +243,8 @@ class Baobzi:
         if self._lib.baobzi_set_mode(self.ptr, m, int(chunk)) != 0:
             raise ValueError("bad mode")
 
-    STAGES = ("lookup", "scan", "scatter", "eval_binned", "eval_direct")
+    # "sort": fused lookup + scan + scatter (binned / bucketed paths); "scan", "scatter": only the unfused fallback
+    STAGES = ("sort", "scan", "scatter", "eval_grouped", "eval_direct")
 
     def profile_begin(self):
         self._lib.baobzi_profile_begin(self.ptr)

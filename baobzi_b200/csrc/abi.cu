@@ -45,7 +45,7 @@ struct Replica {
     BinWorkspace shard_ws;
 };
 
-enum Mode { kAuto = 0, kDirect = 1, kBinned = 2 };
+enum Mode { kAuto = 0, kDirect = 1, kBinned = 2, kBucketed = 3 };
 
 struct Function {
     HostTree host;
@@ -102,6 +102,8 @@ int env_mode() {
             return kDirect;
         if (!std::strcmp(s, "binned"))
             return kBinned;
+        if (!std::strcmp(s, "bucketed"))
+            return kBucketed;
     }
     return kAuto;
 }
@@ -162,7 +164,7 @@ void destroy_context(ExecContext &c) {
 bool use_binned(const Function *f, const DeviceTree &dt, int64_t n) {
     if (!binned_supported(dt.view.dim, dt.view.order))
         return false;
-    if (f->mode == kDirect)
+    if (f->mode == kDirect || f->mode == kBucketed)
         return false;
     if (f->mode == kBinned)
         return true;
@@ -170,6 +172,26 @@ bool use_binned(const Function *f, const DeviceTree &dt, int64_t n) {
     // there are enough points per leaf to fill warp tiles
     const int64_t block_bytes = 8 * (int64_t)std::pow((double)dt.view.order, dt.view.dim);
     return dt.view.dim == 3 && block_bytes >= 1024 && n >= 64 * (int64_t)dt.view.n_leaves && n >= (1 << 16);
+}
+
+// Bucketed path: when the tree (nodes + coefficients) is too big for L2 the direct kernel's gathers go to DRAM,
+// one or more sectors per level and per coefficient line; grouping the chunk's points by grid-cell bucket first
+// turns them into cache hits.
+bool use_bucketed(const Function *f, const DeviceTree &dt, int64_t n) {
+    if (f->mode == kBucketed)
+        return true;
+    if (f->mode != kAuto)
+        return false;
+    return dt.blob_bytes > (size_t(48) << 20) && n >= (1 << 20);
+}
+
+int64_t default_bucket_chunk() {
+    if (const char *s = std::getenv("BAOBZI_B200_BCHUNK")) {
+        long long v = std::atoll(s);
+        if (v > 0)
+            return v;
+    }
+    return int64_t(1) << 24; // measured best on the 1M-leaf benchmark tree: more points per leaf and chunk
 }
 
 // evaluate n device-resident points on `stream`, chunking the binned path
@@ -183,7 +205,7 @@ int eval_device(Function *f, Replica *r, BinWorkspace &ws, const double *d_x, do
         int64_t step = f->chunk > 0 ? f->chunk : default_chunk(r->dt);
         if (step > n)
             step = n;
-        if (ws.chunk_capacity < step) {
+        if (ws.chunk_capacity < step || ws.bucketed) {
             cudaStreamSynchronize(stream);
             free_workspace(ws);
             rc = alloc_workspace(r->dt, step, ws);
@@ -192,6 +214,19 @@ int eval_device(Function *f, Replica *r, BinWorkspace &ws, const double *d_x, do
         ws.prof = prof; // (re)attach: a reallocation starts from a fresh workspace
         if (rc == 0)
             rc = launch_eval_binned(r->dt, ws, d_x, d_res, n, stream, &launches); // chunks of ws.chunk_capacity
+    } else if (use_bucketed(f, r->dt, n)) {
+        int64_t step = f->chunk > 0 ? f->chunk : default_bucket_chunk();
+        if (step > n)
+            step = n;
+        if (ws.chunk_capacity < step || !ws.bucketed) {
+            cudaStreamSynchronize(stream);
+            free_workspace(ws);
+            rc = alloc_bucket_workspace(r->dt, step, ws);
+        }
+        ws.chunk_limit = step;
+        ws.prof = prof;
+        if (rc == 0)
+            rc = launch_eval_bucketed(r->dt, ws, d_x, d_res, n, stream, &launches);
     } else {
         rc = launch_eval_direct(r->dt, d_x, d_res, nullptr, n, stream, &launches, prof);
     }
@@ -574,7 +609,7 @@ int baobzi_sync(const baobzi_t func) {
 
 int baobzi_set_mode(baobzi_t func, int mode, int64_t chunk) {
     Function *f = (Function *)func->obj;
-    if (mode < 0 || mode > 2)
+    if (mode < 0 || mode > 3)
         return 1;
     f->mode = mode;
     f->chunk = chunk > 0 ? chunk : 0;

@@ -72,15 +72,18 @@ constexpr int kSortThreads = 512;
 constexpr size_t kFusedSortMaxSmem = 160 * 1024;
 constexpr int kSortPts = 4; // independent lookups in flight per thread (the lookup is latency bound, not issue bound)
 
-template <int DIM>
+// BYBIN (the bucketed path of large 1D / 2D trees): the key is the grid cell number >> bshift instead of the leaf,
+// so the sort touches no tree data; TILE is 1 and no tile descriptors are written (tile_info == nullptr).
+template <int DIM, bool BYBIN>
 __global__ void __launch_bounds__(kSortThreads)
 bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
                       uint32_t *__restrict__ key, uint32_t *__restrict__ count, uint32_t *__restrict__ count_next,
                       int cshift, uint32_t TILE, uint32_t *__restrict__ perm, uint32_t *__restrict__ tile_leaf,
-                      uint2 *__restrict__ tile_info, uint32_t *__restrict__ n_tiles, uint32_t n, uint32_t skey_cap) {
-    extern __shared__ uint32_t tbl[]; // [n_leaves] histogram -> base -> next free slot
+                      uint2 *__restrict__ tile_info, uint32_t *__restrict__ n_tiles, uint32_t n, uint32_t skey_cap,
+                      uint32_t n_keys, int bshift, uint32_t *__restrict__ key_start) {
+    extern __shared__ uint32_t tbl[]; // [n_keys] histogram -> base -> next free slot
     __shared__ uint32_t warp_sums[32];
-    const uint32_t nl = tv.n_leaves;
+    const uint32_t nl = n_keys;
     // keys of the CTA's own range as 16-bit leaf ranks in shared memory when they fit (skey_cap entries follow
     // tbl[]): the scatter then never goes back to global memory for them
     uint16_t *skey = reinterpret_cast<uint16_t *>(tbl + nl);
@@ -105,7 +108,9 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         uint32_t leaf[kSortPts];
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u)
-            leaf[u] = (!have[u] || outside<DIM>(tv, p[u])) ? kNotLeaf : locate_leaf<DIM>(tv, p[u]);
+            leaf[u] = (!have[u] || outside<DIM>(tv, p[u])) ? kNotLeaf
+                      : BYBIN                               ? linear_bin<DIM>(tv, p[u]) >> bshift
+                                                            : locate_leaf<DIM>(tv, p[u]);
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u) {
             if (!have[u])
@@ -165,21 +170,30 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         const uint32_t c = __ldcg(count + ((size_t)l << cshift));
         const uint32_t padded = (c + TILE - 1) / TILE * TILE;
         if (l % gridDim.x == blockIdx.x) { // this CTA's leaves: padding slots, tile descriptors, counter reset
-            for (uint32_t s = start + c; s < start + padded; ++s)
-                perm[s] = kInvalidSlot;
-            const uint32_t node = __ldg(tv.leaf_node + l);
-            const uint2 info = make_uint2(node, load_head(tv.nodes, node).coeff16);
-            for (uint32_t t = start / TILE; t < (start + padded) / TILE; ++t) {
-                tile_leaf[t] = l;
-                tile_info[t] = info;
+            if (!BYBIN) {
+                for (uint32_t s = start + c; s < start + padded; ++s)
+                    perm[s] = kInvalidSlot;
+                const uint32_t node = __ldg(tv.leaf_node + l);
+                const uint2 info = make_uint2(node, load_head(tv.nodes, node).coeff16);
+                for (uint32_t t = start / TILE; t < (start + padded) / TILE; ++t) {
+                    tile_leaf[t] = l;
+                    tile_info[t] = info;
+                }
             }
             count_next[(size_t)l << cshift] = 0; // the buffer the NEXT chunk histograms into
         }
+        if (BYBIN && blockIdx.x == 0)
+            key_start[l] = start; // first slot of every bucket, for the evaluation kernel
         tbl[l] += start;
         start += padded;
     }
-    if (blockIdx.x == 0 && tid == nthr - 1)
+    if (blockIdx.x == 0 && tid == nthr - 1) {
         *n_tiles = (warp_sums[nthr / 32 - 1]) / TILE;
+        if (BYBIN) {
+            key_start[nl] = warp_sums[nthr / 32 - 1];
+            n_tiles[1] = 0; // work queue of the evaluation kernel
+        }
+    }
     __syncthreads();
 
     // ---- scatter
@@ -328,7 +342,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     ws.sort_ctas = 0;
     if (ws.fused) { // cooperative launch: the grid is what is co-resident
         const size_t hist = (size_t)nl * sizeof(uint32_t);
-        cudaFuncSetAttribute(bin_sort_fused_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
+        cudaFuncSetAttribute(bin_sort_fused_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
         int want = 2;
         if (const char *e = std::getenv("BAOBZI_B200_SORT_CTAS"))
             if (std::atoi(e) > 0)
@@ -343,7 +357,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             cap = (cap + 7) / 8 * 8;
             const size_t smem = hist + (size_t)cap * sizeof(uint16_t);
             if (smem <= kFusedSortMaxSmem) {
-                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<3>, kSortThreads, smem);
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<3, false>, kSortThreads, smem);
                 if (per_sm >= want) {
                     per_sm = want;
                     ws.sort_skey = (uint32_t)cap;
@@ -352,7 +366,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             }
         }
         if (!ws.sort_skey) {
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<3>, kSortThreads, hist);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<3, false>, kSortThreads, hist);
             per_sm = per_sm < want ? per_sm : want;
         }
         ws.sort_ctas = dt.sm_count * per_sm;
@@ -369,7 +383,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         // its L2 traffic slows the evaluation by a third -- 18.1 ms per 2e8 points against 13.6 ms back to back.
         // Off by default; BAOBZI_B200_OVERLAP=1 enables it.
         if (ws.fused && ov && std::atoi(ov) != 0 && bin_eval_footprint(ws.variant, &k4_regs, &k4_smem) &&
-            cudaFuncGetAttributes(&sa, bin_sort_fused_kernel<3>) == cudaSuccess) {
+            cudaFuncGetAttributes(&sa, bin_sort_fused_kernel<3, false>) == cudaSuccess) {
             const int per_warp = (sa.numRegs * 32 + 511) / 512 * 512;
             int warps = (65536 - k4_regs) / per_warp;
             warps = warps > kSortThreads / 32 ? kSortThreads / 32 : warps;
@@ -501,10 +515,11 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         ws.flip = !ws.flip;
         TreeView tvv = tv;
         int cshift = ws.cshift;
-        uint32_t tile = TILE, nn = n, skey = 0;
+        uint32_t tile = TILE, nn = n, skey = 0, nkeys = tv.n_leaves;
+        int bshift = 0;
         void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
-                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey};
-        rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3>, dim3(grid), dim3(ws.sort_threads), args,
+                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start};
+        rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3, false>, dim3(grid), dim3(ws.sort_threads), args,
                                                    ws.sort_smem, ss);
         if (pf) {
             cudaEventRecord(ev[1], ss);
@@ -540,10 +555,11 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         ws.flip = !ws.flip;
         TreeView tvv = tv;
         int cshift = ws.cshift;
-        uint32_t tile = TILE, nn = n, skey = ws.sort_skey;
+        uint32_t tile = TILE, nn = n, skey = ws.sort_skey, nkeys = tv.n_leaves;
+        int bshift = 0;
         void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
-                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey};
-        rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3>, dim3(grid), dim3(ws.sort_threads), args,
+                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start};
+        rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3, false>, dim3(grid), dim3(ws.sort_threads), args,
                                                    ws.sort_smem, st);
         if (pf) { // the three classic stages are one launch here: all of it is booked under "lookup"
             cudaEventRecord(ev[1], st);
@@ -593,6 +609,142 @@ int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x
             *launches += ws.fused ? 2 : 5;
     }
     return rc; // every side-stream launch is an ancestor of the last evaluation on `stream`: the join is implicit
+}
+
+// ------------------------------------------------------------------------------------------ bucketed path
+template <int DIM>
+static int launch_bucket_sort(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, uint32_t n,
+                              cudaStream_t st) {
+    uint32_t grid = (uint32_t)ws.sort_ctas;
+    const uint32_t per_cta = (uint32_t)ws.sort_threads * kSortPts;
+    const uint32_t useful = (n + per_cta - 1) / per_cta;
+    grid = grid < useful ? grid : (useful ? useful : 1u);
+    uint32_t *cur = ws.flip ? ws.cursor : ws.count, *next = ws.flip ? ws.count : ws.cursor;
+    ws.flip = !ws.flip;
+    TreeView tvv = dt.view;
+    int cshift = ws.cshift, bshift = ws.bshift;
+    uint32_t tile = 1, nn = n, skey = ws.sort_skey, nkeys = ws.n_keys;
+    uint32_t *no_tile_leaf = nullptr;
+    uint2 *no_tile_info = nullptr;
+    void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
+                    &no_tile_leaf, &no_tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start};
+    return (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<DIM, true>, dim3(grid), dim3(ws.sort_threads),
+                                            args, ws.sort_smem, st);
+}
+
+template <int DIM>
+static int configure_bucket_sort(const DeviceTree &dt, BinWorkspace &ws, int64_t chunk) {
+    const size_t hist = (size_t)ws.n_keys * sizeof(uint32_t);
+    cudaFuncSetAttribute(bin_sort_fused_kernel<DIM, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
+    const int want = 2;
+    const int64_t range = (chunk + (int64_t)dt.sm_count * want - 1) / ((int64_t)dt.sm_count * want);
+    int64_t cap = range > kSortThreads * kSortPts ? range : kSortThreads * kSortPts;
+    cap = (cap + 7) / 8 * 8;
+    int per_sm = 0;
+    ws.sort_skey = 0;
+    ws.sort_smem = hist;
+    if (hist + (size_t)cap * sizeof(uint16_t) <= kFusedSortMaxSmem) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<DIM, true>, kSortThreads,
+                                                      hist + (size_t)cap * sizeof(uint16_t));
+        if (per_sm >= want) {
+            ws.sort_skey = (uint32_t)cap;
+            ws.sort_smem = hist + (size_t)cap * sizeof(uint16_t);
+        }
+    }
+    if (!ws.sort_skey)
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<DIM, true>, kSortThreads, hist);
+    per_sm = per_sm < want ? per_sm : want;
+    if (per_sm < 1)
+        return (int)cudaErrorInvalidConfiguration;
+    ws.sort_ctas = dt.sm_count * per_sm;
+    ws.sort_threads = kSortThreads;
+    return 0;
+}
+
+int alloc_bucket_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
+    if (chunk < 1)
+        chunk = 1;
+    if (chunk > 0x7FFFFFFFll)
+        chunk = 0x7FFFFFFFll;
+    ws.bucketed = true;
+    // at most kMaxBuckets buckets of 2^bshift consecutive grid cells (cells are x-fastest, nodes and coefficient
+    // blocks are stored cell by cell, so a bucket is one contiguous piece of the tree, small enough for L1)
+    uint64_t max_buckets = 4096;
+    if (const char *e = std::getenv("BAOBZI_B200_BUCKETS"))
+        if (std::atoll(e) > 0)
+            max_buckets = (uint64_t)std::atoll(e);
+    ws.bshift = 0;
+    while ((((uint64_t)dt.view.n_bins + (1ull << ws.bshift) - 1) >> ws.bshift) > max_buckets)
+        ws.bshift++;
+    ws.n_keys = (uint32_t)(((uint64_t)dt.view.n_bins + (1ull << ws.bshift) - 1) >> ws.bshift);
+    ws.cshift = 0;
+    ws.fused = true;
+    int rc = dt.view.dim == 1 ? configure_bucket_sort<1>(dt, ws, chunk)
+             : dt.view.dim == 2 ? configure_bucket_sort<2>(dt, ws, chunk)
+                                : configure_bucket_sort<3>(dt, ws, chunk);
+    if (rc)
+        return rc;
+    const size_t cwords = ws.n_keys + 1;
+    cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.perm, sizeof(uint32_t) * chunk);
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.count, sizeof(uint32_t) * cwords);
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.cursor, sizeof(uint32_t) * cwords);
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.n_tiles, 2 * sizeof(uint32_t));
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.start, sizeof(uint32_t) * (cwords + 1));
+    if (e == cudaSuccess)
+        e = cudaMemset(ws.count, 0, sizeof(uint32_t) * cwords);
+    if (e == cudaSuccess)
+        e = cudaMemset(ws.cursor, 0, sizeof(uint32_t) * cwords);
+    if (e != cudaSuccess) {
+        free_workspace(ws);
+        return (int)e;
+    }
+    ws.perm_capacity = chunk;
+    ws.chunk_capacity = chunk;
+    return 0;
+}
+
+int launch_eval_bucketed(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
+                         cudaStream_t stream, int64_t *launches) {
+    if (n <= 0)
+        return 0;
+    if (!ws.bucketed || ws.chunk_capacity <= 0)
+        return (int)cudaErrorInvalidValue;
+    const int dim = dt.view.dim;
+    const int64_t step = ws.chunk_limit > 0 && ws.chunk_limit < ws.chunk_capacity ? ws.chunk_limit : ws.chunk_capacity;
+    StageProfile *pf = ws.prof;
+    int rc = 0;
+    for (int64_t o = 0; o < n && rc == 0; o += step) {
+        const uint32_t m = (uint32_t)(n - o < step ? n - o : step);
+        const double *xc = d_x + dim * o;
+        double *rcp = d_res + o;
+        cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+        if (pf) {
+            for (auto &e : ev)
+                e = pf->get();
+            cudaEventRecord(ev[0], stream);
+        }
+        rc = dim == 1 ? launch_bucket_sort<1>(dt, ws, xc, rcp, m, stream)
+             : dim == 2 ? launch_bucket_sort<2>(dt, ws, xc, rcp, m, stream)
+                        : launch_bucket_sort<3>(dt, ws, xc, rcp, m, stream);
+        if (pf)
+            cudaEventRecord(ev[1], stream);
+        if (rc == 0)
+            rc = launch_eval_buckets(dt, xc, rcp, ws.perm, ws.start, ws.n_tiles + 1, ws.n_keys, ws.bshift, stream);
+        if (pf) {
+            cudaEventRecord(ev[2], stream);
+            pf->spans.push_back({kStageLookup, ev[0], ev[1], (int64_t)m});
+            pf->spans.push_back({kStageEval, ev[1], ev[2], (int64_t)m});
+        }
+        if (launches)
+            *launches += 2;
+    }
+    return rc;
 }
 
 } // namespace bz

@@ -25,10 +25,16 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
     // coefficient store: keep the reference's offsets when every block starts on a 16-byte boundary
     // (always the case for trees the reference writes: blocks are multiples of an even ORDER); otherwise
     // re-pack leaf by leaf.
+    // ... and ascend with the node order (true for files the reference writes: subtrees are fitted cell by cell), so
+    // that neighbouring leaves own neighbouring blocks -- the locality the bucketed path relies on
     bool aligned = true;
+    uint64_t prev_off = 0;
     for (size_t g = 0; g < nn; ++g)
-        if (h.is_leaf((int64_t)g) && (h.coeff_offset[g] & 1))
-            aligned = false;
+        if (h.is_leaf((int64_t)g)) {
+            if ((h.coeff_offset[g] & 1) || h.coeff_offset[g] < prev_off)
+                aligned = false;
+            prev_off = h.coeff_offset[g];
+        }
     std::vector<double> packed;
     std::vector<uint64_t> new_off;
     const std::vector<double> *coeffs = &h.coeffs;
@@ -55,10 +61,11 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
 
     std::vector<NodeRec> recs(nn);
     std::vector<uint32_t> leaf_node;
-    std::vector<uint32_t> bin_root(nb), bin_leaf(nb, kNotLeaf);
+    std::vector<uint32_t> bin_root(nb), bin_leaf(nb, kNotLeaf), bin_first_leaf(nb + 1, 0);
     for (size_t s = 0; s < nb; ++s) {
         const uint32_t b = h.subtree_begin[s], e = h.subtree_begin[s + 1];
         bin_root[s] = b;
+        bin_first_leaf[s] = (uint32_t)leaf_node.size();
         for (uint32_t g = b; g < e; ++g) {
             NodeRec &r = recs[g];
             std::memset(&r, 0, sizeof r);
@@ -83,12 +90,14 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
         }
     }
 
+    bin_first_leaf[nb] = (uint32_t)leaf_node.size();
     // one allocation, 256-byte aligned sections: nodes | bin_root | bin_leaf | leaf_node | coeffs (+ 32 KB of zero
     // slack so that vector loads near the end of the last block never leave the allocation)
     const size_t off_nodes = 0;
     const size_t off_bins = align_up(off_nodes + nn * sizeof(NodeRec), 256);
     const size_t off_binl = align_up(off_bins + nb * sizeof(uint32_t), 256);
-    const size_t off_leaf = align_up(off_binl + nb * sizeof(uint32_t), 256);
+    const size_t off_binf = align_up(off_binl + nb * sizeof(uint32_t), 256);
+    const size_t off_leaf = align_up(off_binf + (nb + 1) * sizeof(uint32_t), 256);
     const size_t off_coef = align_up(off_leaf + leaf_node.size() * sizeof(uint32_t), 256);
     const size_t total = align_up(off_coef + coeffs->size() * sizeof(double) + 32768, 256);
 
@@ -108,6 +117,8 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
         e = cudaMemcpy(base + off_bins, bin_root.data(), nb * sizeof(uint32_t), cudaMemcpyHostToDevice);
     if (e == cudaSuccess)
         e = cudaMemcpy(base + off_binl, bin_leaf.data(), nb * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess)
+        e = cudaMemcpy(base + off_binf, bin_first_leaf.data(), (nb + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice);
     if (e == cudaSuccess && !leaf_node.empty())
         e = cudaMemcpy(base + off_leaf, leaf_node.data(), leaf_node.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
     if (e == cudaSuccess && !coeffs->empty())
@@ -138,6 +149,7 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
     v.nodes = reinterpret_cast<const NodeRec *>(base + off_nodes);
     v.bin_root = reinterpret_cast<const uint32_t *>(base + off_bins);
     v.bin_leaf = reinterpret_cast<const uint32_t *>(base + off_binl);
+    v.bin_first_leaf = reinterpret_cast<const uint32_t *>(base + off_binf);
     v.leaf_node = reinterpret_cast<const uint32_t *>(base + off_leaf);
     v.coeffs = reinterpret_cast<const double *>(base + off_coef);
     return 0;

@@ -52,6 +52,7 @@ struct TreeView {
     const NodeRec *nodes;
     const double *coeffs;
     const uint32_t *leaf_node;
+    const uint32_t *bin_first_leaf; // [n_bins + 1] dense rank of the first leaf of each grid cell's subtree
 };
 
 // Optional per-launch timing (bench.py's roofline): when attached to a workspace / launch, every kernel is
@@ -101,6 +102,9 @@ struct BinWorkspace {
     // Overlap of the (memory / latency bound) sort of chunk c+1 with the (FP64 bound) evaluation of chunk c: the
     // sort runs on its own stream into the second set of buffers below, sized to be co-resident with the
     // evaluation kernel's CTAs (binned.cu: launch_eval_binned).
+    bool bucketed = false;      // workspace of the bucketed path (alloc_bucket_workspace)
+    uint32_t n_keys = 0;        // buckets
+    int bshift = 0;             // bucket = grid cell >> bshift
     bool overlap = false, sort_overlap_ok = false;
     int sort_threads = 0;
     cudaStream_t sort_stream = nullptr;
@@ -138,6 +142,15 @@ int launch_eval_scalar(const DeviceTree &dt, const double *d_x, double *d_y, cud
 // Binned path over n points in chunks of ws.chunk_capacity: sort by leaf (lookup+histogram, padded scan, scatter), evaluation.
 int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
                        cudaStream_t stream, int64_t *launches);
+// Bucketed path (trees whose nodes + coefficients do not fit in L2, any dim): points of a chunk are grouped by
+// grid-cell bucket with the fused sort kernel (key = cell >> shift, no tree access), then evaluated in that order.
+int alloc_bucket_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws);
+int launch_eval_bucketed(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
+                         cudaStream_t stream, int64_t *launches);
+int launch_eval_buckets(const DeviceTree &dt, const double *d_x, double *d_res, const uint32_t *d_perm,
+                        const uint32_t *d_key_start, uint32_t *d_queue, uint32_t n_keys, int bshift, cudaStream_t stream);
+int launch_eval_perm(const DeviceTree &dt, const double *d_x, double *d_res, const uint32_t *d_perm,
+                     const uint32_t *d_n_slots, int64_t n_max, cudaStream_t stream);
 // true when the binned path is implemented for this (dim, order)
 bool binned_supported(int dim, int order);
 

@@ -72,6 +72,149 @@ eval_direct_kernel(const TreeView tv, const double *__restrict__ x, double *__re
     }
 }
 
+// ------------------------------------------------------------------------------------------ bucketed
+// Evaluation in the order of a permutation (binned.cu: points grouped by grid-cell bucket).  Consecutive
+// threads then walk the same few subtrees and read neighbouring coefficient blocks, so the node and
+// coefficient gathers of a tree that does not fit in L2 become L1 / L2 hits instead of DRAM sectors; the
+// point itself is the only random access left (one 32-byte sector inside the L2-resident chunk).
+constexpr int kPermThreads = 256;
+template <int DIM, int ORDER>
+__global__ void __launch_bounds__(kPermThreads)
+eval_perm_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                 const uint32_t *__restrict__ perm, const uint32_t *__restrict__ n_slots_p) {
+    // every CTA walks ONE contiguous range of slots, i.e. a few buckets one after the other: the bucket's nodes and
+    // coefficient blocks are fetched from L2 once and then hit in this SM's L1
+    const uint32_t n_slots = __ldg(n_slots_p);
+    const uint32_t lo = (uint32_t)(((uint64_t)blockIdx.x * n_slots) / gridDim.x);
+    const uint32_t hi = (uint32_t)(((uint64_t)(blockIdx.x + 1) * n_slots) / gridDim.x);
+    for (uint32_t s = lo + threadIdx.x; s < hi; s += blockDim.x) {
+        const uint32_t i = __ldcs(perm + s);
+        double p[DIM];
+        load_point_keep<DIM>(x, i, p);
+        NodeHead head;
+        const uint32_t node = locate<DIM>(tv, p, head);
+        res[i] = eval_leaf<DIM, ORDER>(tv, node, head, p);
+    }
+}
+
+// Bucket by bucket with a CTA-local counting sort by leaf: a bucket (a few grid cells) is taken from a work queue,
+// its points are looked up, sorted by leaf in shared memory and evaluated in that order, so that the lanes of a
+// warp sit in very few leaves and a coefficient load touches very few L1 lines.  (Thread per point in bucket order
+// alone is bound by the L1 tag rate: 32 lanes x 16 bytes out of 32 different blocks per load, ncu in profiles/.)
+constexpr int kBktThreads = 256, kBktBatch = 1024, kBktMaxLeaves = 2048;
+
+template <int DIM, int ORDER>
+__global__ void __launch_bounds__(kBktThreads)
+eval_bucket_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                   const uint32_t *__restrict__ perm, const uint32_t *__restrict__ key_start, uint32_t *__restrict__ queue,
+                   uint32_t n_keys, int bshift) {
+    __shared__ double pts[DIM][kBktBatch];
+    __shared__ uint32_t idx[kBktBatch], nodes[kBktBatch];
+    __shared__ uint16_t order[kBktBatch];
+    __shared__ uint32_t hist[kBktMaxLeaves];
+    __shared__ uint32_t warp_sums[kBktThreads / 32];
+    __shared__ uint32_t next_bucket;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int PER = kBktBatch / kBktThreads;       // points per thread and batch
+    constexpr int HPER = kBktMaxLeaves / kBktThreads;  // histogram entries per thread in the scan
+    for (;;) {
+        __syncthreads();
+        if (tid == 0)
+            next_bucket = atomicAdd(queue, 1u);
+        __syncthreads();
+        const uint32_t b = next_bucket;
+        if (b >= n_keys)
+            break;
+        const uint32_t s0 = __ldg(key_start + b), s1 = __ldg(key_start + b + 1);
+        if (s0 == s1)
+            continue;
+        const uint32_t bin0 = b << bshift;
+        const uint32_t bin1 = min(bin0 + (1u << bshift), tv.n_bins);
+        const uint32_t leaf0 = __ldg(tv.bin_first_leaf + bin0);
+        const uint32_t n_local = __ldg(tv.bin_first_leaf + bin1) - leaf0;
+        const bool sorted = n_local <= (uint32_t)kBktMaxLeaves; // CTA uniform
+        for (uint32_t bs = s0; bs < s1; bs += kBktBatch) {
+            const uint32_t m = min((uint32_t)kBktBatch, s1 - bs);
+            if (sorted)
+                for (uint32_t l = tid; l < n_local; l += kBktThreads)
+                    hist[l] = 0;
+            __syncthreads();
+            uint32_t lkey[PER], rank[PER];
+#pragma unroll
+            for (int u = 0; u < PER; ++u) {
+                const uint32_t t = tid + u * kBktThreads;
+                lkey[u] = 0xFFFFFFFFu;
+                if (t < m) {
+                    const uint32_t i = __ldcs(perm + bs + t);
+                    double p[DIM];
+                    load_point_keep<DIM>(x, i, p);
+#pragma unroll
+                    for (int j = 0; j < DIM; ++j)
+                        pts[j][t] = p[j];
+                    idx[t] = i;
+                    NodeHead head;
+                    const uint32_t node = locate<DIM>(tv, p, head);
+                    nodes[t] = node;
+                    if (sorted) {
+                        lkey[u] = load_tail(tv.nodes, node).leaf_rank - leaf0;
+                        rank[u] = atomicAdd(hist + lkey[u], 1u);
+                    } else {
+                        order[t] = (uint16_t)t;
+                    }
+                }
+            }
+            __syncthreads();
+            if (sorted) { // exclusive scan of hist[0, n_local)
+                uint32_t v[HPER], sum = 0;
+#pragma unroll
+                for (int e = 0; e < HPER; ++e) {
+                    const uint32_t l = tid * HPER + e;
+                    v[e] = l < n_local ? hist[l] : 0u;
+                    sum += v[e];
+                }
+                uint32_t incl = sum;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o)
+                        incl += y;
+                }
+                if (lane == 31)
+                    warp_sums[warp] = incl;
+                __syncthreads();
+                uint32_t base = incl - sum;
+                for (uint32_t w = 0; w < warp; ++w)
+                    base += warp_sums[w];
+#pragma unroll
+                for (int e = 0; e < HPER; ++e) {
+                    const uint32_t l = tid * HPER + e;
+                    if (l < n_local)
+                        hist[l] = base;
+                    base += v[e];
+                }
+                __syncthreads();
+#pragma unroll
+                for (int u = 0; u < PER; ++u)
+                    if (lkey[u] != 0xFFFFFFFFu)
+                        order[hist[lkey[u]] + rank[u]] = (uint16_t)(tid + u * kBktThreads);
+                __syncthreads();
+            }
+#pragma unroll 1
+            for (uint32_t t = tid; t < m; t += kBktThreads) {
+                const uint32_t j = order[t];
+                double p[DIM];
+#pragma unroll
+                for (int d = 0; d < DIM; ++d)
+                    p[d] = pts[d][j];
+                const uint32_t node = nodes[j];
+                const NodeHead head = load_head(tv.nodes, node);
+                res[idx[j]] = eval_leaf<DIM, ORDER>(tv, node, head, p);
+            }
+            __syncthreads();
+        }
+    }
+}
+
 // Scalar twin (template.hpp:851-860 -> Node::eval(x, res, coeffs) 371-375): out_dim values, block k of
 // ORDER... the reference indexes `coeffs + coeff_offset + k*ORDER` for every DIM; only DIM == 1 is
 // meaningful and for DIM > 1 we evaluate component 0 only.
@@ -143,6 +286,25 @@ int launch_eval_direct(const DeviceTree &dt, const double *d_x, double *d_res, i
     }
     if (launches)
         *launches += 1;
+    return (int)cudaGetLastError();
+}
+
+int launch_eval_perm(const DeviceTree &dt, const double *d_x, double *d_res, const uint32_t *d_perm,
+                     const uint32_t *d_n_slots, int64_t n_max, cudaStream_t stream) {
+    const int64_t want = (n_max + kPermThreads - 1) / kPermThreads;
+    const int64_t cap = (int64_t)dt.sm_count * 4;
+    const unsigned grid = (unsigned)(want < cap ? (want > 0 ? want : 1) : cap);
+    BZ_DISPATCH(dt.view.dim, dt.view.order,
+                (eval_perm_kernel<D, O><<<grid, kPermThreads, 0, stream>>>(dt.view, d_x, d_res, d_perm, d_n_slots)));
+    return (int)cudaGetLastError();
+}
+
+int launch_eval_buckets(const DeviceTree &dt, const double *d_x, double *d_res, const uint32_t *d_perm,
+                        const uint32_t *d_key_start, uint32_t *d_queue, uint32_t n_keys, int bshift, cudaStream_t stream) {
+    const unsigned grid = (unsigned)dt.sm_count * 6;
+    BZ_DISPATCH(dt.view.dim, dt.view.order,
+                (eval_bucket_kernel<D, O><<<grid, kBktThreads, 0, stream>>>(dt.view, d_x, d_res, d_perm, d_key_start, d_queue,
+                                                                          n_keys, bshift)));
     return (int)cudaGetLastError();
 }
 

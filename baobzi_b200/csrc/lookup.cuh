@@ -84,6 +84,22 @@ __device__ __forceinline__ uint32_t locate(const TreeView &tv, const double (&x)
     return node;
 }
 
+// get_linear_bin alone (template.hpp:799-820), clamped like locate(): the key of the bucketed path, which needs
+// no tree access at all.
+template <int DIM>
+__device__ __forceinline__ uint32_t linear_bin(const TreeView &tv, const double (&x)[DIM]) {
+    int lin = 0, stride = 1;
+#pragma unroll
+    for (int j = 0; j < DIM; ++j) {
+        const double xb = __dsub_rn(x[j], tv.lower_left[j]);
+        int b = __double2int_rz(__dmul_rn(xb, tv.inv_bin_size[j]));
+        b = min(max(b, 0), tv.n_sub[j] - 1);
+        lin += stride * b;
+        stride *= tv.n_sub[j];
+    }
+    return (uint32_t)lin;
+}
+
 // Same walk, but only the dense leaf rank is returned.  Undivided grid cells (every cell of a tree whose fit
 // never refined past the grid, e.g. the 3D benchmark trees) are answered by the bin_leaf table alone; otherwise
 // every step fetches the whole 64-byte record (both sectors of one line in a single round trip): one dependent

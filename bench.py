@@ -401,7 +401,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--points", type=int, default=0, help="points per GPU (default: the workload's)")
-    ap.add_argument("--mode", default="", choices=["", "auto", "direct", "binned"])
+    ap.add_argument("--mode", default="", choices=["", "auto", "direct", "binned", "bucketed"])
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

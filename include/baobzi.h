@@ -135,7 +135,8 @@ int baobzi_sync(const baobzi_t func);
 
 /* Tuning knobs (also readable from the environment at init/restore):
  *   mode: 0 = auto, 1 = direct (one fused kernel, thread per point), 2 = binned (points grouped by leaf in
- *   L2-resident chunks before a register-blocked evaluation).  BAOBZI_B200_MODE=auto|direct|binned.
+ *   L2-resident chunks before a register-blocked evaluation), 3 = bucketed (points grouped by grid-cell bucket
+ *   before a thread-per-point evaluation: trees larger than L2).  BAOBZI_B200_MODE=auto|direct|binned|bucketed.
  *   chunk: points per binned chunk (0 = default).  BAOBZI_B200_CHUNK. */
 int baobzi_set_mode(baobzi_t func, int mode, int64_t chunk);
 

@@ -32,7 +32,7 @@ def test_golden_host_pointers(gpu_lib, ref, name):
 
 
 @pytest.mark.parametrize("name", golden_cases())
-@pytest.mark.parametrize("mode", ["direct", "binned"])
+@pytest.mark.parametrize("mode", ["direct", "binned", "bucketed"])
 def test_golden_device_pointers(gpu_lib, ref, name, mode):
     import torch
     path, g = load_golden(name)
@@ -64,7 +64,7 @@ def test_ragged_sizes_and_modes(gpu_lib, ref, name, n):
     assert ulp(ref, b(x), want) == 0
     if n:
         xd = torch.from_numpy(x).cuda()
-        for mode, chunk in (("direct", 0), ("binned", 0), ("binned", 1000), ("binned", 4097)):
+        for mode, chunk in (("direct", 0), ("binned", 0), ("binned", 1000), ("binned", 4097), ("bucketed", 0), ("bucketed", 999)):
             b.set_mode(mode, chunk)
             yd = b(xd)
             torch.cuda.synchronize()
