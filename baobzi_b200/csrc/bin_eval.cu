@@ -289,7 +289,7 @@ __device__ __forceinline__ void pick_t(const double (&T)[8], uint32_t t, double 
 }
 __device__ __forceinline__ double shfl_xor_d(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
 
-template <int WARPS, int EXP = 0, bool ROLLED = false>
+template <int WARPS, bool DEFER>
 __global__ void __launch_bounds__(WARPS * 32, 1)
 bin_eval3d_mma8_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
                        const uint32_t *__restrict__ perm, const uint2 *__restrict__ tile_info,
@@ -299,9 +299,6 @@ bin_eval3d_mma8_kernel(const TreeView tv, const double *__restrict__ x, double *
     const uint32_t n_tiles = __ldg(n_tiles_p);
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
     MmaStage *stages = reinterpret_cast<MmaStage *>(smem_raw) + 2 * warp;
-    // ROLLED: the B fragments live in shared memory ([slab][kb][lane], conflict-free 256-byte rows) and the slab loop
-    // is not unrolled, so that every slab is one uninterrupted run of 8 DMMAs followed by its reduction
-    double *sB = reinterpret_cast<double *>(smem_raw + sizeof(MmaStage) * 2 * WARPS) + 512 * warp;
     // contiguous run of tiles per warp: a leaf's tiles are adjacent, so its coefficients are fetched once per run
     const uint32_t nw = gridDim.x * WARPS, wid = blockIdx.x * WARPS + warp;
     const uint32_t t_begin = (uint32_t)(((uint64_t)n_tiles * wid) / nw), t_end = (uint32_t)(((uint64_t)n_tiles * (wid + 1)) / nw);
@@ -336,11 +333,9 @@ bin_eval3d_mma8_kernel(const TreeView tv, const double *__restrict__ x, double *
     int cur = 0;
     for (uint32_t tt = t_begin; tt < t_end; ++tt, cur ^= 1) {
         __syncwarp(); // every lane is done reading stage cur^1
-        if (EXP != 3 || tt < t_begin + 2) {
-            issue(idx_n, stages[cur ^ 1]);
-            load_meta(tt + 2, idx_n);
-        }
-        const uint2 info = EXP == 3 && tt > t_begin ? make_uint2(cur_node, 0) : __ldg(tile_info + tt);
+        issue(idx_n, stages[cur ^ 1]);
+        load_meta(tt + 2, idx_n);
+        const uint2 info = __ldg(tile_info + tt);
         if (info.x != cur_node) { // warp uniform
             cur_node = info.x;
             const double *C = tv.coeffs + 2ull * info.y;
@@ -349,15 +344,6 @@ bin_eval3d_mma8_kernel(const TreeView tv, const double *__restrict__ x, double *
 #pragma unroll
                 for (int kb = 0; kb < 2; ++kb)
                     breg[i][kb] = __ldg(C + i * 64 + (4 * kb + t) * 8 + brow);
-            if (ROLLED) {
-                __syncwarp();
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-#pragma unroll
-                    for (int kb = 0; kb < 2; ++kb)
-                        sB[(i * 2 + kb) * 32 + lane] = breg[i][kb];
-                __syncwarp();
-            }
             const NodeHead head = load_head(tv.nodes, info.x);
             const NodeTail tail = load_tail(tv.nodes, info.x);
             c0 = head.c0, c1 = head.c1, c2 = head.c2;
@@ -375,35 +361,32 @@ bin_eval3d_mma8_kernel(const TreeView tv, const double *__restrict__ x, double *
                 const int q = base + 8 * j + g;
                 const double v = __dmul_rn(__dsub_rn(st.pts[1 * TILE + q], c1), ih1);
                 const double w = __dmul_rn(__dsub_rn(st.pts[2 * TILE + q], c2), ih2);
-                if (EXP == 2) { // timing experiment: no recurrences
-                    a0[j] = w, a1[j] = v, ya[j] = w, yb[j] = v;
-                } else {
                 double T[8];
                 cheb_T<8>(w, T);
                 pick_t(T, t, a0[j], a1[j]);
                 cheb_T<8>(v, T);
                 pick_t(T, t, ya[j], yb[j]);
-                }
             }
             const int own = base + 8 * t + g; // this lane's own point: group t
             const double u = __dmul_rn(__dsub_rn(st.pts[0 * TILE + own], c0), ih0);
             const double x2 = __dadd_rn(u, u);
             double tx = 1.0, tx_prev = u, val = 0.0;
             const bool low = t < 2, odd = t & 1;
-#pragma unroll ROLLED ? 1 : 8
+            // DEFER: the slab loop only produces the lane-local pair sums l (independent two-deep chains that trail
+            // the DMMAs); the quad reduction of all 8 slabs is done afterwards in wide, independent batches, so that
+            // no short dependent FP64 chain sits between the DMMAs of consecutive slabs
+            double keep0[DEFER ? 8 : 1], keep1[DEFER ? 8 : 1], send0[DEFER ? 8 : 1], send1[DEFER ? 8 : 1];
+#pragma unroll
             for (int i = 0; i < 8; ++i) {
-                double l[4];
-                const double b0 = ROLLED ? sB[(i * 2 + 0) * 32 + lane] : breg[i][0];
-                const double b1 = ROLLED ? sB[(i * 2 + 1) * 32 + lane] : breg[i][1];
-                double d0[4], d1[4];
+                double l[4], d0[4], d1[4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     d0[j] = d1[j] = -0.0;
-                    dmma8(d0[j], d1[j], a0[j], b0);
+                    dmma8(d0[j], d1[j], a0[j], breg[i][0]);
                 }
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
-                    dmma8(d0[j], d1[j], a1[j], b1);
+                    dmma8(d0[j], d1[j], a1[j], breg[i][1]);
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                     l[j] = __dmul_rn(ya[j], d0[j]);
@@ -411,18 +394,37 @@ bin_eval3d_mma8_kernel(const TreeView tv, const double *__restrict__ x, double *
                 for (int j = 0; j < 4; ++j)
                     l[j] = __fma_rn(yb[j], d1[j], l[j]); // rows t and t + 4 of point (j, g)
                 // (l0 + l2) + (l1 + l3) over the quad; groups 0,1 are finished on lanes t < 2, groups 2,3 on t >= 2
-                double d;
-                if (EXP == 1) { // timing experiment: no shuffles / selects
-                    d = __dadd_rn(__dadd_rn(l[0], l[2]), __dadd_rn(l[1], l[3]));
+                if constexpr (DEFER) {
+                    keep0[i] = low ? l[0] : l[2], keep1[i] = low ? l[1] : l[3];
+                    send0[i] = low ? l[2] : l[0], send1[i] = low ? l[3] : l[1];
                 } else {
-                const double r0 = shfl_xor_d(low ? l[2] : l[0], 2), r1 = shfl_xor_d(low ? l[3] : l[1], 2);
-                const double s0 = __dadd_rn(low ? l[0] : l[2], r0), s1 = __dadd_rn(low ? l[1] : l[3], r1);
-                d = __dadd_rn(odd ? s1 : s0, shfl_xor_d(odd ? s0 : s1, 1)); // lane t: point (t, g)
+                    const double r0 = shfl_xor_d(low ? l[2] : l[0], 2), r1 = shfl_xor_d(low ? l[3] : l[1], 2);
+                    const double s0 = __dadd_rn(low ? l[0] : l[2], r0), s1 = __dadd_rn(low ? l[1] : l[3], r1);
+                    const double d = __dadd_rn(odd ? s1 : s0, shfl_xor_d(odd ? s0 : s1, 1)); // lane t: point (t, g)
+                    val = __fma_rn(tx, d, val);
+                    const double tn = __fma_rn(x2, tx, -tx_prev);
+                    tx_prev = tx;
+                    tx = tn;
                 }
-                val = __fma_rn(tx, d, val);
-                const double tn = __fma_rn(x2, tx, -tx_prev);
-                tx_prev = tx;
-                tx = tn;
+            }
+            if constexpr (DEFER) {
+                double s0[8], s1[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    s0[i] = __dadd_rn(keep0[i], shfl_xor_d(send0[i], 2));
+                    s1[i] = __dadd_rn(keep1[i], shfl_xor_d(send1[i], 2));
+                }
+                double d[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    d[i] = __dadd_rn(odd ? s1[i] : s0[i], shfl_xor_d(odd ? s0[i] : s1[i], 1));
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    val = __fma_rn(tx, d[i], val);
+                    const double tn = __fma_rn(x2, tx, -tx_prev);
+                    tx_prev = tx;
+                    tx = tn;
+                }
             }
             const uint32_t id = st.idx[own];
             if (id != kInvalidSlotE)
@@ -432,10 +434,10 @@ bin_eval3d_mma8_kernel(const TreeView tv, const double *__restrict__ x, double *
     cp_async_wait<0>();
 }
 
-template <int WARPS, int EXP = 0, bool ROLLED = false>
+template <int WARPS, bool DEFER>
 static int launch_k4_mma8(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
-    auto kern = bin_eval3d_mma8_kernel<WARPS, EXP, ROLLED>;
-    constexpr size_t smem = sizeof(MmaStage) * 2 * WARPS + (ROLLED ? 4096 * WARPS : 0);
+    auto kern = bin_eval3d_mma8_kernel<WARPS, DEFER>;
+    constexpr size_t smem = sizeof(MmaStage) * 2 * WARPS;
     static bool configured = false;
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -475,12 +477,14 @@ static int launch_k4(const DeviceTree &dt, const BinWorkspace &ws, const double 
 #define BZ_K4(O_, P_, W_, F_, Y_)                                                                                      \
     {O_, P_, W_, F_, Y_, launch_k4<O_, P_, W_, F_, Y_>, (const void *)bin_eval3d_kernel<O_, P_, W_, F_, Y_>,           \
      sizeof(PipeStage<O_, P_>) * 2 * W_}
-#define BZ_K4M(W_) {8, 4, W_, true, true, launch_k4_mma8<W_>, (const void *)bin_eval3d_mma8_kernel<W_>, sizeof(MmaStage) * 2 * W_}
+#define BZ_K4M(W_, D_)                                                                                                 \
+    {8, D_ ? 5 : 4, W_, true, true, launch_k4_mma8<W_, D_>, (const void *)bin_eval3d_mma8_kernel<W_, D_>, sizeof(MmaStage) * 2 * W_}
 // first entry of an order = its default
 static const K4Variant kVariants[] = {
     BZ_K4(6, 4, 8, false, true),   BZ_K4(6, 4, 12, false, true),  BZ_K4(6, 4, 16, false, false),
     BZ_K4(8, 4, 8, false, true),   BZ_K4(8, 4, 8, false, false),
-    BZ_K4M(16), BZ_K4M(12), BZ_K4M(8), // tzfly && tykeep together = the DMMA kernel  BZ_K4(8, 3, 12, false, false),
+    // tzfly && tykeep together = the DMMA kernel (P = 5 in the selector: deferred quad reduction)
+    BZ_K4M(16, false), BZ_K4M(12, false), BZ_K4M(8, false), BZ_K4M(16, true), BZ_K4M(12, true), BZ_K4M(8, true),  BZ_K4(8, 3, 12, false, false),
     BZ_K4(8, 3, 12, false, true),  BZ_K4(8, 4, 12, true, false),  BZ_K4(8, 2, 16, false, false),
     BZ_K4(8, 2, 16, false, true),  BZ_K4(8, 3, 8, false, true),
     BZ_K4(10, 2, 8, false, true),  BZ_K4(10, 3, 8, false, false), BZ_K4(10, 4, 8, true, false),
@@ -488,9 +492,6 @@ static const K4Variant kVariants[] = {
     BZ_K4(14, 2, 4, false, true),  BZ_K4(14, 3, 4, true, false),
     BZ_K4(16, 2, 2, false, true),  BZ_K4(16, 2, 3, false, false),
 #ifdef BZ_EXPERIMENTS // timing experiments with WRONG results: P = 91 / 92 select them
-    {8, 96, 16, true, true, launch_k4_mma8<16, 0, true>, nullptr, 0}, {8, 97, 12, true, true, launch_k4_mma8<12, 0, true>, nullptr, 0},
-    {8, 98, 8, true, true, launch_k4_mma8<8, 0, true>, nullptr, 0},
-    {8, 93, 16, true, true, launch_k4_mma8<16, 1>, nullptr, 0}, {8, 94, 16, true, true, launch_k4_mma8<16, 2>, nullptr, 0}, {8, 95, 16, true, true, launch_k4_mma8<16, 3>, nullptr, 0},
     {8, 91, 8, false, true, launch_k4<8, 4, 8, false, true, 1>, nullptr, 0}, {8, 92, 8, false, true, launch_k4<8, 4, 8, false, true, 2>, nullptr, 0},
     {8, 91, 12, false, false, launch_k4<8, 3, 12, false, false, 1>, nullptr, 0}, {8, 92, 12, false, false, launch_k4<8, 3, 12, false, false, 2>, nullptr, 0},
 #endif
@@ -521,7 +522,7 @@ int bin_eval_select(int order, int *P) {
     }
     if (!v)
         return -1;
-    *P = v->P > 90 ? (v->warps == 12 && v->P < 93 ? 3 : 4) : v->P;
+    *P = v->P > 90 ? (v->warps == 12 ? 3 : 4) : (v->P == 5 ? 4 : v->P);
     return (int)(v - kVariants);
 }
 

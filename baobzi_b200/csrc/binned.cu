@@ -80,13 +80,18 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
                       uint32_t *__restrict__ key, uint32_t *__restrict__ count, uint32_t *__restrict__ count_next,
                       int cshift, uint32_t TILE, uint32_t *__restrict__ perm, uint32_t *__restrict__ tile_leaf,
                       uint2 *__restrict__ tile_info, uint32_t *__restrict__ n_tiles, uint32_t n, uint32_t skey_cap,
-                      uint32_t n_keys, int bshift, uint32_t *__restrict__ key_start) {
+                      uint32_t n_keys, int bshift, uint32_t *__restrict__ key_start, uint32_t coal_cap) {
     extern __shared__ uint32_t tbl[]; // [n_keys] histogram -> base -> next free slot
     __shared__ uint32_t warp_sums[32];
     const uint32_t nl = n_keys;
     // keys of the CTA's own range as 16-bit leaf ranks in shared memory when they fit (skey_cap entries follow
     // tbl[]): the scatter then never goes back to global memory for them
     uint16_t *skey = reinterpret_cast<uint16_t *>(tbl + nl);
+    // coal_cap > 0: the scatter goes through a CTA-local counting sort in shared memory (cnt[], loc[], sorted[] follow
+    // tbl[]), and the CTA's run of every leaf leaves as ONE merged store per 8 slots instead of one 4-byte store per
+    // point (the scattered 4-byte stores were 40 % of this kernel: L2 takes them one partial sector at a time)
+    uint32_t *cnt = tbl + nl, *loc = cnt + nl;
+    uint16_t *sorted = reinterpret_cast<uint16_t *>(loc + nl + 1);
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     for (uint32_t l = tid; l < nl; l += nthr)
         tbl[l] = 0;
@@ -94,6 +99,7 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     const uint32_t lo = (uint32_t)(((uint64_t)blockIdx.x * n) / gridDim.x);
     const uint32_t hi = (uint32_t)(((uint64_t)(blockIdx.x + 1) * n) / gridDim.x);
     const bool use_skey = hi - lo <= skey_cap; // CTA uniform
+    const bool coalesce = coal_cap > 0 && hi - lo <= coal_cap;
 
     // ---- phase A
     for (uint32_t i0 = lo + tid; i0 < hi; i0 += kSortPts * nthr) {
@@ -105,18 +111,25 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
             have[u] = i < hi;
             load_point_keep<DIM>(x, have[u] ? i : i0, p[u]); // default cache policy: K4 gathers these again
         }
-        uint32_t leaf[kSortPts];
+        uint32_t leaf[kSortPts], lin[kSortPts];
 #pragma unroll
-        for (int u = 0; u < kSortPts; ++u)
-            leaf[u] = (!have[u] || outside<DIM>(tv, p[u])) ? kNotLeaf
-                      : BYBIN                               ? linear_bin<DIM>(tv, p[u]) >> bshift
-                                                            : locate_leaf<DIM>(tv, p[u]);
+        for (int u = 0; u < kSortPts; ++u) { // all table lookups in flight before any (rare) descent
+            lin[u] = linear_bin<DIM>(tv, p[u]);
+            leaf[u] = BYBIN ? lin[u] >> bshift : __ldg(tv.bin_leaf + lin[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < kSortPts; ++u) {
+            if (!have[u] || outside<DIM>(tv, p[u]))
+                leaf[u] = kNotLeaf;
+            else if (!BYBIN && leaf[u] == kNotLeaf)
+                leaf[u] = walk_to_leaf<DIM>(tv, lin[u], p[u]);
+        }
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u) {
             if (!have[u])
                 continue;
             const uint32_t i = i0 + u * nthr;
-            if (use_skey)
+            if (use_skey && !coalesce)
                 skey[i - lo] = (uint16_t)leaf[u]; // kNotLeaf -> 0xFFFF (n_leaves < 0xFFFF when skey_cap > 0)
             else
                 key[i] = leaf[u];
@@ -129,6 +142,8 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     __syncthreads();
     for (uint32_t l = tid; l < nl; l += nthr) {
         const uint32_t h = tbl[l];
+        if (coalesce)
+            cnt[l] = h;
         tbl[l] = h ? atomicAdd(count + ((size_t)l << cshift), h) : 0u;
     }
     __threadfence();
@@ -197,6 +212,51 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     __syncthreads();
 
     // ---- scatter
+    if (coalesce) {
+        uint32_t mine2 = 0;
+        for (uint32_t l = l0; l < l1; ++l)
+            mine2 += cnt[l];
+        uint32_t incl2 = mine2;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl2, o);
+            if (lane >= o)
+                incl2 += t;
+        }
+        if (lane == 31)
+            warp_sums[warp] = incl2;
+        __syncthreads();
+        uint32_t off = incl2 - mine2;
+        for (uint32_t w = 0; w < warp; ++w)
+            off += warp_sums[w];
+        for (uint32_t l = l0; l < l1; ++l) {
+            loc[l] = off;
+            off += cnt[l];
+        }
+        if (l1 == nl)
+            loc[nl] = off; // every thread at or past the end holds the total
+        __syncthreads();
+        for (uint32_t i0 = lo + tid; i0 < hi; i0 += kSortPts * nthr) {
+            uint32_t k[kSortPts];
+#pragma unroll
+            for (int u = 0; u < kSortPts; ++u) {
+                const uint32_t i = i0 + u * nthr;
+                k[u] = i < hi ? __ldcs(key + i) : kNotLeaf;
+            }
+#pragma unroll
+            for (int u = 0; u < kSortPts; ++u)
+                if (k[u] != kNotLeaf)
+                    sorted[loc[k[u]] + atomicSub(cnt + k[u], 1u) - 1u] = (uint16_t)(i0 + u * nthr - lo);
+        }
+        __syncthreads();
+        const uint32_t sub = tid & 7;
+        for (uint32_t l = tid >> 3; l < nl; l += nthr >> 3) { // 8 lanes per run: their stores merge into one sector
+            const uint32_t b = loc[l], len = loc[l + 1] - b, g = tbl[l];
+            for (uint32_t e = sub; e < len; e += 8)
+                perm[g + e] = lo + sorted[b + e];
+        }
+        return;
+    }
     for (uint32_t i0 = lo + tid; i0 < hi; i0 += kSortPts * nthr) {
         uint32_t k[kSortPts];
 #pragma unroll
@@ -212,17 +272,7 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u)
             if (k[u] != kNotLeaf)
-            {
-#if defined(BZ_SORT_EXP) && BZ_SORT_EXP == 1 // timing experiment: no scattered stores
-                const uint32_t slot = atomicAdd(tbl + k[u], 1u);
-                if (slot == 0xFFFFFFF0u)
-                    perm[slot] = i0 + u * nthr;
-#elif defined(BZ_SORT_EXP) && BZ_SORT_EXP == 2 // timing experiment: no shared atomics in the scatter
-                perm[tbl[k[u]] + (i0 & 7)] = i0 + u * nthr;
-#else
                 perm[atomicAdd(tbl + k[u], 1u)] = i0 + u * nthr;
-#endif
-            }
     }
 }
 
@@ -369,6 +419,26 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<3, false>, kSortThreads, hist);
             per_sm = per_sm < want ? per_sm : want;
         }
+        // optional: the coalescing scatter (three tables + the 16-bit local order of the CTA's range).  Measured on
+        // B200 (C3): 3.82 ms per 2e8 points against 3.37 ms -- the second shared-memory pass costs more than the merged
+        // stores save -- so it is opt-in (BAOBZI_B200_SORT_COAL=1).
+        ws.sort_coal = 0;
+        if (std::getenv("BAOBZI_B200_SORT_COAL") && std::atoi(std::getenv("BAOBZI_B200_SORT_COAL")) != 0) {
+            const int64_t range = (chunk + (int64_t)dt.sm_count * want - 1) / ((int64_t)dt.sm_count * want);
+            int64_t cap = range > kSortThreads * kSortPts ? range : kSortThreads * kSortPts;
+            cap = (cap + 7) / 8 * 8;
+            const size_t smem = 3 * hist + 8 + (size_t)cap * sizeof(uint16_t);
+            int occ = 0;
+            if (cap <= 0xFFFF && smem <= kFusedSortMaxSmem &&
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, bin_sort_fused_kernel<3, false>, kSortThreads, smem) ==
+                    cudaSuccess &&
+                occ >= want) {
+                per_sm = want;
+                ws.sort_coal = (uint32_t)cap;
+                ws.sort_skey = 0;
+                ws.sort_smem = smem;
+            }
+        }
         ws.sort_ctas = dt.sm_count * per_sm;
         ws.sort_threads = kSortThreads;
         ws.fused = per_sm >= 1;
@@ -394,6 +464,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
                 ws.sort_threads = warps * 32;
                 ws.sort_ctas = dt.sm_count;
                 ws.sort_skey = 0;
+                ws.sort_coal = 0;
                 ws.sort_smem = hist;
             }
         }
@@ -401,8 +472,8 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             std::fprintf(stderr, "baobzi: overlap %d: sort CTA %d threads beside %d K4 registers / %zu B smem\n",
                          (int)ws.sort_overlap_ok, ws.sort_threads, k4_regs, k4_smem);
         if (std::getenv("BAOBZI_B200_DEBUG"))
-            std::fprintf(stderr, "baobzi: fused sort: %d CTAs/SM, %zu B smem, %u shared keys per CTA, chunk %lld\n", per_sm,
-                         ws.sort_smem, ws.sort_skey, (long long)chunk);
+            std::fprintf(stderr, "baobzi: fused sort: %d CTAs/SM, %zu B smem, %u shared keys / %u local-sort slots per CTA, chunk %lld\n",
+                         per_sm, ws.sort_smem, ws.sort_skey, ws.sort_coal, (long long)chunk);
     }
     cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
     if (e == cudaSuccess)
@@ -515,10 +586,10 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         ws.flip = !ws.flip;
         TreeView tvv = tv;
         int cshift = ws.cshift;
-        uint32_t tile = TILE, nn = n, skey = 0, nkeys = tv.n_leaves;
+        uint32_t tile = TILE, nn = n, skey = 0, nkeys = tv.n_leaves, coal = 0;
         int bshift = 0;
         void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
-                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start};
+                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start, &coal};
         rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3, false>, dim3(grid), dim3(ws.sort_threads), args,
                                                    ws.sort_smem, ss);
         if (pf) {
@@ -555,10 +626,10 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         ws.flip = !ws.flip;
         TreeView tvv = tv;
         int cshift = ws.cshift;
-        uint32_t tile = TILE, nn = n, skey = ws.sort_skey, nkeys = tv.n_leaves;
+        uint32_t tile = TILE, nn = n, skey = ws.sort_skey, nkeys = tv.n_leaves, coal = ws.sort_coal;
         int bshift = 0;
         void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
-                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start};
+                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start, &coal};
         rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3, false>, dim3(grid), dim3(ws.sort_threads), args,
                                                    ws.sort_smem, st);
         if (pf) { // the three classic stages are one launch here: all of it is booked under "lookup"
@@ -623,11 +694,11 @@ static int launch_bucket_sort(const DeviceTree &dt, BinWorkspace &ws, const doub
     ws.flip = !ws.flip;
     TreeView tvv = dt.view;
     int cshift = ws.cshift, bshift = ws.bshift;
-    uint32_t tile = 1, nn = n, skey = ws.sort_skey, nkeys = ws.n_keys;
+    uint32_t tile = 1, nn = n, skey = ws.sort_skey, nkeys = ws.n_keys, coal = ws.sort_coal;
     uint32_t *no_tile_leaf = nullptr;
     uint2 *no_tile_info = nullptr;
     void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
-                    &no_tile_leaf, &no_tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start};
+                    &no_tile_leaf, &no_tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start, &coal};
     return (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<DIM, true>, dim3(grid), dim3(ws.sort_threads),
                                             args, ws.sort_smem, st);
 }
@@ -654,6 +725,20 @@ static int configure_bucket_sort(const DeviceTree &dt, BinWorkspace &ws, int64_t
     if (!ws.sort_skey)
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<DIM, true>, kSortThreads, hist);
     per_sm = per_sm < want ? per_sm : want;
+    ws.sort_coal = 0;
+    if (std::getenv("BAOBZI_B200_SORT_COAL") && std::atoi(std::getenv("BAOBZI_B200_SORT_COAL")) != 0) {
+        const size_t smem = 3 * hist + 8 + (size_t)cap * sizeof(uint16_t);
+        int occ = 0;
+        if (cap <= 0xFFFF && smem <= kFusedSortMaxSmem &&
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, bin_sort_fused_kernel<DIM, true>, kSortThreads, smem) ==
+                cudaSuccess &&
+            occ >= want) {
+            per_sm = want;
+            ws.sort_coal = (uint32_t)cap;
+            ws.sort_skey = 0;
+            ws.sort_smem = smem;
+        }
+    }
     if (per_sm < 1)
         return (int)cudaErrorInvalidConfiguration;
     ws.sort_ctas = dt.sm_count * per_sm;

@@ -89,6 +89,7 @@ struct BinWorkspace {
                                 // are then the two histogram buffers used by alternate chunks
     bool flip = false;          // which of the two the next chunk histograms into
     int sort_ctas = 0;          // grid of the cooperative kernel (all CTAs co-resident)
+    uint32_t sort_coal = 0;     // per-CTA capacity of the shared-memory local sort (0: direct 4-byte scatter)
     uint32_t sort_skey = 0;     // per-CTA capacity of the shared-memory key array (0: keys go through key[])
     size_t sort_smem = 0;       // dynamic shared memory of the cooperative kernel
     uint2 *tile_info = nullptr; // [max_tiles] {node, coefficient offset / 16 B} of each tile's leaf

@@ -104,20 +104,9 @@ __device__ __forceinline__ uint32_t linear_bin(const TreeView &tv, const double 
 // never refined past the grid, e.g. the 3D benchmark trees) are answered by the bin_leaf table alone; otherwise
 // every step fetches the whole 64-byte record (both sectors of one line in a single round trip): one dependent
 // load fewer than locate() + load_tail().
+// descent from the root of grid cell `lin` to the leaf holding x, returning the dense leaf rank
 template <int DIM>
-__device__ __forceinline__ uint32_t locate_leaf(const TreeView &tv, const double (&x)[DIM]) {
-    int lin = 0, stride = 1;
-#pragma unroll
-    for (int j = 0; j < DIM; ++j) {
-        const double xb = __dsub_rn(x[j], tv.lower_left[j]);
-        int b = __double2int_rz(__dmul_rn(xb, tv.inv_bin_size[j]));
-        b = min(max(b, 0), tv.n_sub[j] - 1);
-        lin += stride * b;
-        stride *= tv.n_sub[j];
-    }
-    const uint32_t direct = __ldg(tv.bin_leaf + lin); // undivided cell: done after one 4-byte load
-    if (direct != kNotLeaf)
-        return direct;
+__device__ __forceinline__ uint32_t walk_to_leaf(const TreeView &tv, uint32_t lin, const double (&x)[DIM]) {
     uint32_t node = __ldg(tv.bin_root + lin);
     for (;;) {
         const double2 *p = reinterpret_cast<const double2 *>(tv.nodes + node);
@@ -132,6 +121,13 @@ __device__ __forceinline__ uint32_t locate_leaf(const TreeView &tv, const double
             bits |= (uint32_t)(x[2] > b.x) << 2;
         node = child0 + bits;
     }
+}
+
+template <int DIM>
+__device__ __forceinline__ uint32_t locate_leaf(const TreeView &tv, const double (&x)[DIM]) {
+    const uint32_t lin = linear_bin<DIM>(tv, x);
+    const uint32_t direct = __ldg(tv.bin_leaf + lin); // undivided cell: done after one 4-byte load
+    return direct != kNotLeaf ? direct : walk_to_leaf<DIM>(tv, lin, x);
 }
 
 template <int DIM>

@@ -272,6 +272,57 @@ __global__ void __launch_bounds__(W * 32, 1) pat_h(double *out, const double *in
     if (s == 1.2345) out[0] = s;
 }
 
+// K: the slab body of the tensor-core evaluation kernel in isolation (registers only): 8 DMMA (4 groups x 2 chained),
+// the lane-local pair sums, the quad reduction with shuffles, the val / tx updates.  MODE 0: full body; 1: without
+// the quad reduction (l summed locally); 2: DMMAs only feed a running sum.
+__device__ __forceinline__ double shx(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
+template <int W, int MODE>
+__global__ void __launch_bounds__(W * 32, 1) pat_k(double *out, const double *in) {
+    const int lane = threadIdx.x & 31, t = lane & 3;
+    const bool low = t < 2, odd = t & 1;
+    double a0[4], a1[4], ya[4], yb[4], breg[8][2];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { a0[j] = in[lane + j]; a1[j] = in[lane + 4 + j]; ya[j] = in[lane + 8 + j]; yb[j] = in[lane + 12 + j]; }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { breg[i][0] = in[32 + lane + i]; breg[i][1] = in[48 + lane + i]; }
+    double val = 0, tx = 1.0, tx_prev = in[lane], x2 = in[lane] * 2;
+    for (int it = 0; it < ITERS / 8; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            double l[4], d0[4], d1[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                d0[j] = d1[j] = -0.0;
+                asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d0[j]), "+d"(d1[j]) : "d"(a0[j]), "d"(breg[i][0]));
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(d0[j]), "+d"(d1[j]) : "d"(a1[j]), "d"(breg[i][1]));
+            double d;
+            if (MODE == 2) {
+                d = (d0[0] + d1[1]) + (d0[2] + d1[3]);
+                val += d;
+                continue;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) l[j] = __fma_rn(yb[j], d1[j], __dmul_rn(ya[j], d0[j]));
+            if (MODE == 1) {
+                d = __dadd_rn(__dadd_rn(l[0], l[2]), __dadd_rn(l[1], l[3]));
+            } else {
+                const double r0 = shx(low ? l[2] : l[0], 2), r1 = shx(low ? l[3] : l[1], 2);
+                const double s0 = __dadd_rn(low ? l[0] : l[2], r0), s1 = __dadd_rn(low ? l[1] : l[3], r1);
+                d = __dadd_rn(odd ? s1 : s0, shx(odd ? s0 : s1, 1));
+            }
+            val = __fma_rn(tx, d, val);
+            const double tn = __fma_rn(x2, tx, -tx_prev);
+            tx_prev = tx;
+            tx = tn;
+        }
+        a0[it & 3] += 1e-9; // keep the iterations distinct
+    }
+    if (val == 1.2345) out[0] = val;
+}
+
 // DMMA rounding probe: D = A*B + C with A row 0 = (a0..a3), B col 0 = (b0..b3): which FMA order reproduces it?
 __global__ void dmma_probe(double *out, const double *av, const double *bv, double c0) {
     const int lane = threadIdx.x, g = lane >> 2, t = lane & 3;
@@ -339,6 +390,10 @@ int main() {
         printf("H warps/SM=%2d %-22s %.3f ms  pipe cycles needed/elapsed = %.3f\n", W, K == 0 ? "DMMA warps + DFMA warps" : K == 1 ? "DMMA warps only" : "DFMA warps only", ms, \
                (K == 0 ? 2.0 : 1.0) * 8 * 16.0 * ITERS * (W / 8.0) / (ms * 1e-3 * khz * 1e3)); }
     RUN_H(8, 1); RUN_H(8, 2); RUN_H(8, 0); RUN_H(16, 1); RUN_H(16, 2); RUN_H(16, 0);
+#define RUN_K(W, M, NF) { double ms = time_ms([&] { pat_k<W, M><<<sms, W * 32>>>(d, in); }); \
+        printf("K slab body mode %d  warps/SM=%2d  %.3f ms  pipe cycles needed/elapsed = %.3f\n", M, W, ms, \
+               (8 * 16.0 + NF * 2.0) * ITERS * (W / 4.0) / (ms * 1e-3 * khz * 1e3)); }
+    RUN_K(16, 0, 13); RUN_K(16, 1, 13); RUN_K(16, 2, 4); RUN_K(8, 0, 13); RUN_K(12, 0, 13);
     // rounding probe
     double ha[4] = {1.0 + 0x1p-30, 1.0 + 0x1p-31, 1.0 - 0x1p-29, 1.0 + 0x1p-33}, hb[4] = {1.0 + 0x1p-28, 1.0 - 0x1p-27, 1.0 + 0x1p-30, 1.0 - 0x1p-31};
     double *da, *db; cudaMalloc(&da, 32); cudaMalloc(&db, 32);
