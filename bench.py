@@ -65,6 +65,29 @@ def host_cores():
         return os.cpu_count() or 1
 
 
+def ncu_traffic(stage, points_per_launch):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` summary (profiles/), scaled
+    to this run's points per launch; None when there is no capture of that kernel."""
+    import glob
+    pat = {"eval_grouped": "*_k4_ncu_summary.json", "sort": "*_sort_fused_ncu_summary.json"}.get(stage)
+    if not pat:
+        return None
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", pat)))
+    if not files:
+        return None
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    try:
+        rec = json.load(open(files[-1]))[0]
+        tot = 0.0
+        for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            v, u = rec[k].split()
+            tot += float(v) * unit[u]
+        captured_points = 33554432 / 4.0  # scripts/gpu_round.sh: 32 Mi points = 4 chunks of 2048 points per leaf
+        return tot * points_per_launch / captured_points
+    except Exception:
+        return None
+
+
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -361,7 +384,7 @@ def run_ours(args, cfg, rank, world, local_rank):
                     "achieved": tf if fp64_bound else gb, "peak": fp.value if fp64_bound else hbm_peak,
                     "unit": "TFLOP/s" if fp64_bound else "GB/s",
                     "frac": (tf / fp.value if fp.value else None) if fp64_bound else gb / hbm_peak,
-                    "traffic": None,
+                    "traffic": ncu_traffic(name, pts_per_launch),
                     "peak_source": "DFMA microbenchmark baobzi_b200_fp64_peak, measured in this run" if fp64_bound else hbm_src,
                     "algorithmic_flops_per_eval": flops_per_eval(dim, order), "algorithmic_bytes_per_eval": bytes_per_eval(dim),
                     "avg_launch_ms": per_launch_s * 1e3, "points_per_launch": pts_per_launch,
