@@ -264,7 +264,18 @@ def run_ours(args, cfg, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on stdout at the first collective: keep stdout for the ONE JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            warm = torch.zeros(1, device=dev)
+            dist.all_reduce(warm)
+            torch.cuda.synchronize()
+        finally:
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
     if not os.path.exists(baobzi_b200.library_path()):
         baobzi_b200.build()
     dim, order = cfg["dim"], cfg["order"]
@@ -363,6 +374,9 @@ def run_ours(args, cfg, rank, world, local_rank):
                "matches_device_path": same, "timing": "host wall clock around baobzi_eval_multi, pinned host buffers"}
         del xh, yh
 
+    if world > 1:
+        barrier()
+        torch.distributed.destroy_process_group()
     if rank != 0:
         b.free()
         return
