@@ -13,8 +13,9 @@
 // the fly in the k loop (3 live values per point instead of O), T(y) rebuilt per slab instead of kept live.
 //
 // Each warp runs a 2-stage software pipeline over its tiles: while tile j is evaluated out of shared memory,
-// tile j+1's inputs (the leaf's coefficient block, the node record, the gathered points and their indices) are
-// in flight as cp.async copies, and tile j+2's descriptor is being fetched into registers.
+// tile j+1's gathered points and their indices are in flight as cp.async copies, and tile j+2's descriptor is being
+// fetched into registers.  A warp walks a contiguous run of tiles, so the leaf's coefficient block and node record
+// are fetched once per leaf (RUN; the strided variant refetches them with every tile).
 //
 // Arithmetic: cheb.cuh's order (bit-identical to the reference's AVX2+FMA build).  Multiplications by
 // T_0 = 1.0 are not executed (x * 1.0 == x bit for bit): a row chain starts as fma(c_1, T_1, c_0), and the
@@ -85,7 +86,19 @@ __device__ __forceinline__ double dot_packets_one(const double (&a)[O], const do
 
 // TZFLY: T_k(z) advanced inside the k loop (costs O-2 extra FMAs per point and slab, frees (O-3)*P doubles).
 // TYKEEP: T(y) computed once per tile and kept live (O*P doubles) instead of rebuilt after every slab.
-template <int O, int P, int WARPS, bool TZFLY, bool TYKEEP, int EXP = 0>
+// RUN: every warp walks a contiguous run of tiles (tiles of one leaf are adjacent) and keeps ONE copy of the current
+// leaf's coefficient block, refetched only when the leaf changes; the pipeline stages then hold points only.  Half
+// the shared memory per warp, so high orders can run 2-3 times the warps.
+template <int O, int P>
+struct RunSmem { // per warp
+    static constexpr int TILE = 32 * P;
+    double2 coeff[O * O * O / 2];
+    double2 node[4];
+    double pts[2][3 * TILE];
+    uint32_t idx[2][TILE];
+};
+
+template <int O, int P, int WARPS, bool TZFLY, bool TYKEEP, bool RUN>
 __global__ void __launch_bounds__(WARPS * 32, 1)
 bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
                   const uint32_t *__restrict__ perm, const uint2 *__restrict__ tile_info,
@@ -97,13 +110,18 @@ bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__res
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t n_tiles = __ldg(n_tiles_p);
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    Stage *stages = reinterpret_cast<Stage *>(smem_raw) + 2 * warp;
-    const uint32_t stride = gridDim.x * WARPS;
-    uint32_t t = blockIdx.x * WARPS + warp;
+    Stage *stages = reinterpret_cast<Stage *>(smem_raw) + 2 * warp;               // !RUN
+    RunSmem<O, P> &rs = reinterpret_cast<RunSmem<O, P> *>(smem_raw)[warp];          // RUN
+    const uint32_t nw = gridDim.x * WARPS, wid = blockIdx.x * WARPS + warp;
+    const uint32_t stride = RUN ? 1u : nw;
+    uint32_t t = RUN ? (uint32_t)(((uint64_t)n_tiles * wid) / nw) : wid;
+    const uint32_t t_end = RUN ? (uint32_t)(((uint64_t)n_tiles * (wid + 1)) / nw) : n_tiles;
+    auto pts_of = [&](int st) -> double * { return RUN ? rs.pts[st] : stages[st].pts; };
+    auto idx_of = [&](int st) -> uint32_t * { return RUN ? rs.idx[st] : stages[st].idx; };
 
     // descriptor of a tile: {node, coeff16} + the P slot indices of this lane
     auto load_meta = [&](uint32_t tt, uint2 &info, uint32_t (&id)[P]) {
-        if (tt < n_tiles) {
+        if (tt < t_end) {
             info = __ldg(tile_info + tt);
 #pragma unroll
             for (int p = 0; p < P; ++p)
@@ -115,52 +133,72 @@ bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__res
                 id[p] = kInvalidSlotE;
         }
     };
-    auto issue = [&](uint32_t tt, const uint2 &info, const uint32_t (&id)[P], Stage &st) {
-        if (tt < n_tiles && !(EXP == 2 && tt >= blockIdx.x * WARPS + warp + 2 * stride)) {
-            const double2 *Cg = reinterpret_cast<const double2 *>(tv.coeffs + 2ull * info.y);
+    auto fetch_leaf = [&](const uint2 &info, double2 *coeff, double2 *node) {
+        const double2 *Cg = reinterpret_cast<const double2 *>(tv.coeffs + 2ull * info.y);
 #pragma unroll 4
-            for (int j = lane; j < BLK2; j += 32)
-                cp_async16(&st.coeff[j], Cg + j);
-            if (lane < 4)
-                cp_async16(&st.node[lane], reinterpret_cast<const double2 *>(tv.nodes + info.x) + lane);
+        for (int j = lane; j < BLK2; j += 32)
+            cp_async16(&coeff[j], Cg + j);
+        if (lane < 4)
+            cp_async16(&node[lane], reinterpret_cast<const double2 *>(tv.nodes + info.x) + lane);
+    };
+    auto issue = [&](uint32_t tt, const uint2 &info, const uint32_t (&id)[P], int sidx) {
+        if (tt < t_end) {
+            if (!RUN)
+                fetch_leaf(info, stages[sidx].coeff, stages[sidx].node);
+            double *pts = pts_of(sidx);
+            uint32_t *sidxs = idx_of(sidx);
 #pragma unroll
             for (int p = 0; p < P; ++p) {
-                st.idx[p * 32 + lane] = id[p];
+                sidxs[p * 32 + lane] = id[p];
                 if (id[p] != kInvalidSlotE) {
                     const double *q = x + 3ull * id[p];
-                    cp_async8(&st.pts[0 * TILE + p * 32 + lane], q);
-                    cp_async8(&st.pts[1 * TILE + p * 32 + lane], q + 1);
-                    cp_async8(&st.pts[2 * TILE + p * 32 + lane], q + 2);
+                    cp_async8(&pts[0 * TILE + p * 32 + lane], q);
+                    cp_async8(&pts[1 * TILE + p * 32 + lane], q + 1);
+                    cp_async8(&pts[2 * TILE + p * 32 + lane], q + 2);
                 }
             }
         }
         cp_async_commit();
     };
 
-    uint2 info_n;
+    uint2 info_n, info_cur;
     uint32_t idx_n[P];
     load_meta(t, info_n, idx_n);
-    issue(t, info_n, idx_n, stages[0]);
+    issue(t, info_n, idx_n, 0);
+    info_cur = info_n;
     load_meta(t + stride, info_n, idx_n); // descriptor of the second tile
+    uint32_t cur_node = 0xFFFFFFFFu;
     int cur = 0;
-    for (; t < n_tiles; t += stride, cur ^= 1) {
-        __syncwarp(); // every lane is done reading stage cur^1 (tile j-1)
-        issue(t + stride, info_n, idx_n, stages[cur ^ 1]);
+    for (; t < t_end; t += stride, cur ^= 1) {
+        __syncwarp(); // every lane is done reading stage cur^1 (tile j-1) and, in RUN mode, the coefficient block
+        issue(t + stride, info_n, idx_n, cur ^ 1);
+        const uint2 info_next = info_n;
         load_meta(t + 2 * stride, info_n, idx_n); // lands while this tile computes
-        cp_async_wait<1>();
+        if (RUN && info_cur.x != cur_node) {    // warp uniform: a new leaf starts here
+            cur_node = info_cur.x;
+            fetch_leaf(info_cur, rs.coeff, rs.node);
+            cp_async_commit();
+            cp_async_wait<0>();
+        } else {
+            cp_async_wait<1>();
+        }
         __syncwarp();
-        const Stage &st = stages[cur];
+        info_cur = info_next;
+        const double2 *coeff_s = RUN ? rs.coeff : stages[cur].coeff;
+        const double2 *node_s = RUN ? rs.node : stages[cur].node;
+        const double *pts_s = pts_of(cur);
+        const uint32_t *idx_s = idx_of(cur);
 
-        const double2 n0 = st.node[0], n1 = st.node[1], n2 = st.node[2], n3 = st.node[3];
+        const double2 n0 = node_s[0], n1 = node_s[1], n2 = node_s[2], n3 = node_s[3];
         const double c0 = n0.x, c1 = n0.y, c2c = n1.x, ih0 = n2.x, ih1 = n2.y, ih2 = n3.x;
         double Tz[P][NTZ], Tyk[P][TYKEEP ? O : 1], acc[P][O];
         double v[P], w[P], x2[P], w2[P], tx[P], tx_prev[P], val[P];
 #pragma unroll
         for (int p = 0; p < P; ++p) {
-            const bool ok = st.idx[p * 32 + lane] != kInvalidSlotE;
-            const double px = ok ? st.pts[0 * TILE + p * 32 + lane] : c0; // padding lanes evaluate the leaf centre
-            const double py = ok ? st.pts[1 * TILE + p * 32 + lane] : c1;
-            const double pz = ok ? st.pts[2 * TILE + p * 32 + lane] : c2c;
+            const bool ok = idx_s[p * 32 + lane] != kInvalidSlotE;
+            const double px = ok ? pts_s[0 * TILE + p * 32 + lane] : c0; // padding lanes evaluate the leaf centre
+            const double py = ok ? pts_s[1 * TILE + p * 32 + lane] : c1;
+            const double pz = ok ? pts_s[2 * TILE + p * 32 + lane] : c2c;
             const double u = __dmul_rn(__dsub_rn(px, c0), ih0);
             v[p] = __dmul_rn(__dsub_rn(py, c1), ih1);
             w[p] = __dmul_rn(__dsub_rn(pz, c2c), ih2);
@@ -177,7 +215,7 @@ bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__res
         }
 #pragma unroll 1
         for (int i = 0; i < O; ++i) {
-            const double2 *cc = st.coeff + i * (O * O / 2);
+            const double2 *cc = coeff_s + i * (O * O / 2);
             // acc[p][r] = sum_k C_i(r,k) Tz[p][k]: row chains in k order; the k = 0 product is C_i(r,0) itself
             double tk[P], tkm[P];
 #pragma unroll
@@ -199,17 +237,9 @@ bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__res
                 }
 #pragma unroll
                 for (int r = 0; r < O; r += 2) {
-                    double2 c = cc[(k * O + r) / 2];
-                    if (EXP == 1) { // timing experiment: no shared-memory traffic in the slab loop
-                        c = make_double2(x2[0], x2[1]);
-                        asm volatile("" : "+d"(c.x), "+d"(c.y));
-                    }
+                    const double2 c = cc[(k * O + r) / 2];
                     if (k == 1) {
-                        double2 cz = cc[r / 2];
-                        if (EXP == 1) {
-                            cz = make_double2(x2[1], x2[0]);
-                            asm volatile("" : "+d"(cz.x), "+d"(cz.y));
-                        }
+                        const double2 cz = cc[r / 2];
 #pragma unroll
                         for (int p = 0; p < P; ++p) {
                             acc[p][r] = __fma_rn(c.x, tk[p], cz.x);
@@ -244,7 +274,7 @@ bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__res
         }
 #pragma unroll
         for (int p = 0; p < P; ++p) {
-            const uint32_t id = st.idx[p * 32 + lane];
+            const uint32_t id = idx_s[p * 32 + lane];
             if (id != kInvalidSlotE)
                 res[id] = val[p];
         }
@@ -452,16 +482,16 @@ static int launch_k4_mma8(const DeviceTree &dt, const BinWorkspace &ws, const do
 // ------------------------------------------------------------------------------------------ host side
 struct K4Variant {
     int order, P, warps;
-    bool tzfly, tykeep;
+    bool tzfly, tykeep, run;
     int (*launch)(const DeviceTree &, const BinWorkspace &, const double *, double *, cudaStream_t);
     const void *func; // for cudaFuncGetAttributes
     size_t smem;
 };
 
-template <int O, int P, int WARPS, bool TZFLY, bool TYKEEP, int EXP = 0>
+template <int O, int P, int WARPS, bool TZFLY, bool TYKEEP, bool RUN>
 static int launch_k4(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
-    auto kern = bin_eval3d_kernel<O, P, WARPS, TZFLY, TYKEEP, EXP>;
-    constexpr size_t smem = sizeof(PipeStage<O, P>) * 2 * WARPS;
+    auto kern = bin_eval3d_kernel<O, P, WARPS, TZFLY, TYKEEP, RUN>;
+    constexpr size_t smem = RUN ? sizeof(RunSmem<O, P>) * WARPS : sizeof(PipeStage<O, P>) * 2 * WARPS;
     static_assert(smem <= 227 * 1024, "pipeline stages exceed the shared memory of an SM");
     static bool configured = false; // per instantiation
     if (!configured) {
@@ -474,46 +504,45 @@ static int launch_k4(const DeviceTree &dt, const BinWorkspace &ws, const double 
     return (int)cudaGetLastError();
 }
 
-#define BZ_K4(O_, P_, W_, F_, Y_)                                                                                      \
-    {O_, P_, W_, F_, Y_, launch_k4<O_, P_, W_, F_, Y_>, (const void *)bin_eval3d_kernel<O_, P_, W_, F_, Y_>,           \
-     sizeof(PipeStage<O_, P_>) * 2 * W_}
+#define BZ_K4(O_, P_, W_, F_, Y_, R_)                                                                                  \
+    {O_, P_, W_, F_, Y_, R_, launch_k4<O_, P_, W_, F_, Y_, R_>, (const void *)bin_eval3d_kernel<O_, P_, W_, F_, Y_, R_>, \
+     R_ ? sizeof(RunSmem<O_, P_>) * W_ : sizeof(PipeStage<O_, P_>) * 2 * W_}
 #define BZ_K4M(W_, D_)                                                                                                 \
-    {8, D_ ? 5 : 4, W_, true, true, launch_k4_mma8<W_, D_>, (const void *)bin_eval3d_mma8_kernel<W_, D_>, sizeof(MmaStage) * 2 * W_}
+    {8, D_ ? 5 : 4, W_, true, true, false, launch_k4_mma8<W_, D_>, (const void *)bin_eval3d_mma8_kernel<W_, D_>,       \
+     sizeof(MmaStage) * 2 * W_}
 // first entry of an order = its default
 static const K4Variant kVariants[] = {
-    BZ_K4(6, 4, 8, false, true),   BZ_K4(6, 4, 12, false, true),  BZ_K4(6, 4, 16, false, false),
-    BZ_K4(8, 4, 8, false, true),   BZ_K4(8, 4, 8, false, false),
+    BZ_K4(6, 4, 8, false, true, true),    BZ_K4(6, 4, 8, false, true, false),   BZ_K4(6, 4, 12, false, true, true),
+    BZ_K4(8, 4, 8, false, true, true),    BZ_K4(8, 4, 8, false, true, false),   BZ_K4(8, 4, 8, false, false, false),
+    BZ_K4(8, 3, 12, false, false, false), BZ_K4(8, 3, 12, false, false, true),  BZ_K4(8, 2, 16, false, true, false),
     // tzfly && tykeep together = the DMMA kernel (P = 5 in the selector: deferred quad reduction)
-    BZ_K4M(16, false), BZ_K4M(12, false), BZ_K4M(8, false), BZ_K4M(16, true), BZ_K4M(12, true), BZ_K4M(8, true),  BZ_K4(8, 3, 12, false, false),
-    BZ_K4(8, 3, 12, false, true),  BZ_K4(8, 4, 12, true, false),  BZ_K4(8, 2, 16, false, false),
-    BZ_K4(8, 2, 16, false, true),  BZ_K4(8, 3, 8, false, true),
-    BZ_K4(10, 2, 8, false, true),  BZ_K4(10, 3, 8, false, false), BZ_K4(10, 4, 8, true, false),
-    BZ_K4(12, 2, 4, false, true),  BZ_K4(12, 3, 4, false, false), BZ_K4(12, 4, 4, true, false),
-    BZ_K4(14, 2, 4, false, true),  BZ_K4(14, 3, 4, true, false),
-    BZ_K4(16, 2, 2, false, true),  BZ_K4(16, 2, 3, false, false),
-#ifdef BZ_EXPERIMENTS // timing experiments with WRONG results: P = 91 / 92 select them
-    {8, 91, 8, false, true, launch_k4<8, 4, 8, false, true, 1>, nullptr, 0}, {8, 92, 8, false, true, launch_k4<8, 4, 8, false, true, 2>, nullptr, 0},
-    {8, 91, 12, false, false, launch_k4<8, 3, 12, false, false, 1>, nullptr, 0}, {8, 92, 12, false, false, launch_k4<8, 3, 12, false, false, 2>, nullptr, 0},
-#endif
+    BZ_K4M(16, false), BZ_K4M(12, false), BZ_K4M(16, true),
+    BZ_K4(10, 3, 8, false, false, true),  BZ_K4(10, 2, 8, false, true, false),  BZ_K4(10, 3, 8, false, false, false),
+    BZ_K4(10, 3, 12, false, false, true),
+    BZ_K4(12, 3, 8, false, false, true),  BZ_K4(12, 2, 4, false, true, false),  BZ_K4(12, 3, 4, false, false, false),
+    BZ_K4(12, 2, 8, false, true, true),   BZ_K4(12, 2, 12, false, false, true),
+    BZ_K4(14, 2, 8, false, true, true),   BZ_K4(14, 2, 4, false, true, false),  BZ_K4(14, 3, 8, true, false, true),
+    BZ_K4(16, 2, 4, false, true, true),   BZ_K4(16, 2, 2, false, true, false),  BZ_K4(16, 2, 6, false, false, true),
 };
 #undef BZ_K4
 #undef BZ_K4M
 
-static const K4Variant *find_variant(int order, int P, int warps, int tzfly, int tykeep) {
+static const K4Variant *find_variant(int order, int P, int warps, int tzfly, int tykeep, int run) {
     for (const K4Variant &v : kVariants)
-        if (v.order == order && (P < 0 || (v.P == P && v.warps == warps && v.tzfly == (tzfly != 0) && v.tykeep == (tykeep != 0))))
+        if (v.order == order && (P < 0 || (v.P == P && v.warps == warps && v.tzfly == (tzfly != 0) &&
+                                           v.tykeep == (tykeep != 0) && v.run == (run != 0))))
             return &v;
     return nullptr;
 }
 
-// Variant for a 3D tree of this order: the default, or BAOBZI_B200_K4="P,warps,tzfly,tykeep" (benchmarks).
+// Variant for a 3D tree of this order: the default, or BAOBZI_B200_K4="P,warps,tzfly,tykeep[,run]" (benchmarks).
 // Returns the points per lane (tile = 32 * P slots) and an opaque index for launch_bin_eval3d; -1 if unsupported.
 int bin_eval_select(int order, int *P) {
-    const K4Variant *v = find_variant(order, -1, 0, 0, 0);
+    const K4Variant *v = find_variant(order, -1, 0, 0, 0, 0);
     if (const char *e = std::getenv("BAOBZI_B200_K4")) {
-        int p = 0, w = 0, f = 0, y = 0;
-        if (std::sscanf(e, "%d,%d,%d,%d", &p, &w, &f, &y) == 4) {
-            const K4Variant *o = find_variant(order, p, w, f, y);
+        int p = 0, w = 0, f = 0, y = 0, r = 0;
+        if (std::sscanf(e, "%d,%d,%d,%d,%d", &p, &w, &f, &y, &r) >= 4) {
+            const K4Variant *o = find_variant(order, p, w, f, y, r);
             if (o)
                 v = o;
             else
@@ -522,7 +551,7 @@ int bin_eval_select(int order, int *P) {
     }
     if (!v)
         return -1;
-    *P = v->P > 90 ? (v->warps == 12 ? 3 : 4) : (v->P == 5 ? 4 : v->P);
+    *P = v->P == 5 ? 4 : v->P;
     return (int)(v - kVariants);
 }
 
