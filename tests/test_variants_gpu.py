@@ -1,0 +1,73 @@
+"""Every opt-in kernel variant of the 3D path gives the bits of the default one (and of the oracle): the FP64
+tensor-core kernel (DMMA rounds like the FMA chain it replaces), the strided / run tile orders, the coalescing
+scatter, the two-stream sort/evaluate overlap, and the bucketed path on a tree with refined cells."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+VARIANTS = [
+    {"BAOBZI_B200_K4": "4,16,1,1"},          # DMMA kernel, 16 warps
+    {"BAOBZI_B200_K4": "5,16,1,1"},          # DMMA kernel, deferred quad reduction
+    {"BAOBZI_B200_K4": "4,8,0,1,0"},         # DFMA kernel, strided tiles (coefficients staged per tile)
+    {"BAOBZI_B200_K4": "3,12,0,0,1"},        # P = 3, 12 warps, run order
+    {"BAOBZI_B200_SORT_COAL": "1"},          # coalescing scatter
+    {"BAOBZI_B200_OVERLAP": "1"},            # sort of chunk c+1 beside the evaluation of chunk c
+    {"BAOBZI_B200_FUSED_SORT": "0"},         # four-kernel sort (fallback for trees whose histogram exceeds smem)
+    {"BAOBZI_B200_SORT_SKEY": "0"},          # keys through global memory
+]
+
+
+@pytest.mark.parametrize("env", VARIANTS, ids=lambda e: ",".join("%s=%s" % kv for kv in e.items()))
+def test_variant_bits(gpu_lib, ref, env):
+    import torch
+    from conftest import load_golden
+    from test_parity_gpu import ulp
+    path, g = load_golden("t3d_o8")
+    t = ref.OracleTree(path)
+    a = t.arrays()
+    rng = np.random.default_rng(11)
+    n = 300_000
+    x = a["lower_left"] + rng.random((n, 3)) * (a["upper_right"] - a["lower_left"]) * 1.01 - 0.005
+    want = t.eval_multi(x, ref.ARITH_AVX2)
+    xd = torch.from_numpy(x).cuda()
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        b = gpu_lib.Baobzi(filename=path, mode="binned")   # the knobs are read when the workspace is built
+        for chunk in (0, 70_001):                          # one chunk, then several (exercises the buffer ping-pong)
+            b.set_mode("binned", chunk)
+            y = b(xd)
+            torch.cuda.synchronize()
+            assert ulp(ref, y.cpu().numpy(), want) == 0, (env, chunk)
+        b.free()
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+def test_bucketed_on_refined_tree(gpu_lib, ref):
+    """The bucketed path's per-bucket leaf sort on a tree whose grid cells are subdivided (2D oscillatory fixture)."""
+    import torch
+    from conftest import load_golden
+    from test_parity_gpu import ulp
+    path, g = load_golden("osc_2d")
+    t = ref.OracleTree(path)
+    a = t.arrays()
+    rng = np.random.default_rng(5)
+    n = 400_000
+    x = a["lower_left"] + rng.random((n, 2)) * (a["upper_right"] - a["lower_left"])
+    want = t.eval_multi(x, ref.ARITH_AVX2)
+    b = gpu_lib.Baobzi(filename=path, mode="bucketed")
+    xd = torch.from_numpy(x).cuda()
+    for chunk in (0, 50_000):
+        b.set_mode("bucketed", chunk)
+        y = b(xd)
+        torch.cuda.synchronize()
+        assert ulp(ref, y.cpu().numpy(), want) == 0
+    b.free()
