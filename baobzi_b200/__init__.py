@@ -57,6 +57,7 @@ ABI = {
                                             C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
     "baobzi_sync": (C.c_int, [baobzi_t]),
     "baobzi_set_mode": (C.c_int, [baobzi_t, C.c_int, C.c_int64]),
+    "baobzi_eval_multi_device_all": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "baobzi_launch_count": (C.c_int64, [baobzi_t]),
     "baobzi_profile_begin": (C.c_int, [baobzi_t]),
     "baobzi_profile_end": (C.c_int, [baobzi_t, c_double_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
@@ -208,6 +209,22 @@ class Baobzi:
         y = np.empty(max(1, self.output_dim), dtype=np.float64)
         self._lib.baobzi_eval(self.ptr, xarr.ctypes.data, y.ctypes.data)
         return y
+
+    def eval_all(self, x):
+        """Every output component for a batch of device-resident points of a 1D tree: (n, output_dim) tensor whose
+        row i is what eval(x[i]) returns (baobzi_eval_multi_device_all)."""
+        import torch
+        dp = _device_pointer(x)
+        if dp is None:
+            raise TypeError("eval_all takes a CUDA float64 tensor / array")
+        ptr, count, _keep = dp
+        n = count // self.dim
+        out = torch.empty((n, max(1, self.output_dim)), dtype=torch.float64, device=x.device)
+        rc = self._lib.baobzi_eval_multi_device_all(self.ptr, ptr, out.data_ptr(), n,
+                                                    torch.cuda.current_stream(x.device).cuda_stream)
+        if rc != 0:
+            raise RuntimeError("baobzi_eval_multi_device_all failed with CUDA error %d" % rc)
+        return out
 
     def node_index(self, x):
         """Global node index per point (the reference's Function::get_global_node_index), -1 outside."""

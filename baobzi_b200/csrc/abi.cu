@@ -531,6 +531,25 @@ int baobzi_eval_multi_device(const baobzi_t func, const double *d_x, double *d_r
     return bz::eval_device(f, r, r->shard_ws, d_x, d_res, ntrg, (cudaStream_t)cuda_stream);
 }
 
+int baobzi_eval_multi_device_all(const baobzi_t func, const double *d_x, double *d_res, int64_t ntrg, void *cuda_stream) {
+    Function *f = (Function *)func->obj;
+    if (ntrg <= 0)
+        return 0;
+    if (func->DIM != 1)
+        return (int)cudaErrorNotSupported; // the reference's multi-output fit is only meaningful in 1D
+    int dev = bz::device_of_pointer(d_x);
+    if (dev < 0)
+        return (int)cudaErrorInvalidDevicePointer;
+    bz::Replica *r = bz::get_replica(f, dev);
+    if (!r)
+        return (int)cudaErrorMemoryAllocation;
+    bz::DeviceGuard g(dev);
+    int64_t launches = 0;
+    const int rc = bz::launch_eval_all_1d(r->dt, d_x, d_res, ntrg, (cudaStream_t)cuda_stream, &launches);
+    f->launches += launches;
+    return rc;
+}
+
 int baobzi_node_index_multi_device(const baobzi_t func, const double *d_x, int64_t *d_idx, int64_t ntrg,
                                    void *cuda_stream) {
     Function *f = (Function *)func->obj;

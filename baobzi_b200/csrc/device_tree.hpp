@@ -136,6 +136,9 @@ void free_workspace(BinWorkspace &ws);
 // reference's global node index per point (-1 outside).  res may be nullptr (index query only).
 int launch_eval_direct(const DeviceTree &dt, const double *d_x, double *d_res, int64_t *d_node_idx, int64_t n,
                        cudaStream_t stream, int64_t *launches, StageProfile *prof = nullptr);
+// Every output component of a 1D tree: d_res[i * out_dim + k] (what baobzi_eval writes to y[k], batched).
+int launch_eval_all_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream,
+                       int64_t *launches);
 // Dependent-DFMA microbenchmark on the current device: sustained FP64 FMA rate in TFLOP/s (2 flops per FMA).
 int measure_fp64_peak(double *tflops, int repeats);
 // Scalar twin: x[dim] -> y[out_dim] (reference Function::eval(x, res), template.hpp:851-860).

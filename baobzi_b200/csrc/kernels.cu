@@ -245,6 +245,32 @@ __global__ void eval_scalar_kernel(const TreeView tv, const double *__restrict__
     }
 }
 
+// Batched twin of the scalar multi-output entry: every output component of a 1D tree for every
+// point, res[i * out_dim + k] = the value baobzi_eval writes to y[k] (block k at +k*ORDER, template.hpp:371-375).
+// One thread per (point, component): the lookup is redone per component (cache hits), the stores are contiguous.
+template <int ORDER>
+__global__ void __launch_bounds__(kDirectThreads)
+eval_all_1d_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res, int64_t n) {
+    const int64_t total = n * (int64_t)tv.out_dim;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
+        const int64_t i = e / tv.out_dim;
+        const uint32_t k = (uint32_t)(e - i * tv.out_dim);
+        double p[1] = {__ldg(x + i)};
+        double y = __longlong_as_double(0x7ff8000000000000ll);
+        if (!outside<1>(tv, p)) {
+            NodeHead head;
+            const uint32_t node = locate<1>(tv, p, head);
+            const NodeTail tail = load_tail(tv.nodes, node);
+            if (k < tail.out_dim) {
+                const double u = __dmul_rn(__dsub_rn(p[0], head.c0), tail.ih0);
+                y = cheb_eval_1d<ORDER>(u, tv.coeffs + 2ull * head.coeff16 + (size_t)k * ORDER);
+            }
+        }
+        __stcs(res + e, y);
+    }
+}
+
 #define BZ_DISPATCH_ORDER(DIM, order, CALL)                                                                            \
     switch (order) {                                                                                                   \
     case 6: { constexpr int O = 6; constexpr int D = DIM; CALL; } break;                                               \
@@ -305,6 +331,22 @@ int launch_eval_buckets(const DeviceTree &dt, const double *d_x, double *d_res, 
     BZ_DISPATCH(dt.view.dim, dt.view.order,
                 (eval_bucket_kernel<D, O><<<grid, kBktThreads, 0, stream>>>(dt.view, d_x, d_res, d_perm, d_key_start, d_queue,
                                                                           n_keys, bshift)));
+    return (int)cudaGetLastError();
+}
+
+int launch_eval_all_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream,
+                       int64_t *launches) {
+    if (dt.view.dim != 1)
+        return (int)cudaErrorInvalidValue;
+    if (n <= 0)
+        return 0;
+    const int64_t want = (n * dt.view.out_dim + kDirectThreads - 1) / kDirectThreads;
+    const int64_t cap = (int64_t)dt.sm_count * 64;
+    const unsigned grid = (unsigned)(want < cap ? want : cap);
+    BZ_DISPATCH_ORDER(1, dt.view.order,
+                      ((void)D, eval_all_1d_kernel<O><<<grid, kDirectThreads, 0, stream>>>(dt.view, d_x, d_res, n)));
+    if (launches)
+        *launches += 1;
     return (int)cudaGetLastError();
 }
 

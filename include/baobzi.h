@@ -119,6 +119,12 @@ baobzi_t baobzi_free(baobzi_t func);
  * NULL = legacy default stream).  64-bit count.  Returns 0 or a cudaError_t value. */
 int baobzi_eval_multi_device(const baobzi_t func, const double *d_x, double *d_res, int64_t ntrg, void *cuda_stream);
 
+/* All output components of a 1D multi-output tree, batched (extension): d_res[i * OUTPUT_DIM + k] is
+ * what baobzi_eval (baobzi.cpp:61 -> template.hpp:851-860, 371-375) writes to y[k] for point i, bit for bit; NaN outside
+ * the domain.  baobzi_eval_multi itself keeps the reference's behaviour (first component only).  DIM must be 1
+ * (cudaErrorNotSupported otherwise).  Asynchronous on `cuda_stream`. */
+int baobzi_eval_multi_device_all(const baobzi_t func, const double *d_x, double *d_res, int64_t ntrg, void *cuda_stream);
+
 /* Global node index per point, exactly Function::get_global_node_index of the reference
  * (baobzi_template.hpp:846-849; all nodes, subtree-major, breadth-first inside a subtree);
  * -1 outside the domain.  Device and host pointer variants. */

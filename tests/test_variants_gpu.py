@@ -71,3 +71,32 @@ def test_bucketed_on_refined_tree(gpu_lib, ref):
         torch.cuda.synchronize()
         assert ulp(ref, y.cpu().numpy(), want) == 0
     b.free()
+
+
+def test_eval_all_multi_output_1d(gpu_lib, ref):
+    """baobzi_eval_multi_device_all: row i == what baobzi_eval writes for point i (every output component), and
+    column 0 == baobzi_eval_multi; NaN rows outside the domain; not supported for DIM > 1."""
+    import torch
+    from conftest import load_golden
+    path, g = load_golden("tc_1d2")
+    b = gpu_lib.Baobzi(filename=path)
+    assert b.output_dim == 2
+    t = ref.OracleTree(path)
+    a = t.arrays()
+    rng = np.random.default_rng(3)
+    x = a["lower_left"] + rng.random((5000, 1)) * (a["upper_right"] - a["lower_left"]) * 1.02 - 0.01
+    xd = torch.from_numpy(x).cuda()
+    y = b.eval_all(xd).cpu().numpy()
+    assert y.shape == (5000, 2)
+    first = b(xd).cpu().numpy()
+    assert np.array_equal(np.nan_to_num(y[:, 0], nan=-7.0), np.nan_to_num(first, nan=-7.0))
+    for i in list(range(0, 5000, 97)):
+        ys = b.eval(x[i])
+        assert np.array_equal(np.nan_to_num(ys, nan=-7.0), np.nan_to_num(y[i], nan=-7.0)), i
+    assert np.isnan(y).any() and not np.isnan(y).all()
+    b.free()
+    path3, _ = load_golden("t3d_o8")
+    b3 = gpu_lib.Baobzi(filename=path3)
+    with pytest.raises(RuntimeError):
+        b3.eval_all(torch.zeros((4, 3), dtype=torch.float64, device="cuda"))
+    b3.free()
