@@ -1,3 +1,8 @@
-python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; tail -2 gpurun_out/pytest_gpu.log
-python bench.py --no-cpu > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; python -c "
-import json; d=json.load(open('gpurun_out/bench_default.json')); print(d['value'], d['e2e']['value'], d['roofline']['frac'], d['roofline']['traffic'], d['roofline']['stages_ms_per_step'])"
+cp baobzi_b200/lib/libbaobzi.so /tmp/good.so
+for e in 3 4; do
+  cp baobzi_b200/lib/libbaobzi_exp$e.so baobzi_b200/lib/libbaobzi.so
+  python bench.py --points 200000000 --steps 3 --warmup 3 --no-cpu --no-e2e > gpurun_out/var_sortexp$e.json 2> gpurun_out/var_sortexp$e.err
+  python -c "
+import json; d=json.load(open('gpurun_out/var_sortexp$e.json')); print('sortexp$e', {k:round(v,2) for k,v in d['roofline']['stages_ms_per_step'].items()})" || tail -3 gpurun_out/var_sortexp$e.err
+done
+cp /tmp/good.so baobzi_b200/lib/libbaobzi.so
