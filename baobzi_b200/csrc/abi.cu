@@ -92,7 +92,9 @@ int64_t default_chunk(const DeviceTree &dt) {
             return v;
     }
     int64_t c = (int64_t)dt.view.n_leaves * 2048;
-    const int64_t lo = int64_t(1) << 21, hi = int64_t(1) << 24;
+    // 2D: the evaluation is bound by the 16-byte point gather, so the chunk's points must stay in L2 (4 Mi points =
+    // 64 MB); 3D is FP64 bound and gathers out of DRAM without loss, so padding waste decides
+    const int64_t lo = int64_t(1) << 21, hi = dt.view.dim == 2 ? int64_t(1) << 22 : int64_t(1) << 24;
     return c < lo ? lo : (c > hi ? hi : c);
 }
 
@@ -162,7 +164,7 @@ void destroy_context(ExecContext &c) {
 }
 
 bool use_binned(const Function *f, const DeviceTree &dt, int64_t n) {
-    if (!binned_supported(dt.view.dim, dt.view.order))
+    if (!binned_supported(dt.view.dim, dt.view.order) || !binned_fits(dt))
         return false;
     if (f->mode == kDirect || f->mode == kBucketed)
         return false;
@@ -171,7 +173,9 @@ bool use_binned(const Function *f, const DeviceTree &dt, int64_t n) {
     // auto: worth it when the per-point coefficient gather (order^dim doubles) dwarfs the point itself and
     // there are enough points per leaf to fill warp tiles
     const int64_t block_bytes = 8 * (int64_t)std::pow((double)dt.view.order, dt.view.dim);
-    return dt.view.dim == 3 && block_bytes >= 1024 && n >= 64 * (int64_t)dt.view.n_leaves && n >= (1 << 16);
+    if (dt.view.dim == 2) // every lane gathering its own block is bound by the L1 tag rate at any block size
+        return n >= 64 * (int64_t)dt.view.n_leaves && n >= (1 << 20);
+    return block_bytes >= 1024 && n >= 64 * (int64_t)dt.view.n_leaves && n >= (1 << 16);
 }
 
 // Bucketed path: when the tree (nodes + coefficients) is too big for L2 the direct kernel's gathers go to DRAM,

@@ -282,6 +282,166 @@ bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__res
     cp_async_wait<0>();
 }
 
+// ------------------------------------------------------------------------------------------ K4, 2D
+// Same scheme for 2D trees: one warp per tile of 32*P slots of one leaf, the leaf's O x O block resident in the warp's
+// shared memory for a whole run of tiles, every coefficient a warp-uniform load feeding P FMAs per lane.  Arithmetic of
+// cheb_eval_2d (template.hpp:163-177): tmp = C * T(y) row by row in k order, value = <T(x), tmp> as the scalar halving
+// tree; products with T_0 = 1 are not executed.  (Thread per point, every lane gathers its own block: 8e9 evals/s on the
+// L2-resident C1 tree, bound by the L1 tag rate.)
+template <int O, int P>
+struct Run2Smem { // per warp
+    static constexpr int TILE = 32 * P;
+    double2 coeff[O * O / 2];
+    double2 node[4];
+    double pts[2][2 * TILE];
+    uint32_t idx[2][TILE];
+};
+
+template <int O, int P, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+bin_eval2d_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                  const uint32_t *__restrict__ perm, const uint2 *__restrict__ tile_info,
+                  const uint32_t *__restrict__ n_tiles_p) {
+    constexpr int TILE = 32 * P;
+    constexpr int BLK2 = O * O / 2;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t n_tiles = __ldg(n_tiles_p);
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    Run2Smem<O, P> &rs = reinterpret_cast<Run2Smem<O, P> *>(smem_raw)[warp];
+    const uint32_t nw = gridDim.x * WARPS, wid = blockIdx.x * WARPS + warp;
+    uint32_t t = (uint32_t)(((uint64_t)n_tiles * wid) / nw);
+    const uint32_t t_end = (uint32_t)(((uint64_t)n_tiles * (wid + 1)) / nw);
+
+    auto load_meta = [&](uint32_t tt, uint2 &info, uint32_t (&id)[P]) {
+        if (tt < t_end) {
+            info = __ldg(tile_info + tt);
+#pragma unroll
+            for (int p = 0; p < P; ++p)
+                id[p] = __ldg(perm + (size_t)tt * TILE + p * 32 + lane);
+        } else {
+            info = make_uint2(0, 0);
+#pragma unroll
+            for (int p = 0; p < P; ++p)
+                id[p] = kInvalidSlotE;
+        }
+    };
+    auto issue = [&](uint32_t tt, const uint32_t (&id)[P], int sidx) {
+        if (tt < t_end) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                rs.idx[sidx][p * 32 + lane] = id[p];
+                if (id[p] != kInvalidSlotE) // a 2D point is one aligned 16-byte item
+                    cp_async16(&rs.pts[sidx][2 * (p * 32 + lane)], x + 2ull * id[p]);
+            }
+        }
+        cp_async_commit();
+    };
+
+    uint2 info_n, info_cur;
+    uint32_t idx_n[P];
+    load_meta(t, info_n, idx_n);
+    issue(t, idx_n, 0);
+    info_cur = info_n;
+    load_meta(t + 1, info_n, idx_n);
+    uint32_t cur_node = 0xFFFFFFFFu;
+    int cur = 0;
+    for (; t < t_end; ++t, cur ^= 1) {
+        __syncwarp();
+        issue(t + 1, idx_n, cur ^ 1);
+        const uint2 info_next = info_n;
+        load_meta(t + 2, info_n, idx_n);
+        if (info_cur.x != cur_node) { // warp uniform: a new leaf starts here
+            cur_node = info_cur.x;
+            const double2 *Cg = reinterpret_cast<const double2 *>(tv.coeffs + 2ull * info_cur.y);
+            for (int j = lane; j < BLK2; j += 32)
+                cp_async16(&rs.coeff[j], Cg + j);
+            if (lane < 4)
+                cp_async16(&rs.node[lane], reinterpret_cast<const double2 *>(tv.nodes + info_cur.x) + lane);
+            cp_async_commit();
+            cp_async_wait<0>();
+        } else {
+            cp_async_wait<1>();
+        }
+        __syncwarp();
+        info_cur = info_next;
+        const double c0 = rs.node[0].x, c1 = rs.node[0].y, ih0 = rs.node[2].x, ih1 = rs.node[2].y;
+        double Ty[P][O], u[P], acc[P][O];
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const bool ok = rs.idx[cur][p * 32 + lane] != kInvalidSlotE;
+            const double2 q = *reinterpret_cast<const double2 *>(&rs.pts[cur][2 * (p * 32 + lane)]);
+            const double px = ok ? q.x : c0, py = ok ? q.y : c1; // padding lanes evaluate the leaf centre
+            u[p] = __dmul_rn(__dsub_rn(px, c0), ih0);
+            cheb_T<O>(__dmul_rn(__dsub_rn(py, c1), ih1), Ty[p]);
+        }
+#pragma unroll
+        for (int k = 1; k < O; ++k) {
+#pragma unroll
+            for (int r = 0; r < O; r += 2) {
+                const double2 c = rs.coeff[(k * O + r) / 2];
+                if (k == 1) {
+                    const double2 cz = rs.coeff[r / 2];
+#pragma unroll
+                    for (int p = 0; p < P; ++p) {
+                        acc[p][r] = __fma_rn(c.x, Ty[p][1], cz.x);
+                        acc[p][r + 1] = __fma_rn(c.y, Ty[p][1], cz.y);
+                    }
+                } else {
+#pragma unroll
+                    for (int p = 0; p < P; ++p) {
+                        acc[p][r] = __fma_rn(c.x, Ty[p][k], acc[p][r]);
+                        acc[p][r + 1] = __fma_rn(c.y, Ty[p][k], acc[p][r + 1]);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            double Tx[O];
+            cheb_T<O>(u[p], Tx);
+            const double val = dot_tree_one<0, O, 1, 0, O>(Tx, acc[p]);
+            const uint32_t id = rs.idx[cur][p * 32 + lane];
+            if (id != kInvalidSlotE)
+                res[id] = val;
+        }
+    }
+    cp_async_wait<0>();
+}
+
+template <int O, int P, int WARPS>
+static int launch_k4_2d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
+    auto kern = bin_eval2d_kernel<O, P, WARPS>;
+    constexpr size_t smem = sizeof(Run2Smem<O, P>) * WARPS;
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess)
+            return (int)e;
+        configured = true;
+    }
+    int per_sm = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS * 32, smem);
+    if (per_sm < 1)
+        per_sm = 1;
+    kern<<<dt.sm_count * per_sm, WARPS * 32, smem, st>>>(dt.view, d_x, d_res, ws.perm, ws.tile_info, ws.n_tiles);
+    return (int)cudaGetLastError();
+}
+
+// points per lane of the 2D kernel for this order
+int bin_eval2d_P(int order) { return order <= 10 ? 4 : 2; }
+
+int launch_bin_eval2d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
+    switch (dt.view.order) {
+    case 6: return launch_k4_2d<6, 4, 12>(dt, ws, d_x, d_res, st);
+    case 8: return launch_k4_2d<8, 4, 12>(dt, ws, d_x, d_res, st);
+    case 10: return launch_k4_2d<10, 4, 12>(dt, ws, d_x, d_res, st);
+    case 12: return launch_k4_2d<12, 2, 12>(dt, ws, d_x, d_res, st);
+    case 14: return launch_k4_2d<14, 2, 12>(dt, ws, d_x, d_res, st);
+    case 16: return launch_k4_2d<16, 2, 12>(dt, ws, d_x, d_res, st);
+    default: return (int)cudaErrorInvalidValue;
+    }
+}
+
 // ------------------------------------------------------------------------------------------ K4, FP64 tensor cores
 // Order 8 on the DMMA path.  Measured on B200 (scripts/micro/): a DFMA stream with two fresh register operands per
 // instruction (the register-blocked loop above) tops out at ~77 % of the FP64 peak once its coefficients come from

@@ -32,6 +32,8 @@ constexpr uint32_t kInvalidSlot = 0xFFFFFFFFu;
 constexpr int kBinThreads = 256;
 
 int bin_eval_select(int order, int *P);
+int bin_eval2d_P(int order);
+int launch_bin_eval2d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st);
 bool bin_eval_footprint(int variant, int *cta_regs, size_t *cta_smem);
 int launch_bin_eval3d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st);
 
@@ -365,7 +367,12 @@ bin_scatter_kernel(const uint32_t *__restrict__ key, const uint32_t *__restrict_
 }
 
 // ------------------------------------------------------------------------------------------ host side
-bool binned_supported(int dim, int order) { return dim == 3 && order >= 6 && order <= 16 && order % 2 == 0; }
+// 2D needs the fused sort (per-leaf histogram in shared memory); 3D falls back to the four-kernel sort
+bool binned_fits(const DeviceTree &dt) {
+    return dt.view.dim == 3 || (size_t)dt.view.n_leaves * sizeof(uint32_t) <= kFusedSortMaxSmem;
+}
+
+bool binned_supported(int dim, int order) { return (dim == 2 || dim == 3) && order >= 6 && order <= 16 && order % 2 == 0; }
 
 int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     if (chunk < 1)
@@ -373,10 +380,17 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     if (chunk > 0x7FFFFFFFll)
         chunk = 0x7FFFFFFFll;
     int P = 0;
-    ws.variant = bin_eval_select(dt.view.order, &P);
-    if (ws.variant < 0)
-        return (int)cudaErrorInvalidValue;
+    const bool is2d = dt.view.dim == 2;
+    if (is2d) {
+        P = bin_eval2d_P(dt.view.order);
+        ws.variant = -1;
+    } else {
+        ws.variant = bin_eval_select(dt.view.order, &P);
+        if (ws.variant < 0)
+            return (int)cudaErrorInvalidValue;
+    }
     ws.P = P;
+    const void *sort_fn = is2d ? (const void *)bin_sort_fused_kernel<2, false> : (const void *)bin_sort_fused_kernel<3, false>;
     const int64_t tile = 32 * P;
     const int64_t nl = dt.view.n_leaves;
     ws.perm_capacity = chunk + nl * tile;
@@ -392,7 +406,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     ws.sort_ctas = 0;
     if (ws.fused) { // cooperative launch: the grid is what is co-resident
         const size_t hist = (size_t)nl * sizeof(uint32_t);
-        cudaFuncSetAttribute(bin_sort_fused_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
+        cudaFuncSetAttribute(sort_fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
         int want = 2;
         if (const char *e = std::getenv("BAOBZI_B200_SORT_CTAS"))
             if (std::atoi(e) > 0)
@@ -407,7 +421,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             cap = (cap + 7) / 8 * 8;
             const size_t smem = hist + (size_t)cap * sizeof(uint16_t);
             if (smem <= kFusedSortMaxSmem) {
-                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<3, false>, kSortThreads, smem);
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sort_fn, kSortThreads, smem);
                 if (per_sm >= want) {
                     per_sm = want;
                     ws.sort_skey = (uint32_t)cap;
@@ -416,7 +430,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             }
         }
         if (!ws.sort_skey) {
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_sort_fused_kernel<3, false>, kSortThreads, hist);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sort_fn, kSortThreads, hist);
             per_sm = per_sm < want ? per_sm : want;
         }
         // optional: the coalescing scatter (three tables + the 16-bit local order of the CTA's range).  Measured on
@@ -430,7 +444,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             const size_t smem = 3 * hist + 8 + (size_t)cap * sizeof(uint16_t);
             int occ = 0;
             if (cap <= 0xFFFF && smem <= kFusedSortMaxSmem &&
-                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, bin_sort_fused_kernel<3, false>, kSortThreads, smem) ==
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sort_fn, kSortThreads, smem) ==
                     cudaSuccess &&
                 occ >= want) {
                 per_sm = want;
@@ -452,8 +466,8 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         // Measured on B200 (C3): beside the evaluation kernel the sort is left 6 warps per SM and takes 3.3x as long, and
         // its L2 traffic slows the evaluation by a third -- 18.1 ms per 2e8 points against 13.6 ms back to back.
         // Off by default; BAOBZI_B200_OVERLAP=1 enables it.
-        if (ws.fused && ov && std::atoi(ov) != 0 && bin_eval_footprint(ws.variant, &k4_regs, &k4_smem) &&
-            cudaFuncGetAttributes(&sa, bin_sort_fused_kernel<3, false>) == cudaSuccess) {
+        if (ws.fused && !is2d && ov && std::atoi(ov) != 0 && bin_eval_footprint(ws.variant, &k4_regs, &k4_smem) &&
+            cudaFuncGetAttributes(&sa, sort_fn) == cudaSuccess) {
             const int per_warp = (sa.numRegs * 32 + 511) / 512 * 512;
             int warps = (65536 - k4_regs) / per_warp;
             warps = warps > kSortThreads / 32 ? kSortThreads / 32 : warps;
@@ -475,6 +489,8 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             std::fprintf(stderr, "baobzi: fused sort: %d CTAs/SM, %zu B smem, %u shared keys / %u local-sort slots per CTA, chunk %lld\n",
                          per_sm, ws.sort_smem, ws.sort_skey, ws.sort_coal, (long long)chunk);
     }
+    if (is2d && !ws.fused)
+        return (int)cudaErrorInvalidValue; // the four-kernel fallback sort exists for 3D only
     cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
     if (e == cudaSuccess)
         e = cudaMalloc((void **)&ws.perm, sizeof(uint32_t) * ws.perm_capacity);
@@ -590,7 +606,8 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         int bshift = 0;
         void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
                         &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start, &coal};
-        rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3, false>, dim3(grid), dim3(ws.sort_threads), args,
+        rc_sort = (int)cudaLaunchCooperativeKernel(tv.dim == 2 ? (void *)bin_sort_fused_kernel<2, false> : (void *)bin_sort_fused_kernel<3, false>,
+                                                   dim3(grid), dim3(ws.sort_threads), args,
                                                    ws.sort_smem, ss);
         if (pf) {
             cudaEventRecord(ev[1], ss);
@@ -630,7 +647,8 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         int bshift = 0;
         void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
                         &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start, &coal};
-        rc_sort = (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<3, false>, dim3(grid), dim3(ws.sort_threads), args,
+        rc_sort = (int)cudaLaunchCooperativeKernel(tv.dim == 2 ? (void *)bin_sort_fused_kernel<2, false> : (void *)bin_sort_fused_kernel<3, false>,
+                                                   dim3(grid), dim3(ws.sort_threads), args,
                                                    ws.sort_smem, st);
         if (pf) { // the three classic stages are one launch here: all of it is booked under "lookup"
             cudaEventRecord(ev[1], st);
@@ -650,7 +668,7 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         if (pf)
             cudaEventRecord(ev[3], st);
     }
-    int rc = launch_bin_eval3d(dt, ws, d_x, d_res, st);
+    int rc = tv.dim == 2 ? launch_bin_eval2d(dt, ws, d_x, d_res, st) : launch_bin_eval3d(dt, ws, d_x, d_res, st);
     if (pf) {
         cudaEventRecord(ev[4], st);
         pf->spans.push_back({kStageLookup, ev[0], ev[1], (int64_t)n});
@@ -665,7 +683,7 @@ int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x
                        cudaStream_t stream, int64_t *launches) {
     if (n <= 0)
         return 0;
-    if (dt.view.dim != 3 || ws.chunk_capacity <= 0)
+    if ((dt.view.dim != 3 && dt.view.dim != 2) || ws.bucketed || ws.chunk_capacity <= 0)
         return (int)cudaErrorInvalidValue;
     if (ws.overlap) { // fork: the side stream may start once everything queued before this call is done
         cudaEventRecord(ws.ev_begin, stream);
@@ -675,7 +693,7 @@ int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x
     const int64_t step = ws.chunk_limit > 0 && ws.chunk_limit < ws.chunk_capacity ? ws.chunk_limit : ws.chunk_capacity;
     for (int64_t o = 0; o < n && rc == 0; o += step) {
         const int64_t m = n - o < step ? n - o : step;
-        rc = launch_chunk_3d(dt, ws, d_x + 3 * o, d_res + o, (uint32_t)m, stream);
+        rc = launch_chunk_3d(dt, ws, d_x + dt.view.dim * o, d_res + o, (uint32_t)m, stream);
         if (launches)
             *launches += ws.fused ? 2 : 5;
     }

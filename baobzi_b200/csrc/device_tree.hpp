@@ -157,5 +157,6 @@ int launch_eval_perm(const DeviceTree &dt, const double *d_x, double *d_res, con
                      const uint32_t *d_n_slots, int64_t n_max, cudaStream_t stream);
 // true when the binned path is implemented for this (dim, order)
 bool binned_supported(int dim, int order);
+bool binned_fits(const DeviceTree &dt);
 
 } // namespace bz
