@@ -30,6 +30,7 @@
 namespace bz {
 
 constexpr uint32_t kInvalidSlotE = 0xFFFFFFFFu;
+constexpr int kMaxDevices = 64;
 
 __device__ __forceinline__ void cp_async8(void *smem, const void *gmem) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
@@ -412,12 +413,13 @@ template <int O, int P, int WARPS>
 static int launch_k4_2d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
     auto kern = bin_eval2d_kernel<O, P, WARPS>;
     constexpr size_t smem = sizeof(Run2Smem<O, P>) * WARPS;
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[kMaxDevices] = {}; // function attributes are per device
+    if (dt.device < 0 || dt.device >= kMaxDevices || !configured[dt.device]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess)
             return (int)e;
-        configured = true;
+        if (dt.device >= 0 && dt.device < kMaxDevices)
+            configured[dt.device] = true;
     }
     int per_sm = 1;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS * 32, smem);
@@ -628,12 +630,13 @@ template <int WARPS, bool DEFER>
 static int launch_k4_mma8(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
     auto kern = bin_eval3d_mma8_kernel<WARPS, DEFER>;
     constexpr size_t smem = sizeof(MmaStage) * 2 * WARPS;
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[kMaxDevices] = {}; // function attributes are per device
+    if (dt.device < 0 || dt.device >= kMaxDevices || !configured[dt.device]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess)
             return (int)e;
-        configured = true;
+        if (dt.device >= 0 && dt.device < kMaxDevices)
+            configured[dt.device] = true;
     }
     kern<<<dt.sm_count, WARPS * 32, smem, st>>>(dt.view, d_x, d_res, ws.perm, ws.tile_info, ws.n_tiles);
     return (int)cudaGetLastError();
@@ -653,12 +656,13 @@ static int launch_k4(const DeviceTree &dt, const BinWorkspace &ws, const double 
     auto kern = bin_eval3d_kernel<O, P, WARPS, TZFLY, TYKEEP, RUN>;
     constexpr size_t smem = RUN ? sizeof(RunSmem<O, P>) * WARPS : sizeof(PipeStage<O, P>) * 2 * WARPS;
     static_assert(smem <= 227 * 1024, "pipeline stages exceed the shared memory of an SM");
-    static bool configured = false; // per instantiation
-    if (!configured) {
+    static bool configured[kMaxDevices] = {}; // per instantiation and device (function attributes are per device)
+    if (dt.device < 0 || dt.device >= kMaxDevices || !configured[dt.device]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess)
             return (int)e;
-        configured = true;
+        if (dt.device >= 0 && dt.device < kMaxDevices)
+            configured[dt.device] = true;
     }
     kern<<<dt.sm_count, WARPS * 32, smem, st>>>(dt.view, d_x, d_res, ws.perm, ws.tile_info, ws.n_tiles);
     return (int)cudaGetLastError();
