@@ -350,7 +350,8 @@ def run_ours(args, cfg, rank, world, local_rank):
     if not args.no_e2e:
         import psutil
         need = n * (dim + 1) * 8
-        n_e = n if psutil.virtual_memory().available > 3 * need else max(1 << 20, int(psutil.virtual_memory().available / 3 / ((dim + 1) * 8)))
+        avail = psutil.virtual_memory().available / world  # every rank pins its own buffers at the same time
+        n_e = n if avail > 3 * need else max(1 << 20, int(avail / 3 / ((dim + 1) * 8)))
         n_e = min(n_e, 2**31 - 1)
         xh = torch.empty((n_e, dim), dtype=torch.float64, pin_memory=True)
         yh = torch.empty(n_e, dtype=torch.float64, pin_memory=True)
