@@ -58,6 +58,8 @@ ABI = {
     "baobzi_sync": (C.c_int, [baobzi_t]),
     "baobzi_set_mode": (C.c_int, [baobzi_t, C.c_int, C.c_int64]),
     "baobzi_eval_multi_device_all": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "baobzi_eval_multi_device_dot": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "baobzi_device_view": (C.c_int, [baobzi_t, C.c_int, C.c_void_p, C.c_size_t]),
     "baobzi_launch_count": (C.c_int64, [baobzi_t]),
     "baobzi_profile_begin": (C.c_int, [baobzi_t]),
     "baobzi_profile_end": (C.c_int, [baobzi_t, c_double_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
@@ -225,6 +227,39 @@ class Baobzi:
         if rc != 0:
             raise RuntimeError("baobzi_eval_multi_device_all failed with CUDA error %d" % rc)
         return out
+
+    def dot(self, x, w=None):
+        """sum_i w[i] * f(x[i]) over device-resident points (plain sum without w), evaluated and reduced on the GPU
+        without an n-sized result array (baobzi_eval_multi_device_dot).  Returns a 0-dim CUDA tensor."""
+        import torch
+        dp = _device_pointer(x)
+        if dp is None:
+            raise TypeError("dot takes a CUDA float64 tensor / array")
+        ptr, count, _keep = dp
+        n = count // self.dim
+        wptr = None
+        if w is not None:
+            wp = _device_pointer(w)
+            if wp is None or wp[1] != n:
+                raise TypeError("w must be a CUDA float64 tensor / array with one weight per point")
+            wptr = wp[0]
+        out = torch.empty((), dtype=torch.float64, device=x.device)
+        rc = self._lib.baobzi_eval_multi_device_dot(self.ptr, ptr, wptr, n, out.data_ptr(),
+                                                    torch.cuda.current_stream(x.device).cuda_stream)
+        if rc != 0:
+            raise RuntimeError("baobzi_eval_multi_device_dot failed with CUDA error %d" % rc)
+        return out
+
+    VIEW_BYTES = 160  # sizeof(baobzi_device::View), include/baobzi_device.cuh
+
+    def device_view(self, device=0):
+        """The bytes of the baobzi_device::View of the replica on `device`, to pass by value to a CUDA kernel that
+        includes include/baobzi_device.cuh (baobzi_device_view)."""
+        buf = C.create_string_buffer(self.VIEW_BYTES)
+        rc = self._lib.baobzi_device_view(self.ptr, int(device), buf, self.VIEW_BYTES)
+        if rc != 0:
+            raise RuntimeError("baobzi_device_view failed with error %d" % rc)
+        return buf.raw
 
     def node_index(self, x):
         """Global node index per point (the reference's Function::get_global_node_index), -1 outside."""

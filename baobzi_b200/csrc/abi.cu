@@ -43,6 +43,9 @@ struct Replica {
     std::vector<std::unique_ptr<ExecContext>> contexts;
     cudaStream_t shard_stream = nullptr; // baobzi_eval_multi_sharded
     BinWorkspace shard_ws;
+    // baobzi_eval_multi_device_dot: per-CTA partial sums, and the chunk of values of the binned / bucketed paths
+    double *dot_partial = nullptr, *dot_tmp = nullptr;
+    int64_t dot_partial_cap = 0, dot_tmp_cap = 0;
 };
 
 enum Mode { kAuto = 0, kDirect = 1, kBinned = 2, kBucketed = 3 };
@@ -413,6 +416,10 @@ void fn_free(void *obj) {
         if (r->shard_stream)
             cudaStreamDestroy(r->shard_stream);
         free_workspace(r->shard_ws);
+        if (r->dot_partial)
+            cudaFree(r->dot_partial);
+        if (r->dot_tmp)
+            cudaFree(r->dot_tmp);
         free_tree(r->dt);
     }
     delete f;
@@ -552,6 +559,80 @@ int baobzi_eval_multi_device_all(const baobzi_t func, const double *d_x, double 
     const int rc = bz::launch_eval_all_1d(r->dt, d_x, d_res, ntrg, (cudaStream_t)cuda_stream, &launches);
     f->launches += launches;
     return rc;
+}
+
+// grow a device buffer of doubles (the old one may still be in use by work queued on `stream`)
+static int reserve_doubles(double *&buf, int64_t &cap, int64_t want, cudaStream_t stream) {
+    if (cap >= want)
+        return 0;
+    if (buf) {
+        cudaStreamSynchronize(stream);
+        cudaFree(buf);
+        buf = nullptr;
+        cap = 0;
+    }
+    cudaError_t e = cudaMalloc(&buf, (size_t)want * sizeof(double));
+    if (e != cudaSuccess)
+        return (int)e;
+    cap = want;
+    return 0;
+}
+
+int baobzi_eval_multi_device_dot(const baobzi_t func, const double *d_x, const double *d_w, int64_t ntrg, double *d_out,
+                                 void *cuda_stream) {
+    Function *f = (Function *)func->obj;
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    if (ntrg <= 0)
+        return (int)cudaMemsetAsync(d_out, 0, sizeof(double), stream); // empty sum
+    int dev = bz::device_of_pointer(d_x);
+    if (dev < 0)
+        return (int)cudaErrorInvalidDevicePointer;
+    bz::Replica *r = bz::get_replica(f, dev);
+    if (!r)
+        return (int)cudaErrorMemoryAllocation;
+    bz::DeviceGuard g(dev);
+    std::lock_guard<std::mutex> lock(f->mu);
+    const int G = bz::dot_grid(r->dt);
+    int64_t launches = 0;
+    int rc = 0;
+    const bool binned = bz::use_binned(f, r->dt, ntrg), bucketed = !binned && bz::use_bucketed(f, r->dt, ntrg);
+    if (!binned && !bucketed) { // fused: the values never leave registers
+        rc = reserve_doubles(r->dot_partial, r->dot_partial_cap, G, stream);
+        if (rc == 0)
+            rc = bz::launch_eval_dot(r->dt, d_x, d_w, ntrg, r->dot_partial, stream, &launches);
+        if (rc == 0)
+            rc = bz::launch_sum_partials(r->dot_partial, G, d_out, stream, &launches);
+    } else { // grouped evaluation chunk by chunk into an L2-sized scratch array, consumed at once
+        int64_t step = f->chunk > 0 ? f->chunk : (binned ? bz::default_chunk(r->dt) : bz::default_bucket_chunk());
+        if (step > ntrg)
+            step = ntrg;
+        const int64_t n_chunks = (ntrg + step - 1) / step;
+        rc = reserve_doubles(r->dot_partial, r->dot_partial_cap, n_chunks * G, stream);
+        if (rc == 0)
+            rc = reserve_doubles(r->dot_tmp, r->dot_tmp_cap, step, stream);
+        for (int64_t c = 0; c < n_chunks && rc == 0; ++c) {
+            const int64_t off = c * step, m = std::min(step, ntrg - off);
+            rc = bz::eval_device(f, r, r->shard_ws, d_x + off * func->DIM, r->dot_tmp, m, stream);
+            if (rc == 0)
+                rc = bz::launch_dot(r->dt, r->dot_tmp, d_w ? d_w + off : nullptr, m, r->dot_partial + c * G, stream,
+                                    &launches);
+        }
+        if (rc == 0)
+            rc = bz::launch_sum_partials(r->dot_partial, n_chunks * G, d_out, stream, &launches);
+    }
+    f->launches += launches;
+    return rc;
+}
+
+int baobzi_device_view(const baobzi_t func, int device, void *view, size_t view_bytes) {
+    Function *f = (Function *)func->obj;
+    if (!view || view_bytes != sizeof(bz::TreeView))
+        return (int)cudaErrorInvalidValue; // header / library mismatch
+    bz::Replica *r = bz::get_replica(f, device);
+    if (!r)
+        return (int)cudaErrorMemoryAllocation;
+    std::memcpy(view, &r->dt.view, sizeof(bz::TreeView));
+    return 0;
 }
 
 int baobzi_node_index_multi_device(const baobzi_t func, const double *d_x, int64_t *d_idx, int64_t ntrg,

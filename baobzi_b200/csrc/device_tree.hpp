@@ -55,6 +55,8 @@ struct TreeView {
     const uint32_t *bin_first_leaf; // [n_bins + 1] dense rank of the first leaf of each grid cell's subtree
 };
 
+static_assert(sizeof(TreeView) == 160, "TreeView is part of the device ABI (include/baobzi_device.cuh, Baobzi.VIEW_BYTES)");
+
 // Optional per-launch timing (bench.py's roofline): when attached to a workspace / launch, every kernel is
 // bracketed by CUDA events on the launching stream; elapsed times are summed per stage after a sync.
 enum Stage { kStageLookup = 0, kStageScan = 1, kStageScatter = 2, kStageEval = 3, kStageDirect = 4, kNumStages = 5 };
@@ -136,6 +138,11 @@ void free_workspace(BinWorkspace &ws);
 // reference's global node index per point (-1 outside).  res may be nullptr (index query only).
 int launch_eval_direct(const DeviceTree &dt, const double *d_x, double *d_res, int64_t *d_node_idx, int64_t n,
                        cudaStream_t stream, int64_t *launches, StageProfile *prof = nullptr);
+// 1D trees that fit in shared memory (eval1d.cu): launch_eval_direct routes to this kernel from
+// table_1d_min_points() points up (env BAOBZI_B200_TABLE1D_MIN; negative = never).
+bool table_1d_fits(const DeviceTree &dt);
+int64_t table_1d_min_points();
+int launch_eval_table_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream);
 // Every output component of a 1D tree: d_res[i * out_dim + k] (what baobzi_eval writes to y[k], batched).
 int launch_eval_all_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream,
                        int64_t *launches);
@@ -155,6 +162,14 @@ int launch_eval_buckets(const DeviceTree &dt, const double *d_x, double *d_res, 
                         const uint32_t *d_key_start, uint32_t *d_queue, uint32_t n_keys, int bshift, cudaStream_t stream);
 int launch_eval_perm(const DeviceTree &dt, const double *d_x, double *d_res, const uint32_t *d_perm,
                      const uint32_t *d_n_slots, int64_t n_max, cudaStream_t stream);
+// Evaluation fused with a reduction (reduce.cu): per-CTA partial sums of w_i * f(x_i) (d_w may be null), dot_grid(dt)
+// of them per launch; launch_dot consumes an array of values instead; launch_sum_partials folds m partials into *d_out.
+int dot_grid(const DeviceTree &dt);
+int launch_eval_dot(const DeviceTree &dt, const double *d_x, const double *d_w, int64_t n, double *d_partial,
+                    cudaStream_t stream, int64_t *launches);
+int launch_dot(const DeviceTree &dt, const double *d_y, const double *d_w, int64_t n, double *d_partial,
+               cudaStream_t stream, int64_t *launches);
+int launch_sum_partials(const double *d_partial, int64_t m, double *d_out, cudaStream_t stream, int64_t *launches);
 // true when the binned path is implemented for this (dim, order)
 bool binned_supported(int dim, int order);
 bool binned_fits(const DeviceTree &dt);

@@ -14,10 +14,9 @@
 //           aligned slots, (4) evaluation where every warp works on ONE leaf, so each 16-byte
 //           coefficient load is a warp-uniform broadcast served from L1 and feeds 2*P FMAs
 //           (P points per thread, register blocked).  FP64-pipe bound.
-#include "cheb.cuh"
 #include "device_tree.hpp"
+#include "eval_point.cuh"
 #include "host_tree.hpp"
-#include "lookup.cuh"
 
 #include <algorithm>
 #include <cstdio>
@@ -25,25 +24,6 @@
 #include <vector>
 
 namespace bz {
-
-// Node::eval (template.hpp:366-369) for the first output component.
-template <int DIM, int ORDER>
-__device__ __forceinline__ double eval_leaf(const TreeView &tv, uint32_t node, const NodeHead &head,
-                                            const double (&x)[DIM]) {
-    const NodeTail tail = load_tail(tv.nodes, node);
-    const double *C = tv.coeffs + 2ull * head.coeff16;
-    const double u = __dmul_rn(__dsub_rn(x[0], head.c0), tail.ih0);
-    if constexpr (DIM == 1) {
-        return cheb_eval_1d<ORDER>(u, C);
-    } else if constexpr (DIM == 2) {
-        const double v = __dmul_rn(__dsub_rn(x[1], head.c1), tail.ih1);
-        return cheb_eval_2d<ORDER>(u, v, C, LdgLoad());
-    } else {
-        const double v = __dmul_rn(__dsub_rn(x[1], head.c1), tail.ih1);
-        const double w = __dmul_rn(__dsub_rn(x[2], head.c2), tail.ih2);
-        return cheb_eval_3d<ORDER>(u, v, w, C, LdgLoad());
-    }
-}
 
 // ------------------------------------------------------------------------------------------ direct
 constexpr int kDirectThreads = 128;
@@ -300,12 +280,20 @@ int launch_eval_direct(const DeviceTree &dt, const double *d_x, double *d_res, i
         ee = prof->get();
         cudaEventRecord(eb, stream);
     }
-    // enough CTAs to fill every SM several times over, capped so the grid-stride loop amortises launch cost
-    const int64_t want = (n + kDirectThreads - 1) / kDirectThreads;
-    const int64_t cap = (int64_t)dt.sm_count * 64;
-    const unsigned grid = (unsigned)(want < cap ? want : cap);
-    BZ_DISPATCH(dt.view.dim, dt.view.order,
-                (eval_direct_kernel<D, O><<<grid, kDirectThreads, 0, stream>>>(dt.view, d_x, d_res, d_node_idx, n)));
+    const int64_t table_min = table_1d_min_points();
+    if (dt.view.dim == 1 && d_res && !d_node_idx && table_min >= 0 && n >= table_min && table_1d_fits(dt)) {
+        // 1D: the tree lives in shared memory (eval1d.cu)
+        const int rc = launch_eval_table_1d(dt, d_x, d_res, n, stream);
+        if (rc != 0)
+            return rc;
+    } else {
+        // enough CTAs to fill every SM several times over, capped so the grid-stride loop amortises launch cost
+        const int64_t want = (n + kDirectThreads - 1) / kDirectThreads;
+        const int64_t cap = (int64_t)dt.sm_count * 64;
+        const unsigned grid = (unsigned)(want < cap ? want : cap);
+        BZ_DISPATCH(dt.view.dim, dt.view.order,
+                    (eval_direct_kernel<D, O><<<grid, kDirectThreads, 0, stream>>>(dt.view, d_x, d_res, d_node_idx, n)));
+    }
     if (prof) {
         cudaEventRecord(ee, stream);
         prof->mark(kStageDirect, n, eb, ee);

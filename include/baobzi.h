@@ -15,6 +15,7 @@
 #ifndef BAOBZI_B200_BAOBZI_H
 #define BAOBZI_B200_BAOBZI_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -124,6 +125,20 @@ int baobzi_eval_multi_device(const baobzi_t func, const double *d_x, double *d_r
  * the domain.  baobzi_eval_multi itself keeps the reference's behaviour (first component only).  DIM must be 1
  * (cudaErrorNotSupported otherwise).  Asynchronous on `cuda_stream`. */
 int baobzi_eval_multi_device_all(const baobzi_t func, const double *d_x, double *d_res, int64_t ntrg, void *cuda_stream);
+
+/* Evaluation fused with a consumer (no reference counterpart): *d_out = sum_i d_w[i] * f(d_x[i]) over
+ * ntrg device-resident points, d_w == NULL for the plain sum, without an ntrg-sized result array (the values stay in
+ * registers on the direct path, in an L2-sized scratch chunk on the binned / bucketed paths).  The f values are the
+ * bit-exact ones of baobzi_eval_multi; a point outside the domain contributes NaN, as it would through res[].  The
+ * summation order depends only on (ntrg, device, mode), so repeated calls give identical bits.  d_out is a device
+ * pointer; asynchronous on `cuda_stream`. */
+int baobzi_eval_multi_device_dot(const baobzi_t func, const double *d_x, const double *d_w, int64_t ntrg, double *d_out,
+                                 void *cuda_stream);
+
+/* Device-side hook: fills *view (a baobzi_device::View of include/baobzi_device.cuh, view_bytes = sizeof of it) with
+ * the device layout of the replica on `device` (created on first use), for kernels of the caller that evaluate the
+ * function in registers with baobzi_device::eval<DIM, ORDER>.  Valid until baobzi_free. */
+int baobzi_device_view(const baobzi_t func, int device, void *view, size_t view_bytes);
 
 /* Global node index per point, exactly Function::get_global_node_index of the reference
  * (baobzi_template.hpp:846-849; all nodes, subtree-major, breadth-first inside a subtree);

@@ -1,7 +1,4 @@
-run() { name=$1; shift
-env "$@" python bench.py ${ARGS} --steps 3 --warmup 3 --no-cpu --no-e2e > gpurun_out/var_$name.json 2> gpurun_out/var_$name.err
-python -c "
-import json; d=json.load(open('gpurun_out/var_$name.json')); r=d['roofline']; print('$name value=%.3e ms=%.2f'%(d['value'], d['ms_per_step']), 'frac=%.3f'%r['frac'], {k:round(v,2) for k,v in r['stages_ms_per_step'].items()})" || tail -3 gpurun_out/var_$name.err
-}
-ARGS="--points 400000000"
-for c in 4194304 6291456 8388608 12582912 16777216; do run chunk_$c BAOBZI_B200_CHUNK=$c; done
+# scratch experiment: device hooks + full GPU suite + C2 line
+timeout 900 python -m pytest tests/test_device_hook.py -x -q -m gpu 2>&1 | tail -8
+timeout 1500 python -m pytest tests -x -q -m gpu 2>&1 | tail -3
+timeout 300 python bench.py --workload C2 --steps 5 --warmup 3 > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err; tail -c 600 gpurun_out/bench_c2.json

@@ -100,3 +100,49 @@ def test_eval_all_multi_output_1d(gpu_lib, ref):
     with pytest.raises(RuntimeError):
         b3.eval_all(torch.zeros((4, 3), dtype=torch.float64, device="cuda"))
     b3.free()
+
+
+ONE_D = ["t1d_o6", "t1d_o8", "t1d_o10", "t1d_o12", "t1d_o14", "t1d_o16", "deep_1d", "tc_1d2"]
+
+
+@pytest.mark.parametrize("name", ONE_D)
+def test_table_1d_kernel_bits(gpu_lib, ref, name):
+    """The shared-memory 1D kernel (eval1d.cu) forced on from the first point: golden points (edge cases included)
+    and seeded points over and slightly beyond the domain, 0 ulp against the reference's AVX2+FMA values, ragged
+    sizes around the tile size, an odd (8-byte aligned only) input offset, and the generic kernel's bits."""
+    import torch
+    from conftest import load_golden
+    from test_parity_gpu import ulp
+    path, g = load_golden(name)
+    t = ref.OracleTree(path)
+    a = t.arrays()
+    rng = np.random.default_rng(21)
+    n = 200_003
+    x = a["lower_left"] + rng.random((n, 1)) * (a["upper_right"] - a["lower_left"]) * 1.02 - 0.01
+    x[::1001] = np.nan
+    want = t.eval_multi(x, ref.ARITH_AVX2)
+    gx = np.ascontiguousarray(g["x"]).reshape(-1, 1)
+    gwant = t.eval_multi(gx, ref.ARITH_AVX2)
+    old = os.environ.get("BAOBZI_B200_TABLE1D_MIN")
+    try:
+        b = gpu_lib.Baobzi(filename=path, mode="direct")
+        os.environ["BAOBZI_B200_TABLE1D_MIN"] = "-1"       # generic direct kernel
+        xd = torch.from_numpy(x).cuda()
+        y_generic = b(xd).cpu().numpy()
+        os.environ["BAOBZI_B200_TABLE1D_MIN"] = "0"        # table kernel from the first point
+        launches = b.launches
+        y = b(xd).cpu().numpy()
+        assert b.launches == launches + 1
+        assert ulp(ref, y, want) == 0
+        assert np.array_equal(np.isnan(y), np.isnan(want))
+        assert y.tobytes() == y_generic.tobytes()
+        assert ulp(ref, b(torch.from_numpy(gx).cuda()).cpu().numpy(), gwant) == 0
+        for m in (1, 31, 1023, 1024, 1025, 4097, 65_537):   # ragged tails, and an odd element offset
+            ym = b(xd[1:1 + m]).cpu().numpy()
+            assert ym.tobytes() == y[1:1 + m].tobytes(), m
+        b.free()
+    finally:
+        if old is None:
+            os.environ.pop("BAOBZI_B200_TABLE1D_MIN", None)
+        else:
+            os.environ["BAOBZI_B200_TABLE1D_MIN"] = old
