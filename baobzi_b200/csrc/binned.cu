@@ -76,6 +76,31 @@ constexpr int kSortPts = 4; // independent lookups in flight per thread (the loo
 
 // BYBIN (the bucketed path of large 1D / 2D trees): the key is the grid cell number >> bshift instead of the leaf,
 // so the sort touches no tree data; TILE is 1 and no tile descriptors are written (tile_info == nullptr).
+constexpr uint32_t kBigLeafCap = 128;
+
+// Shared-memory counter increment for a warp whose lanes may hold the same key (k == kNotLeaf: no increment).
+// Returns the value the lane's own atomicAdd(tbl + k, 1) would have returned, up to the order inside the warp.
+// `heavy` (warp uniform) says most lanes share keys -- clustered or ordered input, where 32 same-address ATOMS
+// per warp and 16 warps on one bank made the sort 5x slower than on uniform points: the lanes of each key then
+// elect a leader that adds the group's size once.  All 32 lanes must call this together.
+__device__ __forceinline__ uint32_t grouped_add(uint32_t *tbl, uint32_t k, bool heavy, uint32_t lane) {
+    if (!heavy)
+        return k != kNotLeaf ? atomicAdd(tbl + k, 1u) : 0u;
+    const uint32_t grp = __match_any_sync(0xffffffffu, k);
+    const int leader = __ffs(grp) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader && k != kNotLeaf)
+        base = atomicAdd(tbl + k, (uint32_t)__popc(grp));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + (uint32_t)__popc(grp & ((1u << lane) - 1u));
+}
+
+// warp uniform: do at least half of the lanes hold the key of their right neighbour?
+__device__ __forceinline__ bool keys_repeat(uint32_t k, uint32_t lane) {
+    const uint32_t nb = __shfl_sync(0xffffffffu, k, (lane + 1) & 31);
+    return __popc(__ballot_sync(0xffffffffu, nb == k && k != kNotLeaf)) >= 16;
+}
+
 template <int DIM, bool BYBIN>
 __global__ void __launch_bounds__(kSortThreads)
 bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
@@ -85,6 +110,10 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
                       uint32_t n_keys, int bshift, uint32_t *__restrict__ key_start, uint32_t coal_cap) {
     extern __shared__ uint32_t tbl[]; // [n_keys] histogram -> base -> next free slot
     __shared__ uint32_t warp_sums[32];
+    __shared__ uint4 big[kBigLeafCap];
+    __shared__ uint32_t n_big;
+    if (threadIdx.x == 0)
+        n_big = 0;
     const uint32_t nl = n_keys;
     // keys of the CTA's own range as 16-bit leaf ranks in shared memory when they fit (skey_cap entries follow
     // tbl[]): the scatter then never goes back to global memory for them
@@ -104,14 +133,16 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     const bool coalesce = coal_cap > 0 && hi - lo <= coal_cap;
 
     // ---- phase A
-    for (uint32_t i0 = lo + tid; i0 < hi; i0 += kSortPts * nthr) {
+    const uint32_t lane_id = tid & 31;
+    for (uint32_t b0 = lo; b0 < hi; b0 += kSortPts * nthr) { // CTA-uniform trip count: the warps stay converged
+        const uint32_t i0 = b0 + tid;
         double p[kSortPts][DIM];
         bool have[kSortPts];
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u) {
             const uint32_t i = i0 + u * nthr;
             have[u] = i < hi;
-            load_point_keep<DIM>(x, have[u] ? i : i0, p[u]); // default cache policy: K4 gathers these again
+            load_point_keep<DIM>(x, have[u] ? i : lo, p[u]); // default cache policy: K4 gathers these again
         }
         uint32_t leaf[kSortPts], lin[kSortPts];
 #pragma unroll
@@ -126,19 +157,19 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
             else if (!BYBIN && leaf[u] == kNotLeaf)
                 leaf[u] = walk_to_leaf<DIM>(tv, lin[u], p[u]);
         }
+        const bool heavy = keys_repeat(leaf[0], lane_id);
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u) {
-            if (!have[u])
-                continue;
             const uint32_t i = i0 + u * nthr;
-            if (use_skey && !coalesce)
-                skey[i - lo] = (uint16_t)leaf[u]; // kNotLeaf -> 0xFFFF (n_leaves < 0xFFFF when skey_cap > 0)
-            else
-                key[i] = leaf[u];
-            if (leaf[u] == kNotLeaf)
-                res[i] = __longlong_as_double(0x7ff8000000000000ll);
-            else
-                atomicAdd(tbl + leaf[u], 1u);
+            if (have[u]) {
+                if (use_skey && !coalesce)
+                    skey[i - lo] = (uint16_t)leaf[u]; // kNotLeaf -> 0xFFFF (n_leaves < 0xFFFF when skey_cap > 0)
+                else
+                    key[i] = leaf[u];
+                if (leaf[u] == kNotLeaf)
+                    res[i] = __longlong_as_double(0x7ff8000000000000ll);
+            }
+            grouped_add(tbl, leaf[u], heavy, lane_id); // lanes past the end hold kNotLeaf
         }
     }
     __syncthreads();
@@ -183,18 +214,28 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     }
     __syncthreads();
     uint32_t start = (warp ? warp_sums[warp - 1] : 0u) + incl - mine;
+    // A leaf holding a large share of the chunk (clustered input: up to every tile of it) gets its tile descriptors
+    // from the whole grid, not from one thread: 65 K tiles of one leaf took 0.6 ms per chunk that way.  "Large" is
+    // more than 1/kBigLeafCap of all tiles, so the list below cannot overflow and is the same in every CTA.
+    const uint32_t big_tiles = max(256u, warp_sums[nthr / 32 - 1] / TILE / kBigLeafCap);
+    const uint32_t start0 = start;
+    bool any_big = false;
     for (uint32_t l = l0; l < l1; ++l) {
         const uint32_t c = __ldcg(count + ((size_t)l << cshift));
         const uint32_t padded = (c + TILE - 1) / TILE * TILE;
+        const bool is_big = !BYBIN && padded / TILE > big_tiles;
+        any_big = any_big || is_big;
         if (l % gridDim.x == blockIdx.x) { // this CTA's leaves: padding slots, tile descriptors, counter reset
             if (!BYBIN) {
                 for (uint32_t s = start + c; s < start + padded; ++s)
                     perm[s] = kInvalidSlot;
-                const uint32_t node = __ldg(tv.leaf_node + l);
-                const uint2 info = make_uint2(node, load_head(tv.nodes, node).coeff16);
-                for (uint32_t t = start / TILE; t < (start + padded) / TILE; ++t) {
-                    tile_leaf[t] = l;
-                    tile_info[t] = info;
+                if (!is_big) {
+                    const uint32_t node = __ldg(tv.leaf_node + l);
+                    const uint2 info = make_uint2(node, load_head(tv.nodes, node).coeff16);
+                    for (uint32_t t = start / TILE; t < (start + padded) / TILE; ++t) {
+                        tile_leaf[t] = l;
+                        tile_info[t] = info;
+                    }
                 }
             }
             count_next[(size_t)l << cshift] = 0; // the buffer the NEXT chunk histograms into
@@ -204,6 +245,16 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         tbl[l] += start;
         start += padded;
     }
+    if (any_big) { // rare: list this thread's big leaves (kept out of the loop above: an atomic there serialises its loads)
+        uint32_t s2 = start0;
+        for (uint32_t l = l0; l < l1; ++l) {
+            const uint32_t c = __ldcg(count + ((size_t)l << cshift));
+            const uint32_t padded = (c + TILE - 1) / TILE * TILE;
+            if (padded / TILE > big_tiles) // every CTA lists the same (fewer than kBigLeafCap) leaves
+                big[atomicAdd(&n_big, 1u)] = make_uint4(l, s2 / TILE, padded / TILE, __ldg(tv.leaf_node + l));
+            s2 += padded;
+        }
+    }
     if (blockIdx.x == 0 && tid == nthr - 1) {
         *n_tiles = (warp_sums[nthr / 32 - 1]) / TILE;
         if (BYBIN) {
@@ -212,6 +263,16 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         }
     }
     __syncthreads();
+    if (!BYBIN) {
+        for (uint32_t e = 0; e < n_big; ++e) {
+            const uint4 b = big[e]; // {leaf, first tile, tiles, node}
+            const uint2 info = make_uint2(b.w, load_head(tv.nodes, b.w).coeff16);
+            for (uint32_t t = blockIdx.x * nthr + tid; t < b.z; t += gridDim.x * nthr) {
+                tile_leaf[b.y + t] = b.x;
+                tile_info[b.y + t] = info;
+            }
+        }
+    }
 
     // ---- scatter
     if (coalesce) {
@@ -259,7 +320,8 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         }
         return;
     }
-    for (uint32_t i0 = lo + tid; i0 < hi; i0 += kSortPts * nthr) {
+    for (uint32_t b0 = lo; b0 < hi; b0 += kSortPts * nthr) {
+        const uint32_t i0 = b0 + tid;
         uint32_t k[kSortPts];
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u) {
@@ -271,10 +333,13 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
                 k[u] = i < hi ? __ldcs(key + i) : kNotLeaf;
             }
         }
+        const bool heavy = keys_repeat(k[0], lane);
 #pragma unroll
-        for (int u = 0; u < kSortPts; ++u)
+        for (int u = 0; u < kSortPts; ++u) {
+            const uint32_t slot = grouped_add(tbl, k[u], heavy, lane);
             if (k[u] != kNotLeaf)
-                perm[atomicAdd(tbl + k[u], 1u)] = i0 + u * nthr;
+                perm[slot] = i0 + u * nthr;
+        }
     }
 }
 
@@ -456,6 +521,21 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         ws.sort_ctas = dt.sm_count * per_sm;
         ws.sort_threads = kSortThreads;
         ws.fused = per_sm >= 1;
+        // Shared memory / L1 split: by default the driver sizes the carve-out for as many CTAs as shared memory could
+        // hold (3 at 65 KB each => 200 or 233 KB), but only per_sm are ever resident (cooperative grid).  Ask for what
+        // they need and leave the rest to L1, which serves the bin_leaf / node-record gathers of the lookup: a 2 KB
+        // growth of the static shared memory once pushed the carve-out from 200 to 233 KB and the 2D sort from 3.1 to
+        // 4.6 ms per 1e8 points (ncu: launch__shared_mem_config_size).
+        cudaFuncAttributes fa;
+        if (per_sm >= 1 && cudaFuncGetAttributes(&fa, sort_fn) == cudaSuccess) {
+            const double need = (double)per_sm * (double)(ws.sort_smem + fa.sharedSizeBytes + 1024);
+            int pct = (int)(100.0 * need / (228.0 * 1024.0)) + 1;
+            pct = pct > 100 ? 100 : pct;
+            if (const char *e = std::getenv("BAOBZI_B200_SORT_CARVEOUT"))
+                pct = std::atoi(e);
+            if (pct >= 0)
+                cudaFuncSetAttribute(sort_fn, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        }
         // Overlap: can one sort CTA per SM live beside the evaluation kernel's CTA?  Then the sort of the next chunk
         // runs concurrently with the evaluation of this one (different streams); the sort is sized to what is left.
         ws.sort_overlap_ok = false;

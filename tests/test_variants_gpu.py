@@ -146,3 +146,39 @@ def test_table_1d_kernel_bits(gpu_lib, ref, name):
             os.environ.pop("BAOBZI_B200_TABLE1D_MIN", None)
         else:
             os.environ["BAOBZI_B200_TABLE1D_MIN"] = old
+
+
+@pytest.mark.parametrize("name", ["t3d_o8", "t2d_o8"])
+def test_clustered_and_ordered_inputs(gpu_lib, ref, name):
+    """Inputs that are not uniform random: every point inside ONE leaf (its tile descriptors are then written by the
+    whole grid and the histogram updates are aggregated per warp, binned.cu), two heavy leaves plus a sprinkle of
+    others, and a lattice in C order -- same bits as the oracle in the binned path."""
+    import torch
+    from conftest import load_golden
+    from test_parity_gpu import ulp
+    path, g = load_golden(name)
+    t = ref.OracleTree(path)
+    a = t.arrays()
+    dim = len(a["lower_left"])
+    lo, hi = a["lower_left"], a["upper_right"]
+    rng = np.random.default_rng(29)
+    n = 400_000
+    cases = {}
+    cases["one_leaf"] = lo + (0.31 + 1e-4 * rng.random((n, dim))) * (hi - lo)
+    mix = lo + rng.random((n, dim)) * (hi - lo)
+    mix[: n // 2] = lo + (0.62 + 1e-4 * rng.random((n // 2, dim))) * (hi - lo)
+    mix[n // 2: n - 1000] = lo + (0.17 + 1e-4 * rng.random((n - 1000 - n // 2, dim))) * (hi - lo)
+    cases["two_heavy_leaves"] = mix[rng.permutation(n)]
+    m = int(round(n ** (1.0 / dim)))
+    axes = [lo[j] + (np.arange(m) + 0.5) / m * (hi[j] - lo[j]) for j in range(dim)]
+    cases["lattice"] = np.stack(np.meshgrid(*axes, indexing="ij"), axis=-1).reshape(-1, dim)
+    b = gpu_lib.Baobzi(filename=path, mode="binned")
+    for label, x in cases.items():
+        x = np.ascontiguousarray(x)
+        want = t.eval_multi(x, ref.ARITH_AVX2)
+        xd = torch.from_numpy(x).cuda()
+        for chunk in (0, 150_001):
+            b.set_mode("binned", chunk)
+            y = b(xd).cpu().numpy()
+            assert ulp(ref, y, want) == 0, (label, chunk)
+    b.free()
