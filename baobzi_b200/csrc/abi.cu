@@ -97,7 +97,10 @@ int64_t default_chunk(const DeviceTree &dt) {
     int64_t c = (int64_t)dt.view.n_leaves * 2048;
     // 2D: the evaluation is bound by the 16-byte point gather, so the chunk's points must stay in L2 (4 Mi points =
     // 64 MB); 3D is FP64 bound and gathers out of DRAM without loss, so padding waste decides
-    const int64_t lo = int64_t(1) << 21, hi = dt.view.dim == 2 ? int64_t(1) << 22 : int64_t(1) << 24;
+    // (3D trees with few leaves: measured on the order-12 benchmark tree, 2 Mi -> 8 Mi points per chunk takes the sort
+    // from 22.6 to 11.8 ms per 1e9 points and the evaluation from 0.69 to 0.73 of the FP64 peak)
+    const int64_t lo = dt.view.dim == 2 ? int64_t(1) << 21 : int64_t(1) << 23;
+    const int64_t hi = dt.view.dim == 2 ? int64_t(1) << 22 : int64_t(1) << 24;
     return c < lo ? lo : (c > hi ? hi : c);
 }
 
@@ -177,8 +180,10 @@ bool use_binned(const Function *f, const DeviceTree &dt, int64_t n) {
     // there are enough points per leaf to fill warp tiles
     const int64_t block_bytes = 8 * (int64_t)std::pow((double)dt.view.order, dt.view.dim);
     if (dt.view.dim == 2) // every lane gathering its own block is bound by the L1 tag rate at any block size
-        return n >= 64 * (int64_t)dt.view.n_leaves && n >= (1 << 20);
-    return block_bytes >= 1024 && n >= 64 * (int64_t)dt.view.n_leaves && n >= (1 << 16);
+        return n >= 64 * (int64_t)dt.view.n_leaves && n >= (1 << 19); // measured crossover (C1 tree): 0.25-1 M points
+    // 3D, measured crossover: 16 points per leaf (4096-leaf order-8 tree: 65 Ki points, 0.071 ms against 0.080 ms direct;
+    // 2x ahead at 128 Ki), and from 16 Ki points on trees with few leaves (order 12: 0.038 against 0.069 ms)
+    return block_bytes >= 1024 && n >= 16 * (int64_t)dt.view.n_leaves && n >= (1 << 14);
 }
 
 // Bucketed path: when the tree (nodes + coefficients) is too big for L2 the direct kernel's gathers go to DRAM,

@@ -730,11 +730,8 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         rc_sort = (int)cudaLaunchCooperativeKernel(tv.dim == 2 ? (void *)bin_sort_fused_kernel<2, false> : (void *)bin_sort_fused_kernel<3, false>,
                                                    dim3(grid), dim3(ws.sort_threads), args,
                                                    ws.sort_smem, st);
-        if (pf) { // the three classic stages are one launch here: all of it is booked under "lookup"
+        if (pf) // the three classic stages are one launch here: all of it is booked under "sort"
             cudaEventRecord(ev[1], st);
-            cudaEventRecord(ev[2], st);
-            cudaEventRecord(ev[3], st);
-        }
     } else {
         bin_lookup_kernel<3><<<g1, kBinThreads, 0, st>>>(tv, d_x, d_res, ws.key, ws.count, ws.cshift, n);
         if (pf)
@@ -752,9 +749,15 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
     if (pf) {
         cudaEventRecord(ev[4], st);
         pf->spans.push_back({kStageLookup, ev[0], ev[1], (int64_t)n});
-        pf->spans.push_back({kStageScan, ev[1], ev[2], (int64_t)n});
-        pf->spans.push_back({kStageScatter, ev[2], ev[3], (int64_t)n});
-        pf->spans.push_back({kStageEval, ev[3], ev[4], (int64_t)n});
+        if (ws.fused) {
+            pf->spans.push_back({kStageEval, ev[1], ev[4], (int64_t)n});
+            pf->pool.push_back(ev[2]);
+            pf->pool.push_back(ev[3]);
+        } else {
+            pf->spans.push_back({kStageScan, ev[1], ev[2], (int64_t)n});
+            pf->spans.push_back({kStageScatter, ev[2], ev[3], (int64_t)n});
+            pf->spans.push_back({kStageEval, ev[3], ev[4], (int64_t)n});
+        }
     }
     return rc_sort ? rc_sort : rc ? rc : (int)cudaGetLastError();
 }
