@@ -592,6 +592,11 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         e = cudaMemset(ws.count, 0, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)
         e = cudaMemset(ws.cursor, 0, sizeof(uint32_t) * cwords);
+    // cudaMemset of device memory is asynchronous on the legacy default stream, and the kernels that read these
+    // counters run on the caller's stream, which may be non-blocking (the host-pointer pipeline's are): without this
+    // wait a first sort could histogram into uninitialised counters when the default stream had a backlog
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(nullptr);
     ws.overlap = ws.fused && ws.sort_overlap_ok;
     if (e == cudaSuccess && ws.overlap) {
         e = cudaMalloc((void **)&ws.alt_key, sizeof(uint32_t) * chunk);
@@ -886,6 +891,11 @@ int alloc_bucket_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws
         e = cudaMemset(ws.count, 0, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)
         e = cudaMemset(ws.cursor, 0, sizeof(uint32_t) * cwords);
+    // cudaMemset of device memory is asynchronous on the legacy default stream, and the kernels that read these
+    // counters run on the caller's stream, which may be non-blocking (the host-pointer pipeline's are): without this
+    // wait a first sort could histogram into uninitialised counters when the default stream had a backlog
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(nullptr);
     if (e != cudaSuccess) {
         free_workspace(ws);
         return (int)e;

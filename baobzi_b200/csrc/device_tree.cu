@@ -123,6 +123,10 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
         e = cudaMemcpy(base + off_leaf, leaf_node.data(), leaf_node.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
     if (e == cudaSuccess && !coeffs->empty())
         e = cudaMemcpy(base + off_coef, coeffs->data(), coeffs->size() * sizeof(double), cudaMemcpyHostToDevice);
+    // the copies above go through the legacy default stream (a pageable-source cudaMemcpy may return before its DMA
+    // has landed); the kernels that read the tree run on arbitrary, possibly non-blocking streams
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(nullptr);
     if (e != cudaSuccess) {
         cudaFree(blob);
         return (int)e;

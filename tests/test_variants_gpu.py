@@ -182,3 +182,39 @@ def test_clustered_and_ordered_inputs(gpu_lib, ref, name):
             y = b(xd).cpu().numpy()
             assert ulp(ref, y, want) == 0, (label, chunk)
     b.free()
+
+
+def test_unsynchronised_call_sequences(gpu_lib, ref):
+    """Back-to-back calls without any synchronisation in between, alternating the device-pointer entries (caller's
+    stream) and the host-pointer entry (the library's own non-blocking streams), across handles and modes: every
+    workspace must be initialised before the first kernel that reads it, whichever stream that kernel runs on.
+    (A cudaMemset on the default stream once raced with the first sort of a host-pointer call.)"""
+    import torch
+    from conftest import load_golden
+    rng = np.random.default_rng(41)
+    junk = [torch.full((1 << 22,), 0x7fffffff, dtype=torch.int32, device="cuda") for _ in range(8)]
+    del junk                                   # recycled allocations are not zero
+    for name in ("t2d_o8", "t3d_o8", "osc_2d"):
+        path, g = load_golden(name)
+        t = ref.OracleTree(path)
+        a = t.arrays()
+        n = 60_001
+        x = a["lower_left"] + rng.random((n, len(a["lower_left"]))) * (a["upper_right"] - a["lower_left"])
+        want = t.eval_multi(x, ref.ARITH_AVX2)
+        xd = torch.from_numpy(x).cuda()
+        xh = np.ascontiguousarray(x[:5000])
+        for mode in ("binned", "bucketed"):
+            b = gpu_lib.Baobzi(filename=path, mode=mode)
+            outs = []
+            for chunk in (0, 20_011):
+                b.set_mode(mode, chunk)
+                outs.append(b(xd))
+                b.dot(xd)
+            idx = b.node_index(xd)
+            yh = b(xh)                          # host pointers: other streams, own workspaces
+            outs.append(b(xd))
+            torch.cuda.synchronize()
+            for y in outs:
+                assert y.cpu().numpy().tobytes() == want.tobytes(), (name, mode)
+            assert np.asarray(yh).tobytes() == want[:5000].tobytes(), (name, mode)
+            b.free()
