@@ -46,6 +46,11 @@ struct Replica {
     // baobzi_eval_multi_device_dot: per-CTA partial sums, and the chunk of values of the binned / bucketed paths
     double *dot_partial = nullptr, *dot_tmp = nullptr;
     int64_t dot_partial_cap = 0, dot_tmp_cap = 0;
+    // shard_ws and the dot buffers are ONE set per device: calls that come in on different streams are chained through
+    // this event (wait before the first launch, record after the last), so they never use the workspace concurrently
+    cudaEvent_t ws_done = nullptr;
+    cudaStream_t ws_last_stream = nullptr;
+    bool ws_used = false;
 };
 
 enum Mode { kAuto = 0, kDirect = 1, kBinned = 2, kBucketed = 3 };
@@ -131,6 +136,21 @@ Replica *get_replica(Function *f, int dev) {
     }
     f->replicas.push_back(std::move(r));
     return f->replicas.back().get();
+}
+
+// caller holds f->mu
+void workspace_begin(Replica *r, cudaStream_t stream) {
+    if (r->ws_used && r->ws_last_stream != stream && r->ws_done)
+        cudaStreamWaitEvent(stream, r->ws_done, 0);
+}
+
+void workspace_end(Replica *r, cudaStream_t stream) {
+    if (!r->ws_done)
+        cudaEventCreateWithFlags(&r->ws_done, cudaEventDisableTiming);
+    if (r->ws_done)
+        cudaEventRecord(r->ws_done, stream);
+    r->ws_last_stream = stream;
+    r->ws_used = true;
 }
 
 ExecContext *acquire(Function *f, Replica *r) {
@@ -421,6 +441,8 @@ void fn_free(void *obj) {
         if (r->shard_stream)
             cudaStreamDestroy(r->shard_stream);
         free_workspace(r->shard_ws);
+        if (r->ws_done)
+            cudaEventDestroy(r->ws_done);
         if (r->dot_partial)
             cudaFree(r->dot_partial);
         if (r->dot_tmp)
@@ -544,7 +566,10 @@ int baobzi_eval_multi_device(const baobzi_t func, const double *d_x, double *d_r
     // the binned workspace of the per-device shard slot is reused; calls on one handle+device are
     // serialised on the caller's stream by construction (one workspace), so guard it
     std::lock_guard<std::mutex> lock(f->mu);
-    return bz::eval_device(f, r, r->shard_ws, d_x, d_res, ntrg, (cudaStream_t)cuda_stream);
+    bz::workspace_begin(r, (cudaStream_t)cuda_stream);
+    const int rc = bz::eval_device(f, r, r->shard_ws, d_x, d_res, ntrg, (cudaStream_t)cuda_stream);
+    bz::workspace_end(r, (cudaStream_t)cuda_stream);
+    return rc;
 }
 
 int baobzi_eval_multi_device_all(const baobzi_t func, const double *d_x, double *d_res, int64_t ntrg, void *cuda_stream) {
@@ -600,6 +625,7 @@ int baobzi_eval_multi_device_dot(const baobzi_t func, const double *d_x, const d
     const int G = bz::dot_grid(r->dt);
     int64_t launches = 0;
     int rc = 0;
+    bz::workspace_begin(r, stream);
     const bool binned = bz::use_binned(f, r->dt, ntrg), bucketed = !binned && bz::use_bucketed(f, r->dt, ntrg);
     if (!binned && !bucketed) { // fused: the values never leave registers
         rc = reserve_doubles(r->dot_partial, r->dot_partial_cap, G, stream);
@@ -625,6 +651,7 @@ int baobzi_eval_multi_device_dot(const baobzi_t func, const double *d_x, const d
         if (rc == 0)
             rc = bz::launch_sum_partials(r->dot_partial, n_chunks * G, d_out, stream, &launches);
     }
+    bz::workspace_end(r, stream);
     f->launches += launches;
     return rc;
 }
@@ -697,8 +724,12 @@ int baobzi_eval_multi_sharded(const baobzi_t func, int n_dev, const int *devices
         bz::DeviceGuard g(devices[k]);
         if (!r->shard_stream)
             rc = (int)cudaStreamCreateWithFlags(&r->shard_stream, cudaStreamNonBlocking);
-        if (rc == 0 && ntrg[k] > 0)
+        if (rc == 0 && ntrg[k] > 0) {
+            std::lock_guard<std::mutex> lock(f->mu);
+            bz::workspace_begin(r, r->shard_stream);
             rc = bz::eval_device(f, r, r->shard_ws, d_x[k], d_res[k], ntrg[k], r->shard_stream);
+            bz::workspace_end(r, r->shard_stream);
+        }
     }
     return rc;
 }

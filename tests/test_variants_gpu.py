@@ -218,3 +218,30 @@ def test_unsynchronised_call_sequences(gpu_lib, ref):
                 assert y.cpu().numpy().tobytes() == want.tobytes(), (name, mode)
             assert np.asarray(yh).tobytes() == want[:5000].tobytes(), (name, mode)
             b.free()
+
+
+def test_two_caller_streams_share_one_workspace(gpu_lib, ref):
+    """Calls on one handle from two CUDA streams, no synchronisation between them: the per-device workspace is chained
+    through an event, so the second call's sort never overwrites what the first call's evaluation still reads."""
+    import torch
+    from conftest import load_golden
+    path, g = load_golden("t3d_o8")
+    t = ref.OracleTree(path)
+    a = t.arrays()
+    rng = np.random.default_rng(43)
+    n = 400_000
+    xs = [a["lower_left"] + rng.random((n, 3)) * (a["upper_right"] - a["lower_left"]) for _ in range(2)]
+    wants = [t.eval_multi(x, ref.ARITH_AVX2) for x in xs]
+    xd = [torch.from_numpy(x).cuda() for x in xs]
+    b = gpu_lib.Baobzi(filename=path, mode="binned")
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    torch.cuda.synchronize()
+    outs = []
+    for rep in range(6):
+        k = rep % 2
+        with torch.cuda.stream(streams[k]):
+            outs.append((k, b(xd[k])))
+    torch.cuda.synchronize()
+    for k, y in outs:
+        assert y.cpu().numpy().tobytes() == wants[k].tobytes()
+    b.free()
