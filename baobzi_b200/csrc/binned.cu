@@ -346,54 +346,58 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
 // ------------------------------------------------------------------------------------------ K2
 // Single CTA: exclusive scan of the per-leaf counts rounded up to the warp-tile size.  count[] in: histogram;
 // out: zero (ready for the next chunk's K1).  cursor[] out: zero (for K3).  cnt[] out: dense copy for K2b.
+constexpr int kScanItems = 8; // sub-blocks of 1024 leaves per pass: their counters are all requested before the first scan
 __global__ void __launch_bounds__(1024)
 bin_scan_kernel(uint32_t TILE, uint32_t n_leaves, uint32_t *__restrict__ count, uint32_t *__restrict__ cursor, int cshift,
                 uint32_t *__restrict__ cnt_out, uint32_t *__restrict__ start, uint32_t *__restrict__ n_tiles) {
-    __shared__ uint32_t warp_sums[32];
-    __shared__ uint32_t carry_s;
-    if (threadIdx.x == 0)
-        carry_s = 0;
-    __syncthreads();
+    __shared__ uint32_t warp_sums[2][32];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (uint32_t base = 0; base < n_leaves; base += blockDim.x) {
-        const uint32_t l = base + threadIdx.x;
-        const uint32_t cnt = l < n_leaves ? count[(size_t)l << cshift] : 0u;
-        const uint32_t padded = (cnt + TILE - 1) / TILE * TILE;
-        uint32_t v = padded; // inclusive scan of `padded` across the CTA
+    uint32_t carry = 0; // every thread tracks it: no shared carry, two barriers per 1024 leaves
+    int buf = 0;
+    for (uint32_t base = 0; base < n_leaves; base += blockDim.x * kScanItems) {
+        uint32_t cnt[kScanItems];
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
-            if (lane >= o)
-                v += t;
+        for (int e = 0; e < kScanItems; ++e) { // coalesced, kScanItems loads in flight
+            const uint32_t l = base + e * blockDim.x + threadIdx.x;
+            cnt[e] = l < n_leaves ? count[(size_t)l << cshift] : 0u;
         }
-        if (lane == 31)
-            warp_sums[warp] = v;
-        __syncthreads();
-        if (warp == 0) {
-            uint32_t w = warp_sums[lane];
+#pragma unroll
+        for (int e = 0; e < kScanItems; ++e) {
+            const uint32_t l = base + e * blockDim.x + threadIdx.x;
+            if (base + e * blockDim.x >= n_leaves) // CTA uniform
+                break;
+            const uint32_t padded = (cnt[e] + TILE - 1) / TILE * TILE;
+            uint32_t v = padded;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+                if (lane >= o)
+                    v += t;
+            }
+            if (lane == 31)
+                warp_sums[buf][warp] = v;
+            __syncthreads();
+            uint32_t w = warp_sums[buf][lane]; // every warp scans the 32 warp totals itself
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
                 if (lane >= o)
                     w += t;
             }
-            warp_sums[lane] = w;
+            const uint32_t before = __shfl_sync(0xffffffffu, w, warp ? warp - 1 : 0);
+            const uint32_t total = __shfl_sync(0xffffffffu, w, 31);
+            if (l < n_leaves) {
+                start[l] = carry + (warp ? before : 0u) + v - padded;
+                cnt_out[l] = cnt[e];
+                count[(size_t)l << cshift] = 0;
+                cursor[(size_t)l << cshift] = 0;
+            }
+            carry += total;
+            buf ^= 1; // the other buffer: no second barrier needed before the next sub-block writes
         }
-        __syncthreads();
-        const uint32_t carry = carry_s;
-        if (l < n_leaves) {
-            start[l] = carry + (warp ? warp_sums[warp - 1] : 0u) + v - padded;
-            cnt_out[l] = cnt;
-            count[(size_t)l << cshift] = 0;
-            cursor[(size_t)l << cshift] = 0;
-        }
-        __syncthreads();
-        if (threadIdx.x == blockDim.x - 1)
-            carry_s = carry + warp_sums[31];
-        __syncthreads();
     }
     if (threadIdx.x == 0)
-        *n_tiles = carry_s / TILE;
+        *n_tiles = carry / TILE;
 }
 
 // K2b: one warp per leaf marks the padding slots of perm[] invalid and records the leaf of each of its tiles.

@@ -444,12 +444,15 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--order", type=int, default=0, help="experiments: the workload's function at another order")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     cfg = WORKLOADS[args.workload]
+    if args.order and args.order != cfg["order"]:
+        cfg = dict(cfg, order=args.order, desc=cfg["desc"] + " [order overridden: %d]" % args.order)
     if args.impl == "reference":
         run_reference_arm(args, cfg, rank, world)
     else:
