@@ -72,6 +72,7 @@ bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__res
 // HBM traffic: the points once (8*DIM B) + perm (4 B); key[] (4 B written, 4 B read) lives in L2.
 constexpr int kSortThreads = 512;
 constexpr size_t kFusedSortMaxSmem = 160 * 1024;
+constexpr int kSortBatch = 6; // histogram counters (loads / atomics) in flight per thread in the scan phases
 constexpr int kSortPts = 4; // independent lookups in flight per thread (the lookup is latency bound, not issue bound)
 
 // BYBIN (the bucketed path of large 1D / 2D trees): the key is the grid cell number >> bshift instead of the leaf,
@@ -173,11 +174,27 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         }
     }
     __syncthreads();
-    for (uint32_t l = tid; l < nl; l += nthr) {
-        const uint32_t h = tbl[l];
-        if (coalesce)
-            cnt[l] = h;
-        tbl[l] = h ? atomicAdd(count + ((size_t)l << cshift), h) : 0u;
+    // kSortBatch atomics in flight per thread: one at a time (a round trip to L2 each, nl / nthr of them per thread)
+    // was 18 % of the kernel on a launch-sized 2D chunk
+    for (uint32_t lb = tid; lb < nl; lb += kSortBatch * nthr) {
+        uint32_t h[kSortBatch], r[kSortBatch];
+#pragma unroll
+        for (int j = 0; j < kSortBatch; ++j) {
+            const uint32_t l = lb + j * nthr;
+            h[j] = l < nl ? tbl[l] : 0u;
+        }
+#pragma unroll
+        for (int j = 0; j < kSortBatch; ++j)
+            r[j] = h[j] ? atomicAdd(count + ((size_t)(lb + j * nthr) << cshift), h[j]) : 0u;
+#pragma unroll
+        for (int j = 0; j < kSortBatch; ++j) {
+            const uint32_t l = lb + j * nthr;
+            if (l < nl) {
+                if (coalesce)
+                    cnt[l] = h[j];
+                tbl[l] = r[j];
+            }
+        }
     }
     __threadfence();
     cooperative_groups::this_grid().sync();
@@ -186,9 +203,14 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     const uint32_t per = (nl + nthr - 1) / nthr;
     const uint32_t l0 = min(tid * per, nl), l1 = min(l0 + per, nl);
     uint32_t mine = 0;
-    for (uint32_t l = l0; l < l1; ++l) {
-        const uint32_t c = __ldcg(count + ((size_t)l << cshift));
-        mine += (c + TILE - 1) / TILE * TILE;
+    for (uint32_t lb = l0; lb < l1; lb += kSortBatch) { // kSortBatch counters requested together, not one by one
+        uint32_t c[kSortBatch];
+#pragma unroll
+        for (int j = 0; j < kSortBatch; ++j)
+            c[j] = lb + j < l1 ? __ldcg(count + ((size_t)(lb + j) << cshift)) : 0u;
+#pragma unroll
+        for (int j = 0; j < kSortBatch; ++j)
+            mine += (c[j] + TILE - 1) / TILE * TILE;
     }
     const uint32_t lane = tid & 31, warp = tid >> 5;
     uint32_t incl = mine;
@@ -220,8 +242,17 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     const uint32_t big_tiles = max(256u, warp_sums[nthr / 32 - 1] / TILE / kBigLeafCap);
     const uint32_t start0 = start;
     bool any_big = false;
-    for (uint32_t l = l0; l < l1; ++l) {
-        const uint32_t c = __ldcg(count + ((size_t)l << cshift));
+    for (uint32_t lb = l0; lb < l1; lb += kSortBatch) {
+      uint32_t cb[kSortBatch];
+#pragma unroll
+      for (int j = 0; j < kSortBatch; ++j)
+          cb[j] = lb + j < l1 ? __ldcg(count + ((size_t)(lb + j) << cshift)) : 0u;
+#pragma unroll
+      for (int j = 0; j < kSortBatch; ++j) {
+        const uint32_t l = lb + j;
+        if (l >= l1)
+            break;
+        const uint32_t c = cb[j];
         const uint32_t padded = (c + TILE - 1) / TILE * TILE;
         const bool is_big = !BYBIN && padded / TILE > big_tiles;
         any_big = any_big || is_big;
@@ -244,6 +275,7 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
             key_start[l] = start; // first slot of every bucket, for the evaluation kernel
         tbl[l] += start;
         start += padded;
+      }
     }
     if (any_big) { // rare: list this thread's big leaves (kept out of the loop above: an atomic there serialises its loads)
         uint32_t s2 = start0;
