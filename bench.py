@@ -445,6 +445,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
     ap.add_argument("--order", type=int, default=0, help="experiments: the workload's function at another order")
+    ap.add_argument("--tol", type=float, default=0.0, help="experiments: another fit tolerance")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -453,6 +454,8 @@ def main():
     cfg = WORKLOADS[args.workload]
     if args.order and args.order != cfg["order"]:
         cfg = dict(cfg, order=args.order, desc=cfg["desc"] + " [order overridden: %d]" % args.order)
+    if args.tol and args.tol != cfg["tol"]:
+        cfg = dict(cfg, tol=args.tol, desc=cfg["desc"] + " [tol overridden: %g]" % args.tol)
     if args.impl == "reference":
         run_reference_arm(args, cfg, rank, world)
     else:
