@@ -64,6 +64,7 @@ ABI = {
     "baobzi_profile_begin": (C.c_int, [baobzi_t]),
     "baobzi_profile_end": (C.c_int, [baobzi_t, c_double_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "baobzi_b200_fp64_peak": (C.c_int, [c_double_p]),
+    "baobzi_b200_fp64_peak_sustained": (C.c_int, [c_double_p, C.c_double]),
     "baobzi_b200_version": (C.c_char_p, []),
 }
 DATA_SYMBOLS = ["baobzi_input_default"]

@@ -777,5 +777,6 @@ int baobzi_profile_end(baobzi_t func, double *ms, int64_t *launches, int64_t *po
 }
 
 int baobzi_b200_fp64_peak(double *tflops) { return bz::measure_fp64_peak(tflops, 5); }
+int baobzi_b200_fp64_peak_sustained(double *tflops, double seconds) { return bz::measure_fp64_peak_sustained(tflops, seconds); }
 
 } // extern "C"

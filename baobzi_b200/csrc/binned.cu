@@ -73,6 +73,7 @@ bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__res
 constexpr int kSortThreads = 512;
 constexpr size_t kFusedSortMaxSmem = 160 * 1024;
 constexpr int kSortBatch = 6; // histogram counters (loads / atomics) in flight per thread in the scan phases
+constexpr int kSortSplitDefault = 1; // split sort (phase A of the next chunk beside the scatter of this one): CTAs per SM and kernel, 0 = off
 constexpr int kSortPts = 4; // independent lookups in flight per thread (the lookup is latency bound, not issue bound)
 
 // BYBIN (the bucketed path of large 1D / 2D trees): the key is the grid cell number >> bshift instead of the leaf,
@@ -102,13 +103,20 @@ __device__ __forceinline__ bool keys_repeat(uint32_t k, uint32_t lane) {
     return __popc(__ballot_sync(0xffffffffu, nb == k && k != kNotLeaf)) >= 16;
 }
 
-template <int DIM, bool BYBIN>
+template <int DIM, bool BYBIN, int PHASE = 0>
 __global__ void __launch_bounds__(kSortThreads)
 bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
                       uint32_t *__restrict__ key, uint32_t *__restrict__ count, uint32_t *__restrict__ count_next,
                       int cshift, uint32_t TILE, uint32_t *__restrict__ perm, uint32_t *__restrict__ tile_leaf,
                       uint2 *__restrict__ tile_info, uint32_t *__restrict__ n_tiles, uint32_t n, uint32_t skey_cap,
-                      uint32_t n_keys, int bshift, uint32_t *__restrict__ key_start, uint32_t coal_cap) {
+                      uint32_t n_keys, int bshift, uint32_t *__restrict__ key_start, uint32_t coal_cap,
+                      uint32_t sbin_n, uint32_t /*phase: the template argument*/, uint32_t *__restrict__ base_tbl) {
+    constexpr uint32_t phase = PHASE;
+    // phase 0: everything in one cooperative launch (grid barrier between A and B).  Split mode: phase 1 = A alone
+    // (keys through key[], the CTA's reserved bases saved in base_tbl[CTA][leaf]), phase 2 = B + scatter alone (ordinary
+    // launches of the same grid).  A streams points from HBM, the scatter is bound by the rate at which the chip takes
+    // scattered 4-byte stores: launched on two streams, A of chunk c+1 runs beside the scatter of chunk c.
+    constexpr bool do_a = phase != 2;
     extern __shared__ uint32_t tbl[]; // [n_keys] histogram -> base -> next free slot
     __shared__ uint32_t warp_sums[32];
     __shared__ uint4 big[kBigLeafCap];
@@ -119,6 +127,10 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     // keys of the CTA's own range as 16-bit leaf ranks in shared memory when they fit (skey_cap entries follow
     // tbl[]): the scatter then never goes back to global memory for them
     uint16_t *skey = reinterpret_cast<uint16_t *>(tbl + nl);
+    // sbin_n > 0: the bin_leaf table as 16-bit ranks in shared memory behind the keys.  The gather of phase A then costs
+    // a few bank-conflict wavefronts per warp instead of one L1 wavefront per distinct 128-byte line (~28 of them for 32
+    // random grid cells), and the LSU wavefront rate is what bounds that phase.
+    uint16_t *sbin = skey + skey_cap;
     // coal_cap > 0: the scatter goes through a CTA-local counting sort in shared memory (cnt[], loc[], sorted[] follow
     // tbl[]), and the CTA's run of every leaf leaves as ONE merged store per 8 slots instead of one 4-byte store per
     // point (the scattered 4-byte stores were 40 % of this kernel: L2 takes them one partial sector at a time)
@@ -126,16 +138,21 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     uint16_t *sorted = reinterpret_cast<uint16_t *>(loc + nl + 1);
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     for (uint32_t l = tid; l < nl; l += nthr)
-        tbl[l] = 0;
+        tbl[l] = do_a ? 0u : base_tbl[(size_t)blockIdx.x * nl + l];
+    for (uint32_t l = tid; l < sbin_n; l += nthr)
+        sbin[l] = (uint16_t)__ldg(tv.bin_leaf + l); // kNotLeaf -> 0xFFFF (n_leaves < 0xFFFF when sbin_n > 0)
     __syncthreads();
-    const uint32_t lo = (uint32_t)(((uint64_t)blockIdx.x * n) / gridDim.x);
-    const uint32_t hi = (uint32_t)(((uint64_t)(blockIdx.x + 1) * n) / gridDim.x);
+    // split mode: keys travel through key[] as 16-bit ranks and come back as 128-bit loads, so ranges start at multiples of 8
+    const uint32_t lo_raw = (uint32_t)(((uint64_t)blockIdx.x * n) / gridDim.x);
+    const uint32_t hi_raw = (uint32_t)(((uint64_t)(blockIdx.x + 1) * n) / gridDim.x);
+    const uint32_t lo = PHASE ? lo_raw & ~7u : lo_raw;
+    const uint32_t hi = PHASE && blockIdx.x + 1 != gridDim.x ? hi_raw & ~7u : hi_raw;
     const bool use_skey = hi - lo <= skey_cap; // CTA uniform
     const bool coalesce = coal_cap > 0 && hi - lo <= coal_cap;
 
     // ---- phase A
     const uint32_t lane_id = tid & 31;
-    for (uint32_t b0 = lo; b0 < hi; b0 += kSortPts * nthr) { // CTA-uniform trip count: the warps stay converged
+    for (uint32_t b0 = lo; do_a && b0 < hi; b0 += kSortPts * nthr) { // CTA-uniform trip count: the warps stay converged
         const uint32_t i0 = b0 + tid;
         double p[kSortPts][DIM];
         bool have[kSortPts];
@@ -149,7 +166,14 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u) { // all table lookups in flight before any (rare) descent
             lin[u] = linear_bin<DIM>(tv, p[u]);
-            leaf[u] = BYBIN ? lin[u] >> bshift : __ldg(tv.bin_leaf + lin[u]);
+            if (BYBIN) {
+                leaf[u] = lin[u] >> bshift;
+            } else if (sbin_n) {
+                const uint32_t v = sbin[lin[u]];
+                leaf[u] = v == 0xFFFFu ? kNotLeaf : v;
+            } else {
+                leaf[u] = __ldg(tv.bin_leaf + lin[u]);
+            }
         }
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u) {
@@ -163,7 +187,9 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         for (int u = 0; u < kSortPts; ++u) {
             const uint32_t i = i0 + u * nthr;
             if (have[u]) {
-                if (use_skey && !coalesce)
+                if (PHASE == 1)
+                    reinterpret_cast<uint16_t *>(key)[i] = (uint16_t)leaf[u]; // n_leaves < 0xFFFF in split mode
+                else if (use_skey && !coalesce)
                     skey[i - lo] = (uint16_t)leaf[u]; // kNotLeaf -> 0xFFFF (n_leaves < 0xFFFF when skey_cap > 0)
                 else
                     key[i] = leaf[u];
@@ -176,7 +202,7 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     __syncthreads();
     // kSortBatch atomics in flight per thread: one at a time (a round trip to L2 each, nl / nthr of them per thread)
     // was 18 % of the kernel on a launch-sized 2D chunk
-    for (uint32_t lb = tid; lb < nl; lb += kSortBatch * nthr) {
+    for (uint32_t lb = tid; do_a && lb < nl; lb += kSortBatch * nthr) {
         uint32_t h[kSortBatch], r[kSortBatch];
 #pragma unroll
         for (int j = 0; j < kSortBatch; ++j) {
@@ -193,11 +219,17 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
                 if (coalesce)
                     cnt[l] = h[j];
                 tbl[l] = r[j];
+                if (phase == 1)
+                    base_tbl[(size_t)blockIdx.x * nl + l] = r[j];
             }
         }
     }
-    __threadfence();
-    cooperative_groups::this_grid().sync();
+    if (phase == 1)
+        return;
+    if (phase == 0) {
+        __threadfence();
+        cooperative_groups::this_grid().sync();
+    }
 
     // ---- phase B: padded exclusive scan of the global histogram, thread t owns leaves [t*per, (t+1)*per)
     const uint32_t per = (nl + nthr - 1) / nthr;
@@ -352,6 +384,58 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         }
         return;
     }
+    if constexpr (PHASE == 2) {
+        // Keys come from global memory (written by phase A's launch, mostly evicted from L2 by the points it streamed
+        // afterwards): eight 16-bit keys per 128-bit load, requested two iterations ahead.  With one 4-byte key per
+        // load and no lookahead this loop sat on the load (ncu: half of the kernel's stall samples on its first use).
+        const uint16_t *k16 = reinterpret_cast<const uint16_t *>(key);
+        constexpr uint32_t KPT = 8;
+        const uint32_t per_it = KPT * nthr;
+        auto ld = [&](uint32_t b) -> uint4 {
+            const uint32_t i = b + KPT * tid;
+            return b < hi && i < hi ? __ldcs(reinterpret_cast<const uint4 *>(k16 + i)) : make_uint4(~0u, ~0u, ~0u, ~0u);
+        };
+        uint4 q0 = ld(lo), q1 = ld(lo + per_it);
+        for (uint32_t b0 = lo; b0 < hi; b0 += per_it) {
+            const uint4 q = q0;
+            q0 = q1;
+            q1 = ld(b0 + 2 * per_it);
+            const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+            const uint32_t i0 = b0 + KPT * tid;
+            uint32_t k[KPT];
+#pragma unroll
+            for (int j = 0; j < (int)KPT; ++j) {
+                const uint32_t v = (w[j / 2] >> (16 * (j & 1))) & 0xFFFFu;
+                k[j] = v == 0xFFFFu || i0 + j >= hi ? kNotLeaf : v;
+            }
+            if (!keys_repeat(k[0], lane)) { // the usual case, kept free of branches: eight atomics in flight, then eight stores
+                uint32_t slot[KPT];
+#pragma unroll
+                for (int j = 0; j < (int)KPT; ++j)
+                    slot[j] = k[j] != kNotLeaf ? atomicAdd(tbl + k[j], 1u) : 0u;
+#pragma unroll
+                for (int j = 0; j < (int)KPT; ++j)
+                    if (k[j] != kNotLeaf)
+                        perm[slot[j]] = i0 + j;
+            } else {
+#pragma unroll
+                for (int j = 0; j < (int)KPT; ++j) {
+                    const uint32_t slot = grouped_add(tbl, k[j], true, lane);
+                    if (k[j] != kNotLeaf)
+                        perm[slot] = i0 + j;
+                }
+            }
+        }
+        return;
+    }
+    uint32_t kn[kSortPts]; // keys that come from global memory are requested one iteration ahead
+    if (!use_skey) {
+#pragma unroll
+        for (int u = 0; u < kSortPts; ++u) {
+            const uint32_t i = lo + tid + u * nthr;
+            kn[u] = i < hi ? __ldcs(key + i) : kNotLeaf;
+        }
+    }
     for (uint32_t b0 = lo; b0 < hi; b0 += kSortPts * nthr) {
         const uint32_t i0 = b0 + tid;
         uint32_t k[kSortPts];
@@ -362,15 +446,32 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
                 const uint32_t v = i < hi ? skey[i - lo] : 0xFFFFu;
                 k[u] = v == 0xFFFFu ? kNotLeaf : v;
             } else {
-                k[u] = i < hi ? __ldcs(key + i) : kNotLeaf;
+                k[u] = kn[u];
             }
         }
-        const bool heavy = keys_repeat(k[0], lane);
+        if (!use_skey) {
 #pragma unroll
-        for (int u = 0; u < kSortPts; ++u) {
-            const uint32_t slot = grouped_add(tbl, k[u], heavy, lane);
-            if (k[u] != kNotLeaf)
-                perm[slot] = i0 + u * nthr;
+            for (int u = 0; u < kSortPts; ++u) {
+                const uint32_t i = i0 + kSortPts * nthr + u * nthr;
+                kn[u] = i < hi ? __ldcs(key + i) : kNotLeaf;
+            }
+        }
+        if (!keys_repeat(k[0], lane)) { // the usual case, kept free of branches: all atomics in flight, then the stores
+            uint32_t slot[kSortPts];
+#pragma unroll
+            for (int u = 0; u < kSortPts; ++u)
+                slot[u] = k[u] != kNotLeaf ? atomicAdd(tbl + k[u], 1u) : 0u;
+#pragma unroll
+            for (int u = 0; u < kSortPts; ++u)
+                if (k[u] != kNotLeaf)
+                    perm[slot[u]] = i0 + u * nthr;
+        } else {
+#pragma unroll
+            for (int u = 0; u < kSortPts; ++u) {
+                const uint32_t slot = grouped_add(tbl, k[u], true, lane);
+                if (k[u] != kNotLeaf)
+                    perm[slot] = i0 + u * nthr;
+            }
         }
     }
 }
@@ -514,6 +615,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
                 want = std::atoi(e);
         // preferred: `want` CTAs per SM, each keeping the 16-bit keys of its range in shared memory
         ws.sort_skey = 0;
+        ws.sort_sbin = 0;
         ws.sort_smem = hist;
         int per_sm = 0;
         if (nl < 0xFFFFu && !(std::getenv("BAOBZI_B200_SORT_SKEY") && std::atoi(std::getenv("BAOBZI_B200_SORT_SKEY")) == 0)) {
@@ -527,6 +629,17 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
                     per_sm = want;
                     ws.sort_skey = (uint32_t)cap;
                     ws.sort_smem = smem;
+                }
+            }
+            // ... and the bin_leaf table as 16-bit ranks behind them, when `want` CTAs still fit
+            const size_t smem_b = smem + ((size_t)dt.view.n_bins * sizeof(uint16_t) + 15) / 16 * 16;
+            const char *sb = std::getenv("BAOBZI_B200_SORT_SBIN");
+            if (ws.sort_skey && smem_b <= kFusedSortMaxSmem && !(sb && std::atoi(sb) == 0)) {
+                int occ = 0;
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, sort_fn, kSortThreads, smem_b);
+                if (occ >= want) {
+                    ws.sort_sbin = dt.view.n_bins;
+                    ws.sort_smem = smem_b;
                 }
             }
         }
@@ -551,6 +664,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
                 per_sm = want;
                 ws.sort_coal = (uint32_t)cap;
                 ws.sort_skey = 0;
+                ws.sort_sbin = 0;
                 ws.sort_smem = smem;
             }
         }
@@ -594,6 +708,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
                 ws.sort_threads = warps * 32;
                 ws.sort_ctas = dt.sm_count;
                 ws.sort_skey = 0;
+                ws.sort_sbin = 0;
                 ws.sort_coal = 0;
                 ws.sort_smem = hist;
             }
@@ -634,6 +749,54 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     if (e == cudaSuccess)
         e = cudaStreamSynchronize(nullptr);
     ws.overlap = ws.fused && ws.sort_overlap_ok;
+    // Split sort: opt-in / opt-out through BAOBZI_B200_SORT_SPLIT (value = CTAs per SM and kernel, 0 = off)
+    ws.split = false;
+    if (e == cudaSuccess && ws.fused && !ws.overlap) {
+        int per = kSortSplitDefault;
+        if (const char *sp = std::getenv("BAOBZI_B200_SORT_SPLIT"))
+            per = std::atoi(sp);
+        if (per > 0 && nl < 0xFFFF) { // 16-bit keys between the two launches
+            const size_t hist = (size_t)nl * sizeof(uint32_t);
+            const size_t tblb = ((size_t)dt.view.n_bins * sizeof(uint16_t) + 15) / 16 * 16;
+            ws.split_sbin = nl < 0xFFFFu && hist + tblb <= kFusedSortMaxSmem ? dt.view.n_bins : 0u;
+            ws.split_smem_a = hist + (ws.split_sbin ? tblb : 0);
+            ws.split_smem_b = hist;
+            ws.split_ctas = dt.sm_count * per;
+            ws.split = true;
+            cudaFuncAttributes fa;
+            if (cudaFuncGetAttributes(&fa, sort_fn) == cudaSuccess) {
+                const double need = (double)per * (double)(ws.split_smem_a + ws.split_smem_b + 2 * fa.sharedSizeBytes + 2048);
+                int pct = (int)(100.0 * need / (228.0 * 1024.0)) + 1;
+                pct = pct > 100 ? 100 : pct;
+                if (const char *ce = std::getenv("BAOBZI_B200_SORT_CARVEOUT"))
+                    pct = std::atoi(ce);
+                if (pct >= 0) {
+                    const void *fa1 = is2d ? (const void *)bin_sort_fused_kernel<2, false, 1> : (const void *)bin_sort_fused_kernel<3, false, 1>;
+                    const void *fa2 = is2d ? (const void *)bin_sort_fused_kernel<2, false, 2> : (const void *)bin_sort_fused_kernel<3, false, 2>;
+                    cudaFuncSetAttribute(fa1, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+                    cudaFuncSetAttribute(fa2, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+                }
+            }
+            e = cudaMalloc((void **)&ws.count3, sizeof(uint32_t) * cwords);
+            if (e == cudaSuccess)
+                e = cudaMemset(ws.count3, 0, sizeof(uint32_t) * cwords);
+            if (e == cudaSuccess)
+                e = cudaMalloc((void **)&ws.alt_key, sizeof(uint32_t) * chunk);
+            for (int h = 0; h < 2 && e == cudaSuccess; ++h)
+                e = cudaMalloc((void **)&ws.base_tbl[h], sizeof(uint32_t) * (size_t)ws.split_ctas * nl);
+            if (e == cudaSuccess)
+                e = cudaStreamCreateWithFlags(&ws.sort_stream, cudaStreamNonBlocking);
+            if (e == cudaSuccess)
+                e = cudaEventCreateWithFlags(&ws.ev_begin, cudaEventDisableTiming);
+            for (int h = 0; h < 2 && e == cudaSuccess; ++h) {
+                e = cudaEventCreateWithFlags(&ws.ev_sorted[h], cudaEventDisableTiming);
+                if (e == cudaSuccess)
+                    e = cudaEventCreateWithFlags(&ws.ev_evaluated[h], cudaEventDisableTiming);
+            }
+            if (e == cudaSuccess)
+                e = cudaStreamSynchronize(nullptr);
+        }
+    }
     if (e == cudaSuccess && ws.overlap) {
         e = cudaMalloc((void **)&ws.alt_key, sizeof(uint32_t) * chunk);
         if (e == cudaSuccess)
@@ -672,6 +835,9 @@ void free_workspace(BinWorkspace &ws) {
     cudaFree(ws.tile_leaf);
     cudaFree(ws.n_tiles);
     cudaFree(ws.tile_info);
+    cudaFree(ws.count3);
+    cudaFree(ws.base_tbl[0]);
+    cudaFree(ws.base_tbl[1]);
     cudaFree(ws.alt_key);
     cudaFree(ws.alt_perm);
     cudaFree(ws.alt_tile_leaf);
@@ -723,10 +889,11 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         ws.flip = !ws.flip;
         TreeView tvv = tv;
         int cshift = ws.cshift;
-        uint32_t tile = TILE, nn = n, skey = 0, nkeys = tv.n_leaves, coal = 0;
+        uint32_t tile = TILE, nn = n, skey = 0, nkeys = tv.n_leaves, coal = 0, sbin = 0, phase0 = 0;
+        uint32_t *no_base = nullptr;
         int bshift = 0;
         void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
-                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start, &coal};
+                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start, &coal, &sbin, &phase0, &no_base};
         rc_sort = (int)cudaLaunchCooperativeKernel(tv.dim == 2 ? (void *)bin_sort_fused_kernel<2, false> : (void *)bin_sort_fused_kernel<3, false>,
                                                    dim3(grid), dim3(ws.sort_threads), args,
                                                    ws.sort_smem, ss);
@@ -762,12 +929,19 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
         grid = grid < useful ? grid : (useful ? useful : 1u);
         uint32_t *cur = ws.flip ? ws.cursor : ws.count, *next = ws.flip ? ws.count : ws.cursor;
         ws.flip = !ws.flip;
+        if (ws.count3) { // the split sort's three rotating histogram buffers (calls of both kinds may alternate)
+            uint32_t *hist[3] = {ws.count, ws.cursor, ws.count3};
+            cur = hist[ws.rot % 3];
+            next = hist[(ws.rot + 2) % 3];
+            ws.rot = (ws.rot + 1) % 3;
+        }
         TreeView tvv = tv;
         int cshift = ws.cshift;
-        uint32_t tile = TILE, nn = n, skey = ws.sort_skey, nkeys = tv.n_leaves, coal = ws.sort_coal;
+        uint32_t tile = TILE, nn = n, skey = ws.sort_skey, nkeys = tv.n_leaves, coal = ws.sort_coal, sbin = ws.sort_sbin, phase0 = 0;
+        uint32_t *no_base = nullptr;
         int bshift = 0;
         void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
-                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start, &coal};
+                        &ws.tile_leaf, &ws.tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start, &coal, &sbin, &phase0, &no_base};
         rc_sort = (int)cudaLaunchCooperativeKernel(tv.dim == 2 ? (void *)bin_sort_fused_kernel<2, false> : (void *)bin_sort_fused_kernel<3, false>,
                                                    dim3(grid), dim3(ws.sort_threads), args,
                                                    ws.sort_smem, st);
@@ -803,12 +977,101 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
     return rc_sort ? rc_sort : rc ? rc : (int)cudaGetLastError();
 }
 
+// One phase of the split sort for one chunk (ordinary launch: the kernel never reaches its grid barrier).
+static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t phase, const double *d_x, double *d_res,
+                             uint32_t n, uint32_t *key, uint32_t *cur, uint32_t *next, uint32_t *base, cudaStream_t st) {
+    const TreeView &tv = dt.view;
+    uint32_t grid = (uint32_t)ws.split_ctas;
+    const uint32_t per_cta = (uint32_t)kSortThreads * kSortPts;
+    const uint32_t useful = (n + per_cta - 1) / per_cta;
+    grid = grid < useful ? grid : (useful ? useful : 1u); // a function of n alone: the same for both phases of a chunk
+    const uint32_t TILE = 32u * (uint32_t)ws.P;
+    const size_t smem = phase == 1 ? ws.split_smem_a : ws.split_smem_b;
+    const uint32_t sbin = phase == 1 ? ws.split_sbin : 0u;
+#define BZ_SORT_PHASE(D, PH)                                                                                          \
+    bin_sort_fused_kernel<D, false, PH><<<grid, kSortThreads, smem, st>>>(                                            \
+        tv, d_x, d_res, key, cur, next, ws.cshift, TILE, ws.perm, ws.tile_leaf, ws.tile_info, ws.n_tiles, n, 0u,      \
+        tv.n_leaves, 0, ws.start, 0u, sbin, phase, base)
+    if (tv.dim == 2) {
+        if (phase == 1)
+            BZ_SORT_PHASE(2, 1);
+        else
+            BZ_SORT_PHASE(2, 2);
+    } else {
+        if (phase == 1)
+            BZ_SORT_PHASE(3, 1);
+        else
+            BZ_SORT_PHASE(3, 2);
+    }
+#undef BZ_SORT_PHASE
+    return (int)cudaGetLastError();
+}
+
+static int launch_eval_split(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
+                             cudaStream_t stream, int64_t *launches) {
+    const int dim = dt.view.dim;
+    const int64_t step = ws.chunk_limit > 0 && ws.chunk_limit < ws.chunk_capacity ? ws.chunk_limit : ws.chunk_capacity;
+    const int64_t nc = (n + step - 1) / step;
+    uint32_t *hist[3] = {ws.count, ws.cursor, ws.count3};
+    uint32_t *keys[2] = {ws.key, ws.alt_key};
+    cudaStream_t ss = ws.sort_stream;
+    StageProfile *pf = ws.prof;
+    auto chunk_n = [&](int64_t c) { return (uint32_t)(n - c * step < step ? n - c * step : step); };
+    cudaEventRecord(ws.ev_begin, stream); // fork: the side stream starts once everything queued before this call is done
+    cudaStreamWaitEvent(ss, ws.ev_begin, 0);
+    int rc = launch_sort_phase(dt, ws, 1, d_x, d_res, chunk_n(0), keys[0], hist[ws.rot % 3], nullptr, ws.base_tbl[0], ss);
+    cudaEventRecord(ws.ev_sorted[0], ss);
+    for (int64_t c = 0; c < nc && rc == 0; ++c) {
+        const int h = (int)(c & 1);
+        const uint32_t m = chunk_n(c);
+        cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+        cudaStreamWaitEvent(stream, ws.ev_sorted[h], 0);
+        if (pf) {
+            for (auto &e : ev)
+                e = pf->get();
+            cudaEventRecord(ev[0], stream);
+        }
+        rc = launch_sort_phase(dt, ws, 2, d_x + dim * c * step, d_res + c * step, m, keys[h], hist[(ws.rot + c) % 3],
+                               hist[(ws.rot + c + 2) % 3], ws.base_tbl[h], stream);
+        if (pf)
+            cudaEventRecord(ev[1], stream);
+        if (c + 1 < nc && rc == 0) { // phase A of the next chunk: beside the scatter above, but after evaluation c-1
+            if (c >= 1)
+                cudaStreamWaitEvent(ss, ws.ev_evaluated[h ^ 1], 0);
+            rc = launch_sort_phase(dt, ws, 1, d_x + dim * (c + 1) * step, d_res + (c + 1) * step, chunk_n(c + 1), keys[h ^ 1],
+                                   hist[(ws.rot + c + 1) % 3], nullptr, ws.base_tbl[h ^ 1], ss);
+            cudaEventRecord(ws.ev_sorted[h ^ 1], ss);
+            // The evaluation below does NOT wait for this launch: its CTAs take the SMs as phase A's CTAs leave them.
+            // Measured (C3, 2e8 points): 12.49 ms against 12.79 ms with a wait, at the price of a per-launch evaluation
+            // time (bench.py's roofline) that includes phase A's tail: 411 us against 400 us per 8.4 M points.
+        }
+        if (rc == 0)
+            rc = dim == 2 ? launch_bin_eval2d(dt, ws, d_x + dim * c * step, d_res + c * step, stream)
+                          : launch_bin_eval3d(dt, ws, d_x + dim * c * step, d_res + c * step, stream);
+        cudaEventRecord(ws.ev_evaluated[h], stream);
+        if (pf) {
+            cudaEventRecord(ev[2], stream);
+            pf->spans.push_back({kStageLookup, ev[0], ev[1], (int64_t)m});
+            pf->spans.push_back({kStageEval, ev[1], ev[2], (int64_t)m});
+        }
+        if (launches)
+            *launches += 3;
+    }
+    ws.rot = (int)((ws.rot + nc) % 3);
+    return rc ? rc : (int)cudaGetLastError();
+}
+
 int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
                        cudaStream_t stream, int64_t *launches) {
     if (n <= 0)
         return 0;
     if ((dt.view.dim != 3 && dt.view.dim != 2) || ws.bucketed || ws.chunk_capacity <= 0)
         return (int)cudaErrorInvalidValue;
+    {   // the split sort pays when there is a next chunk to overlap with; a single chunk takes the one-launch sort
+        const int64_t step = ws.chunk_limit > 0 && ws.chunk_limit < ws.chunk_capacity ? ws.chunk_limit : ws.chunk_capacity;
+        if (ws.split && n > step)
+            return launch_eval_split(dt, ws, d_x, d_res, n, stream, launches);
+    }
     if (ws.overlap) { // fork: the side stream may start once everything queued before this call is done
         cudaEventRecord(ws.ev_begin, stream);
         cudaStreamWaitEvent(ws.sort_stream, ws.ev_begin, 0);
@@ -836,11 +1099,12 @@ static int launch_bucket_sort(const DeviceTree &dt, BinWorkspace &ws, const doub
     ws.flip = !ws.flip;
     TreeView tvv = dt.view;
     int cshift = ws.cshift, bshift = ws.bshift;
-    uint32_t tile = 1, nn = n, skey = ws.sort_skey, nkeys = ws.n_keys, coal = ws.sort_coal;
+    uint32_t tile = 1, nn = n, skey = ws.sort_skey, nkeys = ws.n_keys, coal = ws.sort_coal, sbin = 0, phase0 = 0;
+    uint32_t *no_base = nullptr;
     uint32_t *no_tile_leaf = nullptr;
     uint2 *no_tile_info = nullptr;
     void *args[] = {&tvv, (void *)&d_x, (void *)&d_res, &ws.key, &cur, &next, &cshift, &tile, &ws.perm,
-                    &no_tile_leaf, &no_tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start, &coal};
+                    &no_tile_leaf, &no_tile_info, &ws.n_tiles, &nn, &skey, &nkeys, &bshift, &ws.start, &coal, &sbin, &phase0, &no_base};
     return (int)cudaLaunchCooperativeKernel((void *)bin_sort_fused_kernel<DIM, true>, dim3(grid), dim3(ws.sort_threads),
                                             args, ws.sort_smem, st);
 }

@@ -91,6 +91,7 @@ struct BinWorkspace {
                                 // are then the two histogram buffers used by alternate chunks
     bool flip = false;          // which of the two the next chunk histograms into
     int sort_ctas = 0;          // grid of the cooperative kernel (all CTAs co-resident)
+    uint32_t sort_sbin = 0;     // entries of the 16-bit bin_leaf table staged in the sort's shared memory (0: gathered via L1)
     uint32_t sort_coal = 0;     // per-CTA capacity of the shared-memory local sort (0: direct 4-byte scatter)
     uint32_t sort_skey = 0;     // per-CTA capacity of the shared-memory key array (0: keys go through key[])
     size_t sort_smem = 0;       // dynamic shared memory of the cooperative kernel
@@ -114,6 +115,15 @@ struct BinWorkspace {
     cudaEvent_t ev_begin = nullptr, ev_sorted[2] = {nullptr, nullptr}, ev_evaluated[2] = {nullptr, nullptr};
     bool evaluated_valid[2] = {false, false};
     int half = 0;
+    // Split sort (binned.cu: launch_eval_split): phase A of chunk c+1 on sort_stream beside phase B + scatter of chunk c.
+    // key / alt_key and base_tbl[2] alternate between chunks; three histogram buffers rotate (A of chunk c fills
+    // hist3[(rot+c)%3], B of chunk c reads it and clears hist3[(rot+c+2)%3], which chunk c+2 fills next).
+    bool split = false;
+    int split_ctas = 0;
+    uint32_t split_sbin = 0;
+    size_t split_smem_a = 0, split_smem_b = 0;
+    uint32_t *count3 = nullptr, *base_tbl[2] = {nullptr, nullptr};
+    int rot = 0;
     uint32_t *alt_key = nullptr, *alt_perm = nullptr, *alt_tile_leaf = nullptr, *alt_n_tiles = nullptr;
     uint2 *alt_tile_info = nullptr;
 };
@@ -148,6 +158,7 @@ int launch_eval_all_1d(const DeviceTree &dt, const double *d_x, double *d_res, i
                        int64_t *launches);
 // Dependent-DFMA microbenchmark on the current device: sustained FP64 FMA rate in TFLOP/s (2 flops per FMA).
 int measure_fp64_peak(double *tflops, int repeats);
+int measure_fp64_peak_sustained(double *tflops, double seconds);
 // Scalar twin: x[dim] -> y[out_dim] (reference Function::eval(x, res), template.hpp:851-860).
 int launch_eval_scalar(const DeviceTree &dt, const double *d_x, double *d_y, cudaStream_t stream, int64_t *launches);
 // Binned path over n points in chunks of ws.chunk_capacity: sort by leaf (lookup+histogram, padded scan, scatter), evaluation.

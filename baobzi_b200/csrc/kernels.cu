@@ -448,4 +448,44 @@ int measure_fp64_peak(double *tflops, int repeats) {
     return (int)e;
 }
 
+// The same kernel back to back for `seconds`: the rate of the last windows, i.e. at the clocks the board settles to
+// under its power cap.  A kernel timed inside a long FP64-bound step runs at those clocks, not at the burst clock.
+int measure_fp64_peak_sustained(double *tflops, double seconds) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    double *d = nullptr;
+    cudaError_t e = cudaMalloc((void **)&d, 8);
+    if (e != cudaSuccess)
+        return (int)e;
+    cudaEvent_t b, f;
+    cudaEventCreate(&b);
+    cudaEventCreate(&f);
+    const int iters = 8192, grid = sms * 8, threads = 256, per_window = 40;
+    const double flops = 2.0 * 16.0 * iters * (double)grid * threads * per_window;
+    double elapsed = 0.0, last[3] = {0.0, 0.0, 0.0};
+    int windows = 0;
+    if (seconds > 30.0)
+        seconds = 30.0;
+    while (elapsed < seconds || windows < 3) {
+        cudaEventRecord(b);
+        for (int r = 0; r < per_window; ++r)
+            dfma_peak_kernel<<<grid, threads>>>(d, 0.999999, 1e-9, iters);
+        cudaEventRecord(f);
+        e = cudaEventSynchronize(f);
+        if (e != cudaSuccess)
+            break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, b, f);
+        elapsed += ms * 1e-3;
+        last[windows % 3] = flops / (ms * 1e-3) / 1e12;
+        ++windows;
+    }
+    cudaEventDestroy(b);
+    cudaEventDestroy(f);
+    cudaFree(d);
+    *tflops = windows >= 3 ? (last[0] + last[1] + last[2]) / 3.0 : 0.0;
+    return (int)e;
+}
+
 } // namespace bz

@@ -175,6 +175,9 @@ int baobzi_profile_end(baobzi_t func, double *ms, int64_t *launches, int64_t *po
 /* Dependent-FMA microbenchmark on the current device: FP64 rate in TFLOP/s (roofline denominator of the
  * FP64-bound kernels).  Returns 0 or a cudaError_t value. */
 int baobzi_b200_fp64_peak(double *tflops);
+/* The same kernel run back to back for `seconds` (<= 30): the rate of the last windows, i.e. at the clocks the board
+ * settles to under its power cap -- the denominator for a kernel timed inside a long FP64-bound step. */
+int baobzi_b200_fp64_peak_sustained(double *tflops, double seconds);
 
 /* Library identification string, e.g. "baobzi-b200 0.1 (sm_100a)". */
 const char *baobzi_b200_version(void);

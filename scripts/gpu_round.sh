@@ -7,5 +7,5 @@ CMD="python bench.py --points 33554432 --steps 1 --warmup 3 --no-cpu --no-e2e --
 $CMD > gpurun_out/plain.log 2>&1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu1.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:bin_eval3d -s 6 -c 1 -f -o gpurun_out/prof_k4 $CMD > gpurun_out/ncu2.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:bin_sort_fused -s 6 -c 1 -f -o gpurun_out/prof_sort $CMD > gpurun_out/ncu3.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:bin_sort_fused -s 6 -c 2 -f -o gpurun_out/prof_sort $CMD > gpurun_out/ncu3.log 2>&1
 tail -1 gpurun_out/ncu3.log

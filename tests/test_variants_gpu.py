@@ -1,6 +1,6 @@
 """Every opt-in kernel variant of the 3D path gives the bits of the default one (and of the oracle): the FP64
 tensor-core kernel (DMMA rounds like the FMA chain it replaces), the strided / run tile orders, the coalescing
-scatter, the two-stream sort/evaluate overlap, and the bucketed path on a tree with refined cells."""
+scatter, the two-stream sort/evaluate overlap, the split sort (default) against the single cooperative launch, and the bucketed path on a tree with refined cells."""
 import os
 
 import numpy as np
@@ -17,6 +17,9 @@ VARIANTS = [
     {"BAOBZI_B200_OVERLAP": "1"},            # sort of chunk c+1 beside the evaluation of chunk c
     {"BAOBZI_B200_FUSED_SORT": "0"},         # four-kernel sort (fallback for trees whose histogram exceeds smem)
     {"BAOBZI_B200_SORT_SKEY": "0"},          # keys through global memory
+    {"BAOBZI_B200_SORT_SPLIT": "0"},         # one cooperative sort launch per chunk (no phase A / scatter overlap)
+    {"BAOBZI_B200_SORT_SPLIT": "2"},         # split sort, two CTAs per SM and phase
+    {"BAOBZI_B200_SORT_SBIN": "0"},          # bin_leaf gathered through L1 instead of shared memory
 ]
 
 
