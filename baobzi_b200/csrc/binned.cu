@@ -73,7 +73,8 @@ bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__res
 constexpr int kSortThreads = 512;
 constexpr size_t kFusedSortMaxSmem = 160 * 1024;
 constexpr int kSortBatch = 6; // histogram counters (loads / atomics) in flight per thread in the scan phases
-constexpr int kSortSplitDefault = 1; // split sort (phase A of the next chunk beside the scatter of this one): CTAs per SM and kernel, 0 = off
+constexpr int kSortSplitDefault = 1;
+constexpr int64_t kSortSplitMinLeaves = 2048; // split sort (phase A of the next chunk beside the scatter of this one): CTAs per SM and kernel, 0 = off
 constexpr int kSortPts = 4; // independent lookups in flight per thread (the lookup is latency bound, not issue bound)
 
 // BYBIN (the bucketed path of large 1D / 2D trees): the key is the grid cell number >> bshift instead of the leaf,
@@ -752,7 +753,11 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     // Split sort: opt-in / opt-out through BAOBZI_B200_SORT_SPLIT (value = CTAs per SM and kernel, 0 = off)
     ws.split = false;
     if (e == cudaSuccess && ws.fused && !ws.overlap) {
-        int per = kSortSplitDefault;
+        // Default: trees from kSortSplitMinLeaves leaves up.  With few leaves the scatter's stores share sectors and the
+        // scan + scatter launch alone is quick (57 us per 8 Mi points at 512 leaves against 87 us at 4096): beside the
+        // lookup launch both then take ~140 us, more than one after the other (measured, 3D order 12: 6.41e9 evals/s
+        // with the single launch, 6.21e9 split; 4096 leaves at order 8: 1.53e10 -> 1.60e10).
+        int per = nl >= kSortSplitMinLeaves ? kSortSplitDefault : 0;
         if (const char *sp = std::getenv("BAOBZI_B200_SORT_SPLIT"))
             per = std::atoi(sp);
         if (per > 0 && nl < 0xFFFF) { // 16-bit keys between the two launches
@@ -765,7 +770,10 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             ws.split = true;
             cudaFuncAttributes fa;
             if (cudaFuncGetAttributes(&fa, sort_fn) == cudaSuccess) {
-                const double need = (double)per * (double)(ws.split_smem_a + ws.split_smem_b + 2 * fa.sharedSizeBytes + 2048);
+                // both phases' CTAs must be resident together; never below 32 KB (a carve-out sized for a tree with a
+                // few hundred leaves left no room for the second kernel's CTA: the phases ran one after the other)
+                double need = (double)per * (double)(ws.split_smem_a + ws.split_smem_b + 2 * fa.sharedSizeBytes + 2048);
+                need = need < 32.0 * 1024.0 ? 32.0 * 1024.0 : need;
                 int pct = (int)(100.0 * need / (228.0 * 1024.0)) + 1;
                 pct = pct > 100 ? 100 : pct;
                 if (const char *ce = std::getenv("BAOBZI_B200_SORT_CARVEOUT"))
