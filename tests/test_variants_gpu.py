@@ -18,6 +18,7 @@ VARIANTS = [
     {"BAOBZI_B200_FUSED_SORT": "0"},         # four-kernel sort (fallback for trees whose histogram exceeds smem)
     {"BAOBZI_B200_SORT_SKEY": "0"},          # keys through global memory
     {"BAOBZI_B200_SORT_SPLIT": "0"},         # one cooperative sort launch per chunk (no phase A / scatter overlap)
+    {"BAOBZI_B200_SORT_SPLIT": "1"},         # split sort forced (the default only from 2048 leaves; fixtures are smaller)
     {"BAOBZI_B200_SORT_SPLIT": "2"},         # split sort, two CTAs per SM and phase
     {"BAOBZI_B200_SORT_SBIN": "0"},          # bin_leaf gathered through L1 instead of shared memory
 ]
@@ -151,8 +152,20 @@ def test_table_1d_kernel_bits(gpu_lib, ref, name):
             os.environ["BAOBZI_B200_TABLE1D_MIN"] = old
 
 
-@pytest.mark.parametrize("name", ["t3d_o8", "t2d_o8"])
-def test_clustered_and_ordered_inputs(gpu_lib, ref, name):
+@pytest.fixture(params=["0", "1"], ids=["single_launch_sort", "split_sort"])
+def sort_split(request):
+    """Both sort schedules: the golden trees are below the split sort's default leaf threshold, so it is forced."""
+    old = os.environ.get("BAOBZI_B200_SORT_SPLIT")
+    os.environ["BAOBZI_B200_SORT_SPLIT"] = request.param   # read when a handle builds its workspace
+    yield request.param
+    if old is None:
+        os.environ.pop("BAOBZI_B200_SORT_SPLIT", None)
+    else:
+        os.environ["BAOBZI_B200_SORT_SPLIT"] = old
+
+
+@pytest.mark.parametrize("name", ["t3d_o8", "t2d_o8", "tc_2d"])
+def test_clustered_and_ordered_inputs(gpu_lib, ref, name, sort_split):
     """Inputs that are not uniform random: every point inside ONE leaf (its tile descriptors are then written by the
     whole grid and the histogram updates are aggregated per warp, binned.cu), two heavy leaves plus a sprinkle of
     others, and a lattice in C order -- same bits as the oracle in the binned path."""
@@ -187,7 +200,7 @@ def test_clustered_and_ordered_inputs(gpu_lib, ref, name):
     b.free()
 
 
-def test_unsynchronised_call_sequences(gpu_lib, ref):
+def test_unsynchronised_call_sequences(gpu_lib, ref, sort_split):
     """Back-to-back calls without any synchronisation in between, alternating the device-pointer entries (caller's
     stream) and the host-pointer entry (the library's own non-blocking streams), across handles and modes: every
     workspace must be initialised before the first kernel that reads it, whichever stream that kernel runs on.
@@ -223,7 +236,7 @@ def test_unsynchronised_call_sequences(gpu_lib, ref):
             b.free()
 
 
-def test_two_caller_streams_share_one_workspace(gpu_lib, ref):
+def test_two_caller_streams_share_one_workspace(gpu_lib, ref, sort_split):
     """Calls on one handle from two CUDA streams, no synchronisation between them: the per-device workspace is chained
     through an event, so the second call's sort never overwrites what the first call's evaluation still reads."""
     import torch
@@ -237,6 +250,8 @@ def test_two_caller_streams_share_one_workspace(gpu_lib, ref):
     wants = [t.eval_multi(x, ref.ARITH_AVX2) for x in xs]
     xd = [torch.from_numpy(x).cuda() for x in xs]
     b = gpu_lib.Baobzi(filename=path, mode="binned")
+    if sort_split == "1":
+        b.set_mode("binned", 100_003)          # several chunks per call: the side stream and both key buffers are in play
     streams = [torch.cuda.Stream(), torch.cuda.Stream()]
     torch.cuda.synchronize()
     outs = []
