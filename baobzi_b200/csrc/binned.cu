@@ -71,6 +71,7 @@ bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__res
 //            perm[tbl[leaf]++] = i with a shared-memory atomic: no rank array, no global atomics, no table gathers.
 // HBM traffic: the points once (8*DIM B) + perm (4 B); key[] (4 B written, 4 B read) lives in L2.
 constexpr int kSortThreads = 512;
+constexpr int kSortThreadsA = 768; // most threads the lookup launch of the split sort may be given
 constexpr size_t kFusedSortMaxSmem = 160 * 1024;
 constexpr int kSortBatch = 6; // histogram counters (loads / atomics) in flight per thread in the scan phases
 constexpr int kSortSplitDefault = 1;
@@ -105,7 +106,7 @@ __device__ __forceinline__ bool keys_repeat(uint32_t k, uint32_t lane) {
 }
 
 template <int DIM, bool BYBIN, int PHASE = 0>
-__global__ void __launch_bounds__(kSortThreads)
+__global__ void __launch_bounds__(PHASE == 1 ? kSortThreadsA : kSortThreads)
 bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
                       uint32_t *__restrict__ key, uint32_t *__restrict__ count, uint32_t *__restrict__ count_next,
                       int cshift, uint32_t TILE, uint32_t *__restrict__ perm, uint32_t *__restrict__ tile_leaf,
@@ -1002,7 +1003,15 @@ static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t ph
     const uint32_t TILE = 32u * (uint32_t)ws.P;
     const size_t smem = phase == 1 ? ws.split_smem_a : ws.split_smem_b;
     const uint32_t sbin = phase == 1 ? ws.split_sbin : 0u;
-    const int threads = kSortThreads; // phase B with 384 / 256 threads: 12.44 / 12.53 ms against 12.52 (C3, 2e8 points): noise
+    // Threads of the two launches (one CTA of each per SM).  In 2D the lookup (grid cell + descent) is the longer of the
+    // two, so it gets 768 threads and the scatter 256; in 3D 512 + 512.  Measured on B200, A+B threads -> ms per step:
+    // C1 tree, 1e8 points: 512+512 4.95, 640+384 4.76, 640+256 4.73, 768+256 4.59;
+    // C3 tree, 2e8 points: 512+512 12.48, 640+384 12.50, 640+256 12.65, 768+256 12.66.
+    static const int a_env = std::getenv("BAOBZI_B200_SPLIT_ATHREADS") ? std::atoi(std::getenv("BAOBZI_B200_SPLIT_ATHREADS")) : 0;
+    static const int b_env = std::getenv("BAOBZI_B200_SPLIT_BTHREADS") ? std::atoi(std::getenv("BAOBZI_B200_SPLIT_BTHREADS")) : 0;
+    const int a_threads = a_env >= 32 && a_env <= kSortThreadsA ? a_env / 32 * 32 : (tv.dim == 2 ? kSortThreadsA : kSortThreads);
+    const int b_threads = b_env >= 32 && b_env <= kSortThreads ? b_env / 32 * 32 : (tv.dim == 2 ? 256 : kSortThreads);
+    const int threads = phase == 2 ? b_threads : a_threads;
 #define BZ_SORT_PHASE(D, PH)                                                                                          \
     bin_sort_fused_kernel<D, false, PH><<<grid, threads, smem, st>>>(                                            \
         tv, d_x, d_res, key, cur, next, ws.cshift, TILE, ws.perm, ws.tile_leaf, ws.tile_info, ws.n_tiles, n, 0u,      \
