@@ -578,6 +578,29 @@ bool binned_fits(const DeviceTree &dt) {
 
 bool binned_supported(int dim, int order) { return (dim == 2 || dim == 3) && order >= 6 && order <= 16 && order % 2 == 0; }
 
+// third histogram buffer, second key buffer, the per-CTA base tables, side stream and events of the split sort
+static cudaError_t alloc_split_buffers(BinWorkspace &ws, size_t cwords, int64_t chunk, size_t n_keys) {
+    cudaError_t e = cudaMalloc((void **)&ws.count3, sizeof(uint32_t) * cwords);
+    if (e == cudaSuccess)
+        e = cudaMemset(ws.count3, 0, sizeof(uint32_t) * cwords);
+    if (e == cudaSuccess)
+        e = cudaMalloc((void **)&ws.alt_key, sizeof(uint32_t) * chunk);
+    for (int h = 0; h < 2 && e == cudaSuccess; ++h)
+        e = cudaMalloc((void **)&ws.base_tbl[h], sizeof(uint32_t) * (size_t)ws.split_ctas * n_keys);
+    if (e == cudaSuccess)
+        e = cudaStreamCreateWithFlags(&ws.sort_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess)
+        e = cudaEventCreateWithFlags(&ws.ev_begin, cudaEventDisableTiming);
+    for (int h = 0; h < 2 && e == cudaSuccess; ++h) {
+        e = cudaEventCreateWithFlags(&ws.ev_sorted[h], cudaEventDisableTiming);
+        if (e == cudaSuccess)
+            e = cudaEventCreateWithFlags(&ws.ev_evaluated[h], cudaEventDisableTiming);
+    }
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(nullptr);
+    return e;
+}
+
 int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     if (chunk < 1)
         chunk = 1;
@@ -786,24 +809,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
                     cudaFuncSetAttribute(fa2, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
                 }
             }
-            e = cudaMalloc((void **)&ws.count3, sizeof(uint32_t) * cwords);
-            if (e == cudaSuccess)
-                e = cudaMemset(ws.count3, 0, sizeof(uint32_t) * cwords);
-            if (e == cudaSuccess)
-                e = cudaMalloc((void **)&ws.alt_key, sizeof(uint32_t) * chunk);
-            for (int h = 0; h < 2 && e == cudaSuccess; ++h)
-                e = cudaMalloc((void **)&ws.base_tbl[h], sizeof(uint32_t) * (size_t)ws.split_ctas * nl);
-            if (e == cudaSuccess)
-                e = cudaStreamCreateWithFlags(&ws.sort_stream, cudaStreamNonBlocking);
-            if (e == cudaSuccess)
-                e = cudaEventCreateWithFlags(&ws.ev_begin, cudaEventDisableTiming);
-            for (int h = 0; h < 2 && e == cudaSuccess; ++h) {
-                e = cudaEventCreateWithFlags(&ws.ev_sorted[h], cudaEventDisableTiming);
-                if (e == cudaSuccess)
-                    e = cudaEventCreateWithFlags(&ws.ev_evaluated[h], cudaEventDisableTiming);
-            }
-            if (e == cudaSuccess)
-                e = cudaStreamSynchronize(nullptr);
+            e = alloc_split_buffers(ws, cwords, chunk, (size_t)nl);
         }
     }
     if (e == cudaSuccess && ws.overlap) {
@@ -1000,7 +1006,8 @@ static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t ph
     const uint32_t per_cta = (uint32_t)kSortThreads * kSortPts;
     const uint32_t useful = (n + per_cta - 1) / per_cta;
     grid = grid < useful ? grid : (useful ? useful : 1u); // a function of n alone: the same for both phases of a chunk
-    const uint32_t TILE = 32u * (uint32_t)ws.P;
+    const bool bybin = ws.bucketed; // bucketed path: key = grid cell >> bshift, no tile descriptors, no table
+    const uint32_t TILE = bybin ? 1u : 32u * (uint32_t)ws.P;
     const size_t smem = phase == 1 ? ws.split_smem_a : ws.split_smem_b;
     const uint32_t sbin = phase == 1 ? ws.split_sbin : 0u;
     // Threads of the two launches (one CTA of each per SM).  In 2D the lookup (grid cell + descent) is the longer of the
@@ -1009,24 +1016,38 @@ static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t ph
     // C3 tree, 2e8 points: 512+512 12.48, 640+384 12.50, 640+256 12.65, 768+256 12.66.
     static const int a_env = std::getenv("BAOBZI_B200_SPLIT_ATHREADS") ? std::atoi(std::getenv("BAOBZI_B200_SPLIT_ATHREADS")) : 0;
     static const int b_env = std::getenv("BAOBZI_B200_SPLIT_BTHREADS") ? std::atoi(std::getenv("BAOBZI_B200_SPLIT_BTHREADS")) : 0;
-    const int a_threads = a_env >= 32 && a_env <= kSortThreadsA ? a_env / 32 * 32 : (tv.dim == 2 ? kSortThreadsA : kSortThreads);
-    const int b_threads = b_env >= 32 && b_env <= kSortThreads ? b_env / 32 * 32 : (tv.dim == 2 ? 256 : kSortThreads);
+    const bool long_lookup = tv.dim == 2 && !bybin;
+    const int a_threads = a_env >= 32 && a_env <= kSortThreadsA ? a_env / 32 * 32 : (long_lookup ? kSortThreadsA : kSortThreads);
+    const int b_threads = b_env >= 32 && b_env <= kSortThreads ? b_env / 32 * 32 : (long_lookup ? 256 : kSortThreads);
     const int threads = phase == 2 ? b_threads : a_threads;
-#define BZ_SORT_PHASE(D, PH)                                                                                          \
-    bin_sort_fused_kernel<D, false, PH><<<grid, threads, smem, st>>>(                                            \
-        tv, d_x, d_res, key, cur, next, ws.cshift, TILE, ws.perm, ws.tile_leaf, ws.tile_info, ws.n_tiles, n, 0u,      \
-        tv.n_leaves, 0, ws.start, 0u, sbin, phase, base)
-    if (tv.dim == 2) {
-        if (phase == 1)
-            BZ_SORT_PHASE(2, 1);
+    uint32_t *tile_leaf = bybin ? nullptr : ws.tile_leaf;
+    uint2 *tile_info = bybin ? nullptr : ws.tile_info;
+    const uint32_t nkeys = bybin ? ws.n_keys : tv.n_leaves;
+    const int bshift = bybin ? ws.bshift : 0;
+#define BZ_SORT_PHASE(D, BB, PH)                                                                                     \
+    bin_sort_fused_kernel<D, BB, PH><<<grid, threads, smem, st>>>(tv, d_x, d_res, key, cur, next, ws.cshift, TILE,  \
+                                                                  ws.perm, tile_leaf, tile_info, ws.n_tiles, n, 0u,  \
+                                                                  nkeys, bshift, ws.start, 0u, sbin, phase, base)
+#define BZ_SORT_PHASES(D, BB)                                                                                        \
+    do {                                                                                                             \
+        if (phase == 1)                                                                                              \
+            BZ_SORT_PHASE(D, BB, 1);                                                                                 \
+        else                                                                                                         \
+            BZ_SORT_PHASE(D, BB, 2);                                                                                 \
+    } while (0)
+    if (bybin) {
+        if (tv.dim == 1)
+            BZ_SORT_PHASES(1, true);
+        else if (tv.dim == 2)
+            BZ_SORT_PHASES(2, true);
         else
-            BZ_SORT_PHASE(2, 2);
+            BZ_SORT_PHASES(3, true);
+    } else if (tv.dim == 2) {
+        BZ_SORT_PHASES(2, false);
     } else {
-        if (phase == 1)
-            BZ_SORT_PHASE(3, 1);
-        else
-            BZ_SORT_PHASE(3, 2);
+        BZ_SORT_PHASES(3, false);
     }
+#undef BZ_SORT_PHASES
 #undef BZ_SORT_PHASE
     return (int)cudaGetLastError();
 }
@@ -1069,9 +1090,13 @@ static int launch_eval_split(const DeviceTree &dt, BinWorkspace &ws, const doubl
             // Measured (C3, 2e8 points): 12.49 ms against 12.79 ms with a wait, at the price of a per-launch evaluation
             // time (bench.py's roofline) that includes phase A's tail: 411 us against 400 us per 8.4 M points.
         }
-        if (rc == 0)
-            rc = dim == 2 ? launch_bin_eval2d(dt, ws, d_x + dim * c * step, d_res + c * step, stream)
-                          : launch_bin_eval3d(dt, ws, d_x + dim * c * step, d_res + c * step, stream);
+        if (rc == 0) {
+            const double *xc = d_x + dim * c * step;
+            double *rcp = d_res + c * step;
+            rc = ws.bucketed ? launch_eval_buckets(dt, xc, rcp, ws.perm, ws.start, ws.n_tiles + 1, ws.n_keys, ws.bshift, stream)
+                 : dim == 2  ? launch_bin_eval2d(dt, ws, xc, rcp, stream)
+                             : launch_bin_eval3d(dt, ws, xc, rcp, stream);
+        }
         cudaEventRecord(ws.ev_evaluated[h], stream);
         if (pf) {
             cudaEventRecord(ev[2], stream);
@@ -1121,6 +1146,12 @@ static int launch_bucket_sort(const DeviceTree &dt, BinWorkspace &ws, const doub
     grid = grid < useful ? grid : (useful ? useful : 1u);
     uint32_t *cur = ws.flip ? ws.cursor : ws.count, *next = ws.flip ? ws.count : ws.cursor;
     ws.flip = !ws.flip;
+    if (ws.count3) { // the split sort's three rotating histogram buffers (calls of both kinds may alternate)
+        uint32_t *hist[3] = {ws.count, ws.cursor, ws.count3};
+        cur = hist[ws.rot % 3];
+        next = hist[(ws.rot + 2) % 3];
+        ws.rot = (ws.rot + 1) % 3;
+    }
     TreeView tvv = dt.view;
     int cshift = ws.cshift, bshift = ws.bshift;
     uint32_t tile = 1, nn = n, skey = ws.sort_skey, nkeys = ws.n_keys, coal = ws.sort_coal, sbin = 0, phase0 = 0;
@@ -1220,6 +1251,33 @@ int alloc_bucket_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws
     // wait a first sort could histogram into uninitialised counters when the default stream had a backlog
     if (e == cudaSuccess)
         e = cudaStreamSynchronize(nullptr);
+    // split sort for the bucket keys too (same leaf-count rule; BAOBZI_B200_SORT_SPLIT overrides)
+    ws.split = false;
+    if (e == cudaSuccess) {
+        int per = (int64_t)ws.n_keys >= kSortSplitMinLeaves ? kSortSplitDefault : 0;
+        if (const char *sp = std::getenv("BAOBZI_B200_SORT_SPLIT"))
+            per = std::atoi(sp);
+        if (per > 0 && ws.n_keys < 0xFFFF) {
+            const size_t hist = (size_t)ws.n_keys * sizeof(uint32_t);
+            ws.split_sbin = 0;
+            ws.split_smem_a = ws.split_smem_b = hist;
+            ws.split_ctas = dt.sm_count * per;
+            ws.split = hist <= 48 * 1024; // ordinary launches below the opt-in shared-memory size
+            if (ws.split) {
+                double need = (double)per * (double)(2 * hist + 2 * 2304 + 2048);
+                need = need < 32.0 * 1024.0 ? 32.0 * 1024.0 : need;
+                int pct = (int)(100.0 * need / (228.0 * 1024.0)) + 1;
+                pct = pct > 100 ? 100 : pct;
+                const void *fa[6] = {(const void *)bin_sort_fused_kernel<1, true, 1>, (const void *)bin_sort_fused_kernel<1, true, 2>,
+                                     (const void *)bin_sort_fused_kernel<2, true, 1>, (const void *)bin_sort_fused_kernel<2, true, 2>,
+                                     (const void *)bin_sort_fused_kernel<3, true, 1>, (const void *)bin_sort_fused_kernel<3, true, 2>};
+                const int d0 = (dt.view.dim - 1) * 2;
+                cudaFuncSetAttribute(fa[d0], cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+                cudaFuncSetAttribute(fa[d0 + 1], cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+                e = alloc_split_buffers(ws, cwords, chunk, (size_t)ws.n_keys);
+            }
+        }
+    }
     if (e != cudaSuccess) {
         free_workspace(ws);
         return (int)e;
@@ -1237,6 +1295,8 @@ int launch_eval_bucketed(const DeviceTree &dt, BinWorkspace &ws, const double *d
         return (int)cudaErrorInvalidValue;
     const int dim = dt.view.dim;
     const int64_t step = ws.chunk_limit > 0 && ws.chunk_limit < ws.chunk_capacity ? ws.chunk_limit : ws.chunk_capacity;
+    if (ws.split && n > step)
+        return launch_eval_split(dt, ws, d_x, d_res, n, stream, launches);
     StageProfile *pf = ws.prof;
     int rc = 0;
     for (int64_t o = 0; o < n && rc == 0; o += step) {
