@@ -16,6 +16,11 @@
 //   K3 bin_scatter  thread per point: perm[start[key] + cursor[key]++] = i
 //   K4 bin_eval     warp per tile (32*P consecutive slots of one leaf): gather the P points per lane,
 //                   evaluate with register-blocked, reference-ordered arithmetic, scatter the results
+// K1-K3 as written above are the fallback for trees whose histogram exceeds shared memory.  Otherwise they are ONE
+// kernel, bin_sort_fused_kernel, launched either once per chunk (cooperative, a grid barrier between lookup and
+// scan + scatter) or, for trees from kSortSplitMinLeaves leaves whenever a call spans several chunks, as two ordinary
+// launches per chunk on two streams: the lookup of chunk c+1 runs beside the scan + scatter of chunk c
+// (launch_eval_split; DESIGN.md 4.2 has the measurements behind every threshold).
 #include "device_tree.hpp"
 
 #include <cstdio>
