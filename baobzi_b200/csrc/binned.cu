@@ -18,7 +18,7 @@
 //                   evaluate with register-blocked, reference-ordered arithmetic, scatter the results
 // K1-K3 as written above are the fallback for trees whose histogram exceeds shared memory.  Otherwise they are ONE
 // kernel, bin_sort_fused_kernel, launched either once per chunk (cooperative, a grid barrier between lookup and
-// scan + scatter) or, for trees from kSortSplitMinLeaves leaves whenever a call spans several chunks, as two ordinary
+// scan + scatter) or, for trees from kSortSplitMinLeaves(2D) leaves whenever a call spans several chunks, as two ordinary
 // launches per chunk on two streams: the lookup of chunk c+1 runs beside the scan + scatter of chunk c
 // (launch_eval_split; DESIGN.md 4.2 has the measurements behind every threshold).
 #include "device_tree.hpp"
@@ -80,7 +80,8 @@ constexpr int kSortThreadsA = 768; // most threads the lookup launch of the spli
 constexpr size_t kFusedSortMaxSmem = 160 * 1024;
 constexpr int kSortBatch = 6; // histogram counters (loads / atomics) in flight per thread in the scan phases
 constexpr int kSortSplitDefault = 1;
-constexpr int64_t kSortSplitMinLeaves = 2048; // split sort (phase A of the next chunk beside the scatter of this one): CTAs per SM and kernel, 0 = off
+constexpr int64_t kSortSplitMinLeaves = 2048;
+constexpr int64_t kSortSplitMinLeaves2D = 128; // split sort (phase A of the next chunk beside the scatter of this one): CTAs per SM and kernel, 0 = off
 constexpr int kSortPts = 4; // independent lookups in flight per thread (the lookup is latency bound, not issue bound)
 
 // BYBIN (the bucketed path of large 1D / 2D trees): the key is the grid cell number >> bshift instead of the leaf,
@@ -786,7 +787,11 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         // scan + scatter launch alone is quick (57 us per 8 Mi points at 512 leaves against 87 us at 4096): beside the
         // lookup launch both then take ~140 us, more than one after the other (measured, 3D order 12: 6.41e9 evals/s
         // with the single launch, 6.21e9 split; 4096 leaves at order 8: 1.53e10 -> 1.60e10).
-        int per = nl >= kSortSplitMinLeaves ? kSortSplitDefault : 0;
+        // 2D: from kSortSplitMinLeaves2D leaves.  scripts/split_threshold.py (1e8 points, single launch -> split): 217 leaves
+        // 5.51 -> 4.75 ms, 256 leaves 3.98 -> 3.62, 1147 leaves 3.60 -> 3.18, 8860 leaves (C1) 5.15 -> 4.59; the 3D
+        // trees below the threshold gain nothing measurable (64 leaves 15.46 -> 15.36 ms, 512 leaves 10.24 -> 10.15).
+        const int64_t min_leaves = is2d ? kSortSplitMinLeaves2D : kSortSplitMinLeaves;
+        int per = nl >= min_leaves ? kSortSplitDefault : 0;
         if (const char *sp = std::getenv("BAOBZI_B200_SORT_SPLIT"))
             per = std::atoi(sp);
         if (per > 0 && nl < 0xFFFF) { // 16-bit keys between the two launches
