@@ -140,11 +140,22 @@ class Baobzi:
             if not (dim and order and center is not None and half_length is not None and tol):
                 raise ValueError("Baobzi: supply dim, order, center, half_length, and tol for init")
             inp = BaobziInput()
+            self._cb_error = None
             if callable(fin):
                 def trampoline(xp, yp, _data, _f=fin, _d=dim, _o=output_dim):
-                    y = np.atleast_1d(np.asarray(_f(np.ctypeslib.as_array(xp, (_d,))), dtype=np.float64))
-                    for k in range(_o):
-                        yp[k] = y[k]
+                    # ctypes swallows exceptions raised inside a callback: keep the first one, feed the fitter NaN
+                    # (never uninitialised memory) and re-raise once baobzi_init has returned
+                    try:
+                        if self._cb_error is not None:
+                            raise self._cb_error
+                        y = np.atleast_1d(np.asarray(_f(np.ctypeslib.as_array(xp, (_d,))), dtype=np.float64))
+                        for k in range(_o):
+                            yp[k] = y[k]
+                    except BaseException as exc:  # noqa: BLE001
+                        if self._cb_error is None:
+                            self._cb_error = exc
+                        for k in range(_o):
+                            yp[k] = float("nan")
                 self._cb = INPUT_FUNC(trampoline)
                 inp.func = C.cast(self._cb, C.c_void_p)
             else:
@@ -159,6 +170,12 @@ class Baobzi:
             c = np.ascontiguousarray(center, dtype=np.float64)
             h = np.ascontiguousarray(half_length, dtype=np.float64)
             self.ptr = lib.baobzi_init(C.byref(inp), c.ctypes.data_as(c_double_p), h.ctypes.data_as(c_double_p))
+            if self._cb_error is not None:
+                err, self._cb_error = self._cb_error, None
+                if self.ptr:
+                    lib.baobzi_free(self.ptr)
+                    self.ptr = None
+                raise err
         else:
             raise ValueError("Baobzi requires either a 'filename' argument or a 'fin' argument")
         if not self.ptr or not self.ptr[0].obj:
@@ -188,9 +205,16 @@ class Baobzi:
             ptr, count, _keep = dp
             n = count // self.dim
             if out is None:
+                if not hasattr(x, "is_cuda"):
+                    raise TypeError("pass out= (a CUDA float64 array of n values) with a non-torch CUDA input")
                 import torch
                 out = torch.empty(n, dtype=torch.float64, device=x.device)
-            optr = _device_pointer(out)[0]
+            op = _device_pointer(out)
+            if op is None or op[1] < n:
+                raise TypeError("out must be a contiguous CUDA float64 array with at least one value per point")
+            if hasattr(x, "is_cuda") and hasattr(out, "is_cuda") and out.device != x.device:
+                raise TypeError("out must live on the device that holds x")
+            optr = op[0]
             if stream is None and hasattr(x, "is_cuda"):
                 import torch
                 stream = torch.cuda.current_stream(x.device).cuda_stream
@@ -203,6 +227,9 @@ class Baobzi:
         if n > 2**31 - 1:
             raise ValueError("baobzi_eval_multi takes an int count; use the device entry for more points")
         res = out if out is not None else np.empty(n, dtype=np.float64)
+        if not (isinstance(res, np.ndarray) and res.dtype == np.float64 and res.flags.c_contiguous
+                and res.flags.writeable and res.size >= n):
+            raise TypeError("out must be a writeable C-contiguous float64 numpy array with at least one value per point")
         self._lib.baobzi_eval_multi(self.ptr, xarr.ctypes.data, res.ctypes.data, n)
         return res
 

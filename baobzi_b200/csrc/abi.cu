@@ -15,9 +15,11 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <exception>
 #include <memory>
 #include <mutex>
 #include <string>
+#include <utility>
 #include <vector>
 
 namespace bz {
@@ -59,10 +61,11 @@ struct Function {
     HostTree host;
     std::mutex mu;
     std::vector<std::unique_ptr<Replica>> replicas;
-    int mode = kAuto;
-    int64_t chunk = 0;
+    std::atomic<int> mode{kAuto};       // baobzi_set_mode may race with evaluations on other threads
+    std::atomic<int64_t> chunk{0};
     std::atomic<int64_t> launches{0};
-    std::unique_ptr<StageProfile> profile; // non-null while baobzi_profile_begin .. _end
+    std::mutex prof_mu;
+    std::shared_ptr<StageProfile> profile; // non-null while baobzi_profile_begin .. _end (one profiled caller at a time)
 };
 
 namespace {
@@ -189,12 +192,21 @@ void destroy_context(ExecContext &c) {
         cudaStreamDestroy(c.stream);
 }
 
+// The reference API asks nothing of `x` beyond being a double array, so a 2D point array may start on an odd
+// double (a view one element into a buffer).  The grouped 2D kernels gather a point as ONE 16-byte item
+// (cp.async 16 in bin_eval2d_kernel); such input takes the direct kernel, whose loads fall back to two 8-byte ones
+// (lookup.cuh load_point<2>).  1D / 3D kernels only ever issue 8-byte accesses to x.
+bool misaligned_2d(const DeviceTree &dt, const double *d_x) {
+    return dt.view.dim == 2 && (reinterpret_cast<uintptr_t>(d_x) & 15u) != 0;
+}
+
 bool use_binned(const Function *f, const DeviceTree &dt, int64_t n) {
     if (!binned_supported(dt.view.dim, dt.view.order) || !binned_fits(dt))
         return false;
-    if (f->mode == kDirect || f->mode == kBucketed)
+    const int mode = f->mode.load();
+    if (mode == kDirect || mode == kBucketed)
         return false;
-    if (f->mode == kBinned)
+    if (mode == kBinned)
         return true;
     // auto: worth it when the per-point coefficient gather (order^dim doubles) dwarfs the point itself and
     // there are enough points per leaf to fill warp tiles
@@ -210,9 +222,10 @@ bool use_binned(const Function *f, const DeviceTree &dt, int64_t n) {
 // one or more sectors per level and per coefficient line; grouping the chunk's points by grid-cell bucket first
 // turns them into cache hits.
 bool use_bucketed(const Function *f, const DeviceTree &dt, int64_t n) {
-    if (f->mode == kBucketed)
+    const int mode = f->mode.load();
+    if (mode == kBucketed)
         return true;
-    if (f->mode != kAuto)
+    if (mode != kAuto)
         return false;
     return dt.blob_bytes > (size_t(48) << 20) && n >= (1 << 20);
 }
@@ -231,13 +244,21 @@ int eval_device(Function *f, Replica *r, BinWorkspace &ws, const double *d_x, do
                 cudaStream_t stream) {
     int64_t launches = 0;
     int rc = 0;
-    StageProfile *prof = f->profile.get();
+    std::shared_ptr<StageProfile> prof_keep; // stays alive for this call even if baobzi_profile_end runs meanwhile
+    {
+        std::lock_guard<std::mutex> lock(f->prof_mu);
+        prof_keep = f->profile;
+    }
+    StageProfile *prof = prof_keep.get();
     ws.prof = prof;
-    if (use_binned(f, r->dt, n)) {
-        int64_t step = f->chunk > 0 ? f->chunk : default_chunk(r->dt);
+    const bool odd = misaligned_2d(r->dt, d_x);
+    if (!odd && use_binned(f, r->dt, n)) {
+        const int64_t fc = f->chunk.load();
+        int64_t step = fc > 0 ? fc : default_chunk(r->dt);
         if (step > n)
             step = n;
         if (ws.chunk_capacity < step || ws.bucketed) {
+            // (re)allocation: synchronous by nature (cudaMalloc / cudaFree), first call or growth only -- see baobzi.h
             cudaStreamSynchronize(stream);
             free_workspace(ws);
             rc = alloc_workspace(r->dt, step, ws);
@@ -246,8 +267,9 @@ int eval_device(Function *f, Replica *r, BinWorkspace &ws, const double *d_x, do
         ws.prof = prof; // (re)attach: a reallocation starts from a fresh workspace
         if (rc == 0)
             rc = launch_eval_binned(r->dt, ws, d_x, d_res, n, stream, &launches); // chunks of ws.chunk_capacity
-    } else if (use_bucketed(f, r->dt, n)) {
-        int64_t step = f->chunk > 0 ? f->chunk : default_bucket_chunk();
+    } else if (!odd && use_bucketed(f, r->dt, n)) {
+        const int64_t fc = f->chunk.load();
+        int64_t step = fc > 0 ? fc : default_bucket_chunk();
         if (step > n)
             step = n;
         if (ws.chunk_capacity < step || !ws.bucketed) {
@@ -288,8 +310,11 @@ void fn_eval(const void *obj, const double *x, double *y) {
     Function *f = (Function *)obj;
     int dev = 0;
     cudaGetDevice(&dev);
-    if (f->replicas.size() == 1)
-        dev = f->replicas[0]->dt.device; // scalar calls stick to the replica that exists
+    {
+        std::lock_guard<std::mutex> lock(f->mu); // get_replica on another thread may grow the vector
+        if (f->replicas.size() == 1)
+            dev = f->replicas[0]->dt.device; // scalar calls stick to the replica that exists
+    }
     Replica *r = get_replica(f, dev);
     const int od = f->host.output_dim < 1 ? 1 : (int)f->host.output_dim;
     ExecContext *c = r ? acquire(f, r) : nullptr;
@@ -456,7 +481,7 @@ baobzi_t make_handle(std::unique_ptr<Function> f) {
     int dev = 0;
     if (report(cudaGetDevice(&dev), "device query (is a CUDA device visible? there is no CPU evaluation path)"))
         return nullptr;
-    f->mode = env_mode();
+    f->mode.store(env_mode());
     if (!get_replica(f.get(), dev))
         return nullptr;
     baobzi_t res = (baobzi_t)std::malloc(sizeof(baobzi_struct));
@@ -494,7 +519,33 @@ void baobzi_eval_multi(const baobzi_t func, const double *x, double *res, int nt
 
 void baobzi_save(const baobzi_t func, const char *filename) { func->save(func->obj, filename); }
 
+// extern "C" entry points must not let a C++ exception (bad_alloc on a huge tree, ...) unwind into a C caller
+static baobzi_t restore_impl(const char *filename);
+static baobzi_t init_impl(const baobzi_input_t *input, const double *center, const double *half_length);
+
 baobzi_t baobzi_restore(const char *filename) {
+    try {
+        return restore_impl(filename);
+    } catch (const std::exception &e) {
+        std::fprintf(stderr, "Baobzi restore error: Unable to restore from '%s' (%s)\n", filename, e.what());
+    } catch (...) {
+        std::fprintf(stderr, "Baobzi restore error: Unable to restore from '%s'\n", filename);
+    }
+    return nullptr;
+}
+
+baobzi_t baobzi_init(const baobzi_input_t *input, const double *center, const double *half_length) {
+    try {
+        return init_impl(input, center, half_length);
+    } catch (const std::exception &e) { // reference baobzi.cpp:178-182 prints the exception text and returns NULL
+        std::fprintf(stderr, "%s\n", e.what());
+    } catch (...) {
+        std::fprintf(stderr, "Baobzi error: unknown exception during initialization\n");
+    }
+    return nullptr;
+}
+
+static baobzi_t restore_impl(const char *filename) {
     auto f = std::make_unique<Function>();
     std::string err;
     if (!bz::read_baobzi_file(filename, f->host, err)) {
@@ -510,7 +561,7 @@ baobzi_t baobzi_restore(const char *filename) {
     return bz::make_handle(std::move(f));
 }
 
-baobzi_t baobzi_init(const baobzi_input_t *input, const double *center, const double *half_length) {
+static baobzi_t init_impl(const baobzi_input_t *input, const double *center, const double *half_length) {
     // argument checks in the order of reference baobzi.cpp:148-157
     if (input->tol <= 0.0) {
         std::fprintf(stderr, "Baobzi error: Unable to initialize Baobzi due to invalid 'tol' parameter. Please supply "
@@ -626,7 +677,8 @@ int baobzi_eval_multi_device_dot(const baobzi_t func, const double *d_x, const d
     int64_t launches = 0;
     int rc = 0;
     bz::workspace_begin(r, stream);
-    const bool binned = bz::use_binned(f, r->dt, ntrg), bucketed = !binned && bz::use_bucketed(f, r->dt, ntrg);
+    const bool odd = bz::misaligned_2d(r->dt, d_x);
+    const bool binned = !odd && bz::use_binned(f, r->dt, ntrg), bucketed = !odd && !binned && bz::use_bucketed(f, r->dt, ntrg);
     if (!binned && !bucketed) { // fused: the values never leave registers
         rc = reserve_doubles(r->dot_partial, r->dot_partial_cap, G, stream);
         if (rc == 0)
@@ -634,7 +686,8 @@ int baobzi_eval_multi_device_dot(const baobzi_t func, const double *d_x, const d
         if (rc == 0)
             rc = bz::launch_sum_partials(r->dot_partial, G, d_out, stream, &launches);
     } else { // grouped evaluation chunk by chunk into an L2-sized scratch array, consumed at once
-        int64_t step = f->chunk > 0 ? f->chunk : (binned ? bz::default_chunk(r->dt) : bz::default_bucket_chunk());
+        const int64_t fc = f->chunk.load();
+        int64_t step = fc > 0 ? fc : (binned ? bz::default_chunk(r->dt) : bz::default_bucket_chunk());
         if (step > ntrg)
             step = ntrg;
         const int64_t n_chunks = (ntrg + step - 1) / step;
@@ -737,12 +790,17 @@ int baobzi_eval_multi_sharded(const baobzi_t func, int n_dev, const int *devices
 int baobzi_sync(const baobzi_t func) {
     Function *f = (Function *)func->obj;
     int rc = 0;
-    for (auto &r : f->replicas) {
-        bz::DeviceGuard g(r->dt.device);
-        if (r->shard_stream) {
-            int e = (int)cudaStreamSynchronize(r->shard_stream);
-            rc = rc ? rc : e;
-        }
+    std::vector<std::pair<int, cudaStream_t>> streams; // snapshot under the lock, wait outside it
+    {
+        std::lock_guard<std::mutex> lock(f->mu);
+        for (auto &r : f->replicas)
+            if (r->shard_stream)
+                streams.emplace_back(r->dt.device, r->shard_stream);
+    }
+    for (auto &ds : streams) {
+        bz::DeviceGuard g(ds.first);
+        int e = (int)cudaStreamSynchronize(ds.second);
+        rc = rc ? rc : e;
     }
     return rc;
 }
@@ -751,8 +809,8 @@ int baobzi_set_mode(baobzi_t func, int mode, int64_t chunk) {
     Function *f = (Function *)func->obj;
     if (mode < 0 || mode > 3)
         return 1;
-    f->mode = mode;
-    f->chunk = chunk > 0 ? chunk : 0;
+    f->mode.store(mode);
+    f->chunk.store(chunk > 0 ? chunk : 0);
     return 0;
 }
 
@@ -760,15 +818,15 @@ int64_t baobzi_launch_count(const baobzi_t func) { return ((Function *)func->obj
 
 int baobzi_profile_begin(baobzi_t func) {
     Function *f = (Function *)func->obj;
-    std::lock_guard<std::mutex> lock(f->mu);
-    f->profile = std::make_unique<bz::StageProfile>();
+    std::lock_guard<std::mutex> lock(f->prof_mu);
+    f->profile = std::make_shared<bz::StageProfile>();
     return 0;
 }
 
 int baobzi_profile_end(baobzi_t func, double *ms, int64_t *launches, int64_t *points) {
     Function *f = (Function *)func->obj;
     cudaError_t e = cudaDeviceSynchronize();
-    std::lock_guard<std::mutex> lock(f->mu);
+    std::lock_guard<std::mutex> lock(f->prof_mu);
     if (!f->profile)
         return (int)cudaErrorInvalidValue;
     f->profile->collect(ms, launches, points);

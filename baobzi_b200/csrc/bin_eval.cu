@@ -20,9 +20,9 @@
 // Arithmetic: cheb.cuh's order (bit-identical to the reference's AVX2+FMA build).  Multiplications by
 // T_0 = 1.0 are not executed (x * 1.0 == x bit for bit): a row chain starts as fma(c_1, T_1, c_0), and the
 // T recurrences run from T_{-1} = T_1 = x so that every slab executes the same code (fma(2x, 1, -x) == x exactly).
-#include "cheb.cuh"
+#include "baobzi/cheb.cuh"
 #include "device_tree.hpp"
-#include "lookup.cuh"
+#include "baobzi/lookup.cuh"
 
 #include <cstdio>
 #include <cstdlib>

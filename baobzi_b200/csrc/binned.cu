@@ -27,7 +27,7 @@
 #include <cstdlib>
 #include <utility>
 
-#include "lookup.cuh"
+#include "baobzi/lookup.cuh"
 
 #include <cooperative_groups.h>
 

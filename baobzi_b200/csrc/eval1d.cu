@@ -27,9 +27,9 @@
 // (like L1) write-back is 128 B/clk/SM whether or not lanes share an address: 32 clk per warp of points for the
 // coefficients + ~10 for the point, the node table and the result.  That is 1.95e11 evals/s = 0.48 of HBM
 // bandwidth (generic kernel: 1.17e11); orders <= 8 need half the bytes and come out HBM bound.
-#include "cheb.cuh"
+#include "baobzi/cheb.cuh"
 #include "device_tree.hpp"
-#include "lookup.cuh"
+#include "baobzi/lookup.cuh"
 
 #include <cstdio>
 #include <cstdlib>

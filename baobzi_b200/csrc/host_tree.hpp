@@ -19,6 +19,7 @@ namespace bz {
 constexpr uint32_t kNoChild = 0xFFFFFFFFu;            // Node::first_child_idx of a leaf (template.hpp:209)
 constexpr uint64_t kNoCoeffs = 0xFFFFFFFFFFFFFFFFull; // Node::coeff_offset of an internal node (template.hpp:208)
 constexpr int kFormatVersion = 5;                     // include/baobzi/header.h:4
+constexpr uint32_t kMaxOutputDim = 1u << 20;          // sanity bound on output_dim_ read from a file
 
 struct HostTree {
     int dim = 0, order = 0;

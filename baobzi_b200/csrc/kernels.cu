@@ -15,7 +15,7 @@
 //           coefficient load is a warp-uniform broadcast served from L1 and feeds 2*P FMAs
 //           (P points per thread, register blocked).  FP64-pipe bound.
 #include "device_tree.hpp"
-#include "eval_point.cuh"
+#include "baobzi/eval_point.cuh"
 #include "host_tree.hpp"
 
 #include <algorithm>

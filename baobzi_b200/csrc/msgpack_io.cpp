@@ -29,6 +29,16 @@ class Reader {
     Reader(const uint8_t *d, size_t n) : p_(d), end_(d + n) {}
     bool ok() const { return !bad_; }
     void fail() { bad_ = true; }
+    // bytes left: every msgpack object takes at least one, so a declared length above this is a lie and must not
+    // reach resize() (a 4-byte length field could otherwise ask for 32 GB before the first payload byte is seen)
+    size_t remaining() const { return (size_t)(end_ - p_); }
+    uint64_t bounded_len(uint64_t n) {
+        if (n > remaining()) {
+            bad_ = true;
+            return 0;
+        }
+        return n;
+    }
 
     uint64_t be(int nbytes) {
         if ((size_t)(end_ - p_) < (size_t)nbytes) {
@@ -204,13 +214,13 @@ bool read_baobzi_mem(const uint8_t *data, size_t len, HostTree &t, std::string &
             r.box(t.box_center, t.box_inv_half_length, dim);
         } else if (key == "subtrees_") {
             seen_subtrees = true;
-            uint64_t nsub = r.array_len();
+            uint64_t nsub = r.bounded_len(r.array_len());
             t.subtree_begin.assign(1, 0u);
             t.subtree_begin.reserve(nsub + 1);
             for (uint64_t s = 0; s < nsub && r.ok(); ++s) {
                 if (r.array_len() != 1)
                     r.fail();
-                uint64_t nn = r.array_len();
+                uint64_t nn = r.bounded_len(r.array_len());
                 size_t base = t.first_child.size();
                 t.center.resize((base + nn) * dim);
                 t.inv_half_length.resize((base + nn) * dim);
@@ -243,7 +253,7 @@ bool read_baobzi_mem(const uint8_t *data, size_t len, HostTree &t, std::string &
         } else if (key == "inv_bin_size_") {
             r.eigen(t.inv_bin_size, dim);
         } else if (key == "coeffs_") {
-            uint64_t n = r.array_len();
+            uint64_t n = r.bounded_len(r.array_len());
             t.coeffs.resize(n);
             for (uint64_t i = 0; i < n && r.ok(); ++i)
                 t.coeffs[i] = r.real();
@@ -490,6 +500,10 @@ std::string HostTree::validate() const {
         return "inconsistent node arrays";
     if (nn >= 0xFFFFFFFFull)
         return "too many nodes";
+    if (output_dim > kMaxOutputDim)
+        return "output_dim out of range";
+    if (coeffs.size() >= (uint64_t(1) << 35)) // the device layout addresses blocks in 16-byte units with 32 bits
+        return "coefficient array too large";
     const int nchild = 1 << dim;
     // the scalar path reads output_dim blocks of ORDER doubles (template.hpp:373-374); the batched path
     // one block of order^dim
@@ -499,12 +513,19 @@ std::string HostTree::validate() const {
             return "empty subtree";
         for (uint32_t g = b; g < e; ++g) {
             if (is_leaf(g)) {
-                uint64_t need = (uint64_t)block_doubles();
-                if (coeff_offset[g] + need > coeffs.size())
+                // 1D: the scalar / all-components entries read node_output_dim blocks of ORDER doubles
+                // (template.hpp:373-374); otherwise one block of order^dim
+                if (node_output_dim[g] > kMaxOutputDim)
+                    return "node output_dim out of range";
+                const uint64_t od = node_output_dim[g] < 1 ? 1 : node_output_dim[g];
+                const uint64_t need = dim == 1 ? (uint64_t)order * od : (uint64_t)block_doubles();
+                if (coeff_offset[g] > coeffs.size() || need > coeffs.size() - coeff_offset[g]) // no wrap-around
                     return "leaf coefficient block out of range";
             } else {
+                // children follow their parent in the breadth-first order of a subtree (template.hpp:406-457):
+                // a link at or before the node itself would make the descent loop for ever
                 uint64_t c0 = first_child[g];
-                if (first_child[g] == kNoChild || c0 + nchild > (uint64_t)(e - b) || c0 == 0)
+                if (first_child[g] == kNoChild || c0 + nchild > (uint64_t)(e - b) || c0 <= (uint64_t)(g - b))
                     return "child index out of range";
             }
         }

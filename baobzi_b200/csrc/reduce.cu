@@ -9,7 +9,7 @@
 // The summation order is fixed by (n, grid), never by timing: thread t adds its grid-stride elements in sequence, lanes
 // combine by a shuffle tree, warps and CTAs in index order -- two calls on the same device give the same bits.
 #include "device_tree.hpp"
-#include "eval_point.cuh"
+#include "baobzi/eval_point.cuh"
 
 namespace bz {
 

@@ -5,7 +5,7 @@
 #pragma once
 
 #include "cheb.cuh"
-#include "device_tree.hpp"
+#include "device_layout.hpp"
 #include "lookup.cuh"
 
 namespace bz {

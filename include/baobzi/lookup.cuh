@@ -2,7 +2,7 @@
 // test, the grid-cell floor transform and the subtree descent.
 #pragma once
 
-#include "device_tree.hpp"
+#include "device_layout.hpp"
 
 #include <cuda_runtime.h>
 
@@ -133,9 +133,16 @@ __device__ __forceinline__ uint32_t locate_leaf(const TreeView &tv, const double
 template <int DIM>
 __device__ __forceinline__ void load_point(const double *__restrict__ x, int64_t i, double (&p)[DIM]) {
     if constexpr (DIM == 2) {
-        const double2 v = __ldcs(reinterpret_cast<const double2 *>(x) + i); // streamed once
-        p[0] = v.x;
-        p[1] = v.y;
+        // one 16-byte load when the caller's array allows it (uniform test on the base pointer: the reference API does
+        // not promise more than 8-byte alignment), else two 8-byte ones
+        if ((reinterpret_cast<uintptr_t>(x) & 15u) == 0) {
+            const double2 v = __ldcs(reinterpret_cast<const double2 *>(x) + i); // streamed once
+            p[0] = v.x;
+            p[1] = v.y;
+        } else {
+            p[0] = __ldcs(x + 2 * i);
+            p[1] = __ldcs(x + 2 * i + 1);
+        }
     } else {
 #pragma unroll
         for (int j = 0; j < DIM; ++j)

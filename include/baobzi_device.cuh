@@ -24,7 +24,7 @@
 
 #include "baobzi.h"
 
-#include "../baobzi_b200/csrc/eval_point.cuh"
+#include "baobzi/eval_point.cuh" // self-contained: everything it needs lives under include/baobzi/
 
 namespace baobzi_device {
 

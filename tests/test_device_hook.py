@@ -17,9 +17,9 @@ def _nvcc():
     return shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 
 
-def _compile(out, extra=()):
-    cmd = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-O2", "-std=c++17", "-I", os.path.join(ROOT, "include"),
-           *extra, "-o", out, SRC]
+def _compile(out, extra=(), include=None):
+    cmd = [_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-O2", "-std=c++17", "-I",
+           include or os.path.join(ROOT, "include"), *extra, "-o", out, SRC]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     assert r.returncode == 0, r.stdout
     return out
@@ -28,6 +28,18 @@ def _compile(out, extra=()):
 def test_device_header_compiles_in_user_code(tmp_path):
     """No GPU needed: the public device header is self-contained (object file only, nothing runs)."""
     _compile(str(tmp_path / "fused_user_kernel.o"), extra=("-c",))
+
+
+def test_public_headers_are_installable_on_their_own(tmp_path):
+    """include/ copied somewhere else (as `make install` would) still compiles a user kernel: nothing in it reaches
+    back into baobzi_b200/csrc."""
+    inc = tmp_path / "prefix" / "include"
+    shutil.copytree(os.path.join(ROOT, "include"), inc)
+    _compile(str(tmp_path / "fused_user_kernel.o"), extra=("-c",), include=str(inc))
+    for dirpath, _, files in os.walk(inc):
+        for f in files:
+            text = open(os.path.join(dirpath, f)).read()
+            assert not [ln for ln in text.splitlines() if ln.lstrip().startswith("#include") and "csrc" in ln], f
 
 
 @pytest.mark.gpu

@@ -39,6 +39,74 @@ def test_reader_rejects_bad_input(hostlib, tmp_path):
     assert hostlib.bzt_read_status(os.fsencode(path), msg, 256) == 0
 
 
+def _repack(name, edit):
+    """A reference-written golden file decoded with python-msgpack, edited, re-encoded (an unedited re-encode is
+    byte-identical to the file, checked below)."""
+    import copy
+    import msgpack
+    raw = open(load_golden(name)[0], "rb").read()
+    u = msgpack.Unpacker(raw=False, strict_map_key=False)
+    u.feed(raw)
+    head, body = list(u)
+    assert msgpack.packb(head) + msgpack.packb(body) == raw
+    body = copy.deepcopy(body)
+    edit(body)
+    return msgpack.packb(head) + msgpack.packb(body)
+
+
+def test_reader_rejects_structurally_bad_trees(hostlib, tmp_path):
+    """Files that parse as msgpack but would make the kernels read out of bounds or loop for ever."""
+    msg = C.create_string_buffer(256)
+
+    def leaf_of(body, sub=0):
+        return next(n for n in body["subtrees_"][sub][0] if n[1] == 0xFFFFFFFF)
+
+    def deep_sub(body):
+        return next(s[0] for s in body["subtrees_"] if len(s[0]) > 1)
+
+    def wrap(body):                     # coeff_offset + need wraps around 2^64
+        leaf_of(body)[2] = 2 ** 64 - 2
+
+    def past_end(body):
+        leaf_of(body)[2] = len(body["coeffs_"]) - 2
+
+    def multi_output_short(body):       # a 1D leaf claiming more output blocks than coeffs_ holds
+        n = leaf_of(body, len(body["subtrees_"]) - 1)
+        n[3] = 64
+
+    def cycle(body):                    # first_child pointing back at the node itself: the descent would never end
+        nodes = deep_sub(body)
+        parent = next(i for i, n in enumerate(nodes) if n[1] != 0xFFFFFFFF)
+        nodes[parent][1] = parent if parent + 2 <= len(nodes) else 0
+
+    def child_before_parent(body):
+        nodes = deep_sub(body)
+        inner = [i for i, n in enumerate(nodes) if n[1] != 0xFFFFFFFF]
+        nodes[inner[-1]][1] = max(inner[-1] - 1, 0) if inner[-1] else 0
+
+    def huge_output_dim(body):
+        body["output_dim_"] = 2 ** 31
+
+    for tag, name, edit in [("wrap", "t1d_o6", wrap), ("past_end", "t1d_o6", past_end),
+                            ("multi_short", "t1d_o6", multi_output_short), ("cycle", "deep_1d", cycle),
+                            ("backlink", "deep_1d", child_before_parent), ("outdim", "t1d_o6", huge_output_dim)]:
+        p = tmp_path / (tag + ".baobzi")
+        p.write_bytes(_repack(name, edit))
+        assert hostlib.bzt_read_status(os.fsencode(str(p)), msg, 256) != 0, tag
+    # declared lengths far beyond the bytes that follow must fail before any allocation of that size
+    raw = open(load_golden("t1d_o6")[0], "rb").read()
+    k = raw.index(b"coeffs_") + len(b"coeffs_")
+    assert raw[k] == 0xdc                                   # array16 header of coeffs_
+    lie = raw[:k] + b"\xdd\xff\xff\xff\xf0" + raw[k + 3:]     # array32 claiming 4 G entries
+    p = tmp_path / "lie.baobzi"
+    p.write_bytes(lie)
+    assert hostlib.bzt_read_status(os.fsencode(str(p)), msg, 256) != 0
+    k = raw.index(b"subtrees_") + len(b"subtrees_")
+    assert raw[k] == 0xdc
+    p.write_bytes(raw[:k] + b"\xdd\xff\xff\xff\xf0" + raw[k + 3:])
+    assert hostlib.bzt_read_status(os.fsencode(str(p)), msg, 256) != 0
+
+
 FIT_CASES = [  # the four fixtures of the reference's tests/test_c.cpp (27-71, 73-121, 123-168, 170-215)
     ("testfun_1d", 1, 8, 1e-10, [3.0], [1.0], 1.5, 1),
     ("testfun_1d2", 1, 8, 1e-10, [3.0], [1.0], 1.5, 2),
