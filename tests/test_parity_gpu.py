@@ -161,3 +161,92 @@ def test_concurrent_calls_on_one_handle(gpu_lib, ref):
     for i in range(8):
         assert ulp(ref, outs[i], t.eval_multi(xs[i], ref.ARITH_AVX2)) == 0
     b.free()
+
+
+@pytest.mark.parametrize("name", ["t2d_o8", "osc_2d", "t2d_o12"])
+def test_2d_points_that_are_only_8_byte_aligned(gpu_lib, ref, name):
+    """The reference API promises nothing beyond `const double *`: a 2D point array may start on an odd double (a
+    view one element into a buffer).  Every device entry must take it (no misaligned-address fault) and give the
+    same bits -- whatever mode was asked for."""
+    import torch
+    path, _ = load_golden(name)
+    t = ref.OracleTree(path)
+    a = t.arrays()
+    rng = np.random.default_rng(5)
+    n = 1_200_001   # above the auto-mode thresholds of the grouped 2D paths
+    x = a["lower_left"] + rng.random((n, 2)) * (a["upper_right"] - a["lower_left"])
+    want = t.eval_multi(x[:50000], ref.ARITH_AVX2)
+    flat = torch.empty(2 * n + 1, dtype=torch.float64, device="cuda")
+    flat[1:] = torch.from_numpy(x).cuda().reshape(-1)
+    xv = flat[1:].view(n, 2)
+    assert xv.data_ptr() % 16 == 8 and xv.is_contiguous()
+    b = gpu_lib.Baobzi(filename=path)
+    aligned = b(torch.from_numpy(x).cuda()).clone()
+    for mode in ("auto", "direct", "binned", "bucketed"):
+        b.set_mode(mode)
+        y = b(xv)
+        torch.cuda.synchronize()
+        assert torch.equal(y.view(torch.int64), aligned.view(torch.int64)), mode
+    assert ulp(ref, aligned[:50000].cpu().numpy(), want) == 0
+    assert np.array_equal(b.node_index(xv[:50000]).cpu().numpy(), t.node_indices(x[:50000]))
+    w = torch.ones(n, dtype=torch.float64, device="cuda")
+    b.set_mode("direct")
+    assert torch.equal(b.dot(xv, w), b.dot(torch.from_numpy(x).cuda(), w))
+    # the classic entry with device pointers
+    y2 = torch.empty(n, dtype=torch.float64, device="cuda")
+    b._lib.baobzi_eval_multi(b.ptr, xv.data_ptr(), y2.data_ptr(), n)
+    assert torch.equal(y2.view(torch.int64), aligned.view(torch.int64))
+    b.free()
+
+
+class _CudaArray:
+    """A CUDA buffer that is not a torch tensor: only __cuda_array_interface__ (what cupy / numba arrays expose)."""
+
+    def __init__(self, tensor):
+        self._keep = tensor
+        self.__cuda_array_interface__ = {"shape": tuple(tensor.shape), "typestr": "<f%d" % tensor.element_size(),
+                                         "data": (tensor.data_ptr(), False), "version": 3, "strides": None}
+
+
+def test_cuda_array_interface_inputs(gpu_lib, ref):
+    """Binding-level device entry for non-torch CUDA arrays."""
+    import torch
+    path, g = load_golden("t3d_o8")
+    b = gpu_lib.Baobzi(filename=path)
+    xd = torch.from_numpy(g["x"]).cuda()
+    out = torch.full((xd.shape[0],), -7.0, dtype=torch.float64, device="cuda")
+    ret = b(_CudaArray(xd), out=_CudaArray(out))
+    torch.cuda.synchronize()
+    assert isinstance(ret, _CudaArray)
+    assert ulp(ref, out.cpu().numpy(), g["y_avx2"]) == 0
+    with pytest.raises(TypeError):
+        b(_CudaArray(xd))                                     # no torch tensor to size the output from
+    with pytest.raises(TypeError):
+        b(_CudaArray(xd), out=_CudaArray(out[:5]))            # too small
+    with pytest.raises(TypeError):
+        b(_CudaArray(xd.float()))                             # wrong dtype is refused, not reinterpreted
+    b.free()
+
+
+def test_host_out_argument_is_validated(gpu_lib):
+    path, g = load_golden("t2d_o8")
+    b = gpu_lib.Baobzi(filename=path)
+    x = g["x"]
+    for bad in (np.empty(len(x), dtype=np.float32), np.empty(len(x) - 1), np.empty(2 * len(x))[::2]):
+        with pytest.raises(TypeError):
+            b(x, out=bad)
+    out = np.empty(len(x) + 3)
+    assert b(x, out=out) is out
+    b.free()
+
+
+def test_python_callback_exception_propagates(gpu_lib):
+    calls = []
+
+    def f(x):
+        calls.append(1)
+        if len(calls) > 5:
+            raise ZeroDivisionError("boom")
+        return 1.0 + x[0]
+    with pytest.raises(ZeroDivisionError):
+        gpu_lib.Baobzi(fin=f, dim=1, order=8, center=np.array([0.0]), half_length=np.array([1.0]), tol=1e-10)

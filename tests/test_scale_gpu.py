@@ -13,6 +13,15 @@ CONFIGS = {  # BASELINE.json configs
     "C3": dict(func="testfun_3d", dim=3, order=8, tol=1e-12, center=[1.5, 3.0, 1.5], hl=[1.0, 1.0, 1.0], data=None),
     "C5": dict(func="testfun_3d", dim=3, order=12, tol=1e-12, center=[1.5, 3.0, 1.5], hl=[1.0, 1.0, 1.0], data=None),
 }
+# The two trees that take the paths the configurations above never reach (fitted once per session, ~10 s each):
+#   C4  BASELINE.json configs[3]: 2D order 6 oscillatory, 1 041 664 leaves, 300 MB of coefficients (> L2): the only
+#       configuration that selects the bucketed path in auto mode
+#   B3  a 3D tree above 40 960 leaves (C3's function on a 4 x 2 x 2 box, order 6: 65 536 leaves): the histogram no
+#       longer fits in shared memory, so the binned path falls back to its four-kernel sort
+BIG = {
+    "C4": dict(func="testfun_2d_osc", dim=2, order=6, tol=1e-10, center=[0.0, 0.0], hl=[1.0, 1.0], data=20.0),
+    "B3": dict(func="testfun_3d", dim=3, order=6, tol=3e-11, center=[2.0, 3.0, 1.5], hl=[2.0, 1.0, 1.0], data=None),
+}
 
 
 def make(gpu_lib, ref, cfg, **kw):
@@ -34,6 +43,88 @@ def test_benchmark_trees_match_oracle(gpu_lib, ref, tmp_path, tag):
     assert np.array_equal(b.node_index(x), t.node_indices(x))
     assert ref.ulp_diff(b(x), t.eval_multi(x, ref.ARITH_AVX2)).max() == 0
     b.free()
+
+
+@pytest.fixture(scope="module")
+def big_trees(gpu_lib, ref, tmp_path_factory):
+    made = {}
+
+    def get(tag):
+        if tag not in made:
+            b = make(gpu_lib, ref, BIG[tag])
+            path = str(tmp_path_factory.mktemp("big") / (tag + ".baobzi"))
+            b.save(path)
+            made[tag] = (b, ref.OracleTree(path))
+        return made[tag]
+    yield get
+    for b, _ in made.values():
+        b.free()
+
+
+def _uniform(cfg, n, seed):
+    import torch
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    c = torch.tensor(cfg["center"], dtype=torch.float64, device="cuda")
+    h = torch.tensor(cfg["hl"], dtype=torch.float64, device="cuda")
+    return c + (torch.rand((n, cfg["dim"]), generator=g, dtype=torch.float64, device="cuda") * 2 - 1) * h
+
+
+def _stages(b, x):
+    b.profile_begin()
+    y = b(x)
+    st = b.profile_end()
+    return y, {k for k, v in st.items() if v[1] > 0}
+
+
+def test_config4_tree_larger_than_l2(gpu_lib, ref, big_trees):
+    """BASELINE.json configs[3] at its own tree size: auto mode must take the bucketed path and give the oracle's
+    bits; node indices exact; direct and forced-bucketed agree bit for bit on the whole batch."""
+    import torch
+    b, t = big_trees("C4")
+    assert t.n_leaves > 1_000_000 and t.n_nodes > 1_300_000
+    n, m = 3_000_000, 200_000
+    x = _uniform(BIG["C4"], n, 7)
+    b.set_mode("auto")
+    y_auto, used = _stages(b, x)
+    assert used == {"sort", "eval_grouped"}, used            # bucketed: grouped evaluation, no direct kernel
+    y_auto = y_auto.clone()
+    xs = x[:m].cpu().numpy()
+    want = t.eval_multi(xs, ref.ARITH_AVX2)
+    assert ref.ulp_diff(y_auto[:m].cpu().numpy(), want).max() == 0
+    assert np.array_equal(b.node_index(xs), t.node_indices(xs))
+    b.set_mode("direct")
+    y_dir, used = _stages(b, x)
+    assert used == {"eval_direct"}, used
+    assert torch.equal(y_dir.view(torch.int64), y_auto.view(torch.int64))
+    b.set_mode("bucketed", 1 << 19)                           # several chunks: the split sort on bucket keys
+    assert torch.equal(b(x).view(torch.int64), y_auto.view(torch.int64))
+    b.set_mode("bucketed")
+    assert ref.ulp_diff(b(x[:m].contiguous()).cpu().numpy(), want).max() == 0
+    b.set_mode("auto")
+
+
+def test_3d_tree_above_the_fused_sort_limit(gpu_lib, ref, big_trees):
+    """65 536 leaves: auto mode selects the binned path, whose sort is the four-kernel fallback here."""
+    import torch
+    b, t = big_trees("B3")
+    assert t.n_leaves > 40960
+    n, m = 4_000_000, 100_000
+    x = _uniform(BIG["B3"], n, 9)
+    b.set_mode("auto")
+    y_auto, used = _stages(b, x)
+    assert {"scan", "scatter", "eval_grouped"} <= used and "eval_direct" not in used, used
+    y_auto = y_auto.clone()
+    xs = x[:m].cpu().numpy()
+    want = t.eval_multi(xs, ref.ARITH_AVX2)
+    assert ref.ulp_diff(y_auto[:m].cpu().numpy(), want).max() == 0
+    assert np.array_equal(b.node_index(xs), t.node_indices(xs))
+    b.set_mode("direct")
+    assert torch.equal(b(x).view(torch.int64), y_auto.view(torch.int64))
+    b.set_mode("binned", 1 << 20)                             # several chunks through the fallback sort
+    assert torch.equal(b(x).view(torch.int64), y_auto.view(torch.int64))
+    b.set_mode("bucketed")                                    # the same tree through the bucketed path
+    assert torch.equal(b(x).view(torch.int64), y_auto.view(torch.int64))
+    b.set_mode("auto")
 
 
 @pytest.mark.parametrize("tag,n", [("C1", 10_000_000), ("C3", 20_000_000), ("C5", 4_000_000), ("C2", 50_000_000)])
