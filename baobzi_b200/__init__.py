@@ -60,6 +60,8 @@ ABI = {
     "baobzi_eval_multi_device_all": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "baobzi_eval_multi_device_dot": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "baobzi_device_view": (C.c_int, [baobzi_t, C.c_int, C.c_void_p, C.c_size_t]),
+    "baobzi_tree_info": (C.c_int, [baobzi_t, C.POINTER(C.c_int64)]),
+    "baobzi_set_host_devices": (C.c_int, [baobzi_t, C.c_int]),
     "baobzi_launch_count": (C.c_int64, [baobzi_t]),
     "baobzi_profile_begin": (C.c_int, [baobzi_t]),
     "baobzi_profile_end": (C.c_int, [baobzi_t, c_double_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
@@ -323,6 +325,11 @@ class Baobzi:
         if self._lib.baobzi_set_mode(self.ptr, m, int(chunk)) != 0:
             raise ValueError("bad mode")
 
+    def set_host_devices(self, n_devices):
+        """GPUs a numpy (host-pointer) call is spread over: 1 = current device, 0 = all visible."""
+        if self._lib.baobzi_set_host_devices(self.ptr, int(n_devices)) != 0:
+            raise ValueError("bad device count")
+
     # "sort": fused lookup + scan + scatter (binned / bucketed paths); "scan", "scatter": only the unfused fallback
     STAGES = ("sort", "scan", "scatter", "eval_grouped", "eval_direct")
 
@@ -338,6 +345,12 @@ class Baobzi:
         if rc != 0:
             raise RuntimeError("baobzi_profile_end failed with CUDA error %d" % rc)
         return {s: (ms[i], la[i], pts[i]) for i, s in enumerate(self.STAGES)}
+
+    def tree_info(self):
+        """{nodes, leaves, grid_cells, coeff_bytes, device_bytes} of the fitted tree (baobzi_tree_info)."""
+        v = (C.c_int64 * 5)()
+        self._lib.baobzi_tree_info(self.ptr, v)
+        return {"nodes": v[0], "leaves": v[1], "grid_cells": v[2], "coeff_bytes": 8 * v[3], "device_bytes": v[4]}
 
     @property
     def launches(self):

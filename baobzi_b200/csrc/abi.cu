@@ -18,7 +18,9 @@
 #include <exception>
 #include <memory>
 #include <mutex>
+#include <algorithm>
 #include <string>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -28,13 +30,12 @@ namespace bz {
 // workspace, and pinned scratch for the scalar entry point.
 struct ExecContext {
     cudaStream_t stream = nullptr;
-    // host-pointer pipeline: kSlots chunks in flight
-    static constexpr int kSlots = 3;
-    double *d_x[kSlots] = {nullptr, nullptr, nullptr};
-    double *d_res[kSlots] = {nullptr, nullptr, nullptr};
-    cudaStream_t slot_stream[kSlots] = {nullptr, nullptr, nullptr};
+    // host-pointer path: one chunk in flight per context (several contexts work on one call, see fn_eval_multi)
+    double *d_x = nullptr, *d_res = nullptr; // device chunk buffers
     int64_t slot_points = 0;
-    BinWorkspace ws[kSlots];
+    double *h_x = nullptr, *h_res = nullptr; // pinned staging for pageable caller memory
+    int64_t staged_points = 0;
+    BinWorkspace ws;
     double *pinned = nullptr; // scalar eval scratch: x[3] then y[out_dim]
     size_t pinned_doubles = 0;
     bool busy = false;
@@ -59,6 +60,7 @@ enum Mode { kAuto = 0, kDirect = 1, kBinned = 2, kBucketed = 3 };
 
 struct Function {
     HostTree host;
+    int host_devices = 1; // GPUs a host-pointer call is spread over (baobzi_set_host_devices / BAOBZI_B200_DEVICES)
     std::mutex mu;
     std::vector<std::unique_ptr<Replica>> replicas;
     std::atomic<int> mode{kAuto};       // baobzi_set_mode may race with evaluations on other threads
@@ -177,15 +179,13 @@ void release(Function *f, ExecContext *c) {
 }
 
 void destroy_context(ExecContext &c) {
-    for (int s = 0; s < ExecContext::kSlots; ++s) {
-        if (c.d_x[s])
-            cudaFree(c.d_x[s]);
-        if (c.d_res[s])
-            cudaFree(c.d_res[s]);
-        if (c.slot_stream[s])
-            cudaStreamDestroy(c.slot_stream[s]);
-        free_workspace(c.ws[s]);
-    }
+    cudaFree(c.d_x);
+    cudaFree(c.d_res);
+    if (c.h_x)
+        cudaFreeHost(c.h_x);
+    if (c.h_res)
+        cudaFreeHost(c.h_res);
+    free_workspace(c.ws);
     if (c.pinned)
         cudaFreeHost(c.pinned);
     if (c.stream)
@@ -350,26 +350,109 @@ void fn_eval(const void *obj, const double *x, double *y) {
     release(f, c);
 }
 
-bool ensure_slots(ExecContext *c, const DeviceTree &dt, int64_t points) {
-    if (c->slot_points >= points)
-        return true;
-    for (int s = 0; s < ExecContext::kSlots; ++s) {
-        if (c->d_x[s])
-            cudaFree(c->d_x[s]);
-        if (c->d_res[s])
-            cudaFree(c->d_res[s]);
-        c->d_x[s] = c->d_res[s] = nullptr;
-        if (!c->slot_stream[s] &&
-            report(cudaStreamCreateWithFlags(&c->slot_stream[s], cudaStreamNonBlocking), "stream create"))
+// ---- host-pointer path ---------------------------------------------------------------------------------------
+// A call with host pointers is cut into chunks that a few WORKER threads take from a shared counter.  Each worker owns
+// one execution context (stream, device chunk buffers, sort workspace) on one GPU and runs, per chunk,
+//     [memcpy caller -> pinned staging]  H2D  kernels  D2H  [memcpy pinned staging -> caller]
+// The bracketed steps only exist for PAGEABLE caller memory -- what the reference's callers hand over (malloc in
+// examples/C/baobzi_timing.c:44-49, numpy in src/python/__init__.py:126-131): cudaMemcpyAsync from pageable memory is
+// staged by the driver through one small buffer and is synchronous with the host, so the pipeline would degenerate
+// to one copy at a time at a fraction of the link rate; one host thread moves ~10 GB/s, the link needs ~55, hence
+// several workers.  With pinned (or cudaHostRegister'ed) memory three workers per GPU keep both directions of the
+// link and the kernels busy.  Workers on several GPUs (baobzi_set_host_devices / BAOBZI_B200_DEVICES) share the same
+// counter, so the chunks balance themselves over the devices; the tree is replicated lazily, there is no collective.
+struct HostJob {
+    Function *f;
+    const double *x;
+    double *res;
+    int64_t n, chunk, n_chunks;
+    int dim;
+    bool stage_x, stage_res;
+    std::atomic<int64_t> next{0};
+    std::atomic<bool> bad{false};
+};
+
+bool ensure_chunk_buffers(ExecContext *c, const DeviceTree &dt, int64_t points, bool stage_x, bool stage_res) {
+    if (c->slot_points < points) {
+        cudaFree(c->d_x);
+        cudaFree(c->d_res);
+        c->d_x = c->d_res = nullptr;
+        c->slot_points = 0;
+        if (report(cudaMalloc((void **)&c->d_x, sizeof(double) * points * dt.view.dim), "chunk alloc") ||
+            report(cudaMalloc((void **)&c->d_res, sizeof(double) * points), "chunk alloc"))
             return false;
-        if (report(cudaMalloc((void **)&c->d_x[s], sizeof(double) * points * dt.view.dim), "chunk alloc") ||
-            report(cudaMalloc((void **)&c->d_res[s], sizeof(double) * points), "chunk alloc")) {
-            c->slot_points = 0;
-            return false;
-        }
+        c->slot_points = points;
     }
-    c->slot_points = points;
+    if ((stage_x || stage_res) && c->staged_points < points) {
+        if (c->h_x)
+            cudaFreeHost(c->h_x);
+        if (c->h_res)
+            cudaFreeHost(c->h_res);
+        c->h_x = c->h_res = nullptr;
+        c->staged_points = 0;
+        if (report(cudaHostAlloc((void **)&c->h_x, sizeof(double) * points * dt.view.dim, cudaHostAllocDefault), "pinned staging alloc") ||
+            report(cudaHostAlloc((void **)&c->h_res, sizeof(double) * points, cudaHostAllocDefault), "pinned staging alloc"))
+            return false;
+        c->staged_points = points;
+    }
     return true;
+}
+
+void host_worker(HostJob *job, int dev) {
+    Function *f = job->f;
+    if (report(cudaSetDevice(dev), "cudaSetDevice")) {
+        job->bad = true;
+        return;
+    }
+    Replica *r = get_replica(f, dev);
+    ExecContext *c = r ? acquire(f, r) : nullptr;
+    if (!c || !ensure_chunk_buffers(c, r->dt, job->chunk, job->stage_x, job->stage_res)) {
+        job->bad = true;
+        if (c)
+            release(f, c);
+        return;
+    }
+    const int dim = job->dim;
+    cudaStream_t st = c->stream;
+    for (;;) {
+        const int64_t k = job->next.fetch_add(1);
+        if (k >= job->n_chunks || job->bad.load())
+            break;
+        const int64_t o = k * job->chunk, m = std::min(job->chunk, job->n - o);
+        const double *src = job->x + o * dim;
+        if (job->stage_x) {
+            std::memcpy(c->h_x, src, sizeof(double) * m * dim);
+            src = c->h_x;
+        }
+        double *dst = job->stage_res ? c->h_res : job->res + o;
+        bool bad = report(cudaMemcpyAsync(c->d_x, src, sizeof(double) * m * dim, cudaMemcpyHostToDevice, st), "H2D copy");
+        if (!bad)
+            bad = report((cudaError_t)eval_device(f, r, c->ws, c->d_x, c->d_res, m, st), "eval launch");
+        if (!bad)
+            bad = report(cudaMemcpyAsync(dst, c->d_res, sizeof(double) * m, cudaMemcpyDeviceToHost, st), "D2H copy");
+        bad = report(cudaStreamSynchronize(st), "eval_multi") || bad;
+        if (bad) {
+            job->bad = true;
+            break;
+        }
+        if (job->stage_res)
+            std::memcpy(job->res + o, c->h_res, sizeof(double) * m);
+    }
+    release(f, c);
+}
+
+bool is_pageable(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return true;
+    }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+
+int env_int(const char *name, int dflt) {
+    const char *s = std::getenv(name);
+    return s && *s ? std::atoi(s) : dflt;
 }
 
 void fn_eval_multi(const void *obj, const double *x, double *res, int ntrg) {
@@ -384,50 +467,64 @@ void fn_eval_multi(const void *obj, const double *x, double *res, int ntrg) {
         if (!c)
             return;
         DeviceGuard g(xdev);
-        int rc = eval_device(f, r, c->ws[0], x, res, ntrg, c->stream);
+        int rc = eval_device(f, r, c->ws, x, res, ntrg, c->stream);
         report((cudaError_t)rc, "eval_multi (device pointers)");
         report(cudaStreamSynchronize(c->stream), "eval_multi (device pointers)");
         release(f, c);
         return;
     }
 
-    int dev = 0;
-    cudaGetDevice(&dev);
-    Replica *r = get_replica(f, dev);
-    ExecContext *c = r ? acquire(f, r) : nullptr;
-    if (!c) {
-        fill_nan(res, ntrg);
-        return;
-    }
-    DeviceGuard g(dev);
-    const int dim = f->host.dim;
-    // Host pointers: pipeline H2D -> kernels -> D2H over kSlots streams so that PCIe traffic in both
-    // directions overlaps evaluation.  Chunk: 4 Mi points, or less for small calls.
+    int dev0 = 0;
+    cudaGetDevice(&dev0);
     const int64_t n = ntrg;
+    const int dim = f->host.dim;
+    HostJob job;
+    job.f = f;
+    job.x = x;
+    job.res = res;
+    job.n = n;
+    job.dim = dim;
+    // pageable memory is staged through pinned buffers once the call is big enough for that to pay (below, the
+    // driver's own staging of a single cudaMemcpyAsync is as good); BAOBZI_B200_STAGE=0 / 1 forces it off / on
+    const int stage_env = env_int("BAOBZI_B200_STAGE", -1);
+    const bool big = n * (dim + 1) * (int64_t)sizeof(double) >= (int64_t(8) << 20);
+    job.stage_x = stage_env == 0 ? false : (is_pageable(x) && (big || stage_env == 1));
+    job.stage_res = stage_env == 0 ? false : (is_pageable(res) && (big || stage_env == 1));
+    // devices: the current one first, then the others in order
+    int visible = 1;
+    cudaGetDeviceCount(&visible);
+    int n_dev = f->host_devices <= 0 ? visible : std::min(f->host_devices, visible);
+    if (n < (int64_t(1) << 22))
+        n_dev = 1; // not worth waking other GPUs (and replicating the tree) for
+    // workers per device: 3 keep H2D, kernels and D2H of a pinned-memory call overlapped; staging needs more host
+    // threads than that to feed the link (measured on B200 hosts)
+    int per_dev = (job.stage_x || job.stage_res) ? 8 : 3;
+    per_dev = env_int("BAOBZI_B200_HOST_WORKERS", per_dev);
+    per_dev = std::max(1, std::min(per_dev, 16));
+    const int hw = (int)std::thread::hardware_concurrency();
+    if (hw > 0 && n_dev * per_dev > std::max(4, hw))
+        per_dev = std::max(1, std::max(4, hw) / n_dev);
+    // chunk: 4 Mi points, or less so that every worker gets something
     int64_t chunk = int64_t(1) << 22;
-    if (n < chunk * ExecContext::kSlots)
-        chunk = (n + ExecContext::kSlots - 1) / ExecContext::kSlots;
-    if (chunk < 1)
-        chunk = 1;
-    bool bad = !ensure_slots(c, r->dt, chunk);
-    int slot = 0;
-    for (int64_t o = 0; o < n && !bad; o += chunk, slot = (slot + 1) % ExecContext::kSlots) {
-        const int64_t m = n - o < chunk ? n - o : chunk;
-        cudaStream_t st = c->slot_stream[slot];
-        bad = report(cudaMemcpyAsync(c->d_x[slot], x + o * dim, sizeof(double) * m * dim, cudaMemcpyHostToDevice, st),
-                     "H2D copy");
-        if (!bad)
-            bad = report((cudaError_t)eval_device(f, r, c->ws[slot], c->d_x[slot], c->d_res[slot], m, st), "eval launch");
-        if (!bad)
-            bad = report(cudaMemcpyAsync(res + o, c->d_res[slot], sizeof(double) * m, cudaMemcpyDeviceToHost, st),
-                         "D2H copy");
+    const int64_t workers_wanted = (int64_t)n_dev * per_dev;
+    if (n < chunk * workers_wanted)
+        chunk = std::max<int64_t>((n + workers_wanted - 1) / workers_wanted, std::min<int64_t>(n, 1 << 16));
+    job.chunk = chunk;
+    job.n_chunks = (n + chunk - 1) / chunk;
+    const int n_workers = (int)std::min<int64_t>(workers_wanted, job.n_chunks);
+    if (n_workers <= 1) {
+        host_worker(&job, dev0);
+        cudaSetDevice(dev0);
+    } else {
+        std::vector<std::thread> th;
+        th.reserve(n_workers);
+        for (int w = 0; w < n_workers; ++w)
+            th.emplace_back(host_worker, &job, (dev0 + w % n_dev) % visible);
+        for (auto &t : th)
+            t.join();
     }
-    for (int s = 0; s < ExecContext::kSlots; ++s)
-        if (c->slot_stream[s])
-            bad = report(cudaStreamSynchronize(c->slot_stream[s]), "eval_multi") || bad;
-    if (bad)
+    if (job.bad.load())
         fill_nan(res, n);
-    release(f, c);
 }
 
 void fn_save(const void *obj, const char *filename) {
@@ -482,6 +579,8 @@ baobzi_t make_handle(std::unique_ptr<Function> f) {
     if (report(cudaGetDevice(&dev), "device query (is a CUDA device visible? there is no CPU evaluation path)"))
         return nullptr;
     f->mode.store(env_mode());
+    if (const char *d = std::getenv("BAOBZI_B200_DEVICES"))
+        f->host_devices = !std::strcmp(d, "all") ? 0 : std::max(1, std::atoi(d));
     if (!get_replica(f.get(), dev))
         return nullptr;
     baobzi_t res = (baobzi_t)std::malloc(sizeof(baobzi_struct));
@@ -811,6 +910,25 @@ int baobzi_set_mode(baobzi_t func, int mode, int64_t chunk) {
         return 1;
     f->mode.store(mode);
     f->chunk.store(chunk > 0 ? chunk : 0);
+    return 0;
+}
+
+int baobzi_tree_info(const baobzi_t func, int64_t info[5]) {
+    Function *f = (Function *)func->obj;
+    info[0] = f->host.n_nodes();
+    info[1] = f->host.n_leaves();
+    info[2] = f->host.n_bins();
+    info[3] = (int64_t)f->host.coeffs.size();
+    std::lock_guard<std::mutex> lock(f->mu);
+    info[4] = f->replicas.empty() ? 0 : (int64_t)f->replicas[0]->dt.blob_bytes;
+    return 0;
+}
+
+int baobzi_set_host_devices(baobzi_t func, int n_devices) {
+    Function *f = (Function *)func->obj;
+    if (n_devices < 0)
+        return 1;
+    f->host_devices = n_devices; // 0 = every visible device
     return 0;
 }
 

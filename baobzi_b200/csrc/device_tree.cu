@@ -156,6 +156,12 @@ int upload_tree(const HostTree &h, DeviceTree &out) {
     v.bin_first_leaf = reinterpret_cast<const uint32_t *>(base + off_binf);
     v.leaf_node = reinterpret_cast<const uint32_t *>(base + off_leaf);
     v.coeffs = reinterpret_cast<const double *>(base + off_coef);
+    if (dim == 1 && leaf_node.size() <= 16) { // few-leaf 1D kernel: coefficients travel as launch parameters
+        out.leaf_coef_1d.resize(leaf_node.size() * (size_t)h.order);
+        for (size_t l = 0; l < leaf_node.size(); ++l)
+            for (int k = 0; k < h.order; ++k)
+                out.leaf_coef_1d[l * h.order + k] = (*coeffs)[(size_t)recs[leaf_node[l]].coeff16 * 2 + k];
+    }
     return 0;
 }
 

@@ -107,6 +107,9 @@ struct DeviceTree {
     void *blob = nullptr; // single allocation backing every array of `view`
     size_t blob_bytes = 0;
     int sm_count = 0;
+    // 1D trees with a handful of leaves: the first-component coefficients [leaf rank][order] on the host, handed to
+    // eval_sorted_1d_kernel as launch parameters (constant bank); empty otherwise
+    std::vector<double> leaf_coef_1d;
 };
 
 // flatten + upload to the current device; returns cudaError_t (0 = ok)
@@ -126,6 +129,9 @@ int launch_eval_direct(const DeviceTree &dt, const double *d_x, double *d_res, i
 bool table_1d_fits(const DeviceTree &dt);
 int64_t table_1d_min_points();
 int launch_eval_table_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream);
+// ... and for trees of at most 16 leaves: CTA-local sort by leaf, coefficients as constant-bank operands
+bool sorted_1d_fits(const DeviceTree &dt);
+int launch_eval_sorted_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream);
 // Every output component of a 1D tree: d_res[i * out_dim + k] (what baobzi_eval writes to y[k], batched).
 int launch_eval_all_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream,
                        int64_t *launches);

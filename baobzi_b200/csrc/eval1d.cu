@@ -144,6 +144,212 @@ eval_table_1d_kernel(const TreeView tv, const double *__restrict__ x, double *__
     }
 }
 
+// ------------------------------------------------------------------------------------------ few-leaf 1D trees
+// A smooth 1D function fits in a handful of leaves (BASELINE.json configs[1], 1.5 log x on [1,3] at order 16: TWO).
+// The table kernel above still pays ORDER * 8 bytes of shared-memory write-back per point for coefficients that the
+// whole warp could share -- if the warp sat in one leaf.  This kernel makes it so: per tile of blockDim * P points a
+// CTA-local counting sort by leaf (the key has <= kU1MaxLeaves + 1 values), then one pass per leaf in which the
+// Clenshaw coefficients are COMPILE-TIME offsets into the kernel's parameter block, i.e. constant-bank operands of the
+// DADD / DFMA instructions themselves: no coefficient load of any kind.  Shared-memory traffic per point drops from
+// 8 x LDS.128 + the node walk to three 8-byte and two 2-byte accesses, and the FP64 work is exactly cheb_eval_1d's
+// (cheb.cuh; same operations in the same order, so the bits are those of the generic kernel).
+//   A  P coalesced point loads per thread, bounds test, grid cell, descent in the shared-memory node table,
+//      u = (x - centre) * inv_half_length (template.hpp:366-369); key = dense leaf rank, n_leaves when outside
+//   B  histogram of the tile (one shared atomic per distinct key and warp: __match_any_sync), exclusive scan over
+//      the <= 17 keys, placement: u and the origin (16-bit index in the tile) go to the key's run
+//   C  for every leaf: its run, two points per thread in flight, coefficients from the constant bank; values go to
+//      s_val[origin] (NaN for the outside run), then one coalesced streaming store of the tile
+constexpr int kU1MaxLeaves = 16;
+constexpr int kU1Threads = 256, kU1P = 4, kU1Tile = kU1Threads * kU1P;
+constexpr int kU1MaxNodes = 64, kU1MaxBins = 64;
+
+struct U1Coef { // by value: lives in the constant bank of the launch
+    double c[kU1MaxLeaves][16];
+};
+
+template <int ORDER, int LEAF>
+__device__ __forceinline__ void u1_run(const U1Coef &cf, const double *s_u, const uint16_t *s_org, double *s_val,
+                                       uint32_t begin, uint32_t end) {
+    for (uint32_t s = begin + threadIdx.x; s < end; s += 2 * kU1Threads) {
+        const bool two = s + kU1Threads < end;
+        const double ua = s_u[s], ub = two ? s_u[s + kU1Threads] : 0.0;
+        const double a2 = __dadd_rn(ua, ua), b2 = __dadd_rn(ub, ub);
+        double a0 = cf.c[LEAF][0], a1 = cf.c[LEAF][1], b0 = a0, b1 = a1;
+#pragma unroll
+        for (int i = 2; i < ORDER; ++i) { // template.hpp:146-161, two independent chains
+            const double c = cf.c[LEAF][i];
+            const double ta = a1, tb = b1;
+            a1 = __dsub_rn(c, a0);
+            b1 = __dsub_rn(c, b0);
+            a0 = __fma_rn(a0, a2, ta);
+            b0 = __fma_rn(b0, b2, tb);
+        }
+        // both chains run unconditionally (the compiler otherwise sinks the second one into a branch and the two no
+        // longer overlap); a missing second point lands in the spare slot behind the tile
+        s_val[s_org[s]] = __fma_rn(a0, ua, a1);
+        s_val[two ? (uint32_t)s_org[s + kU1Threads] : (uint32_t)kU1Tile] = __fma_rn(b0, ub, b1);
+    }
+}
+
+template <int ORDER, int LEAF>
+__device__ __forceinline__ void u1_leaves(const U1Coef &cf, uint32_t n_leaves, const uint32_t *s_start, const double *s_u,
+                                          const uint16_t *s_org, double *s_val) {
+    if constexpr (LEAF < kU1MaxLeaves) {
+        if (LEAF < n_leaves) { // CTA uniform
+            u1_run<ORDER, LEAF>(cf, s_u, s_org, s_val, s_start[LEAF], s_start[LEAF + 1]);
+            u1_leaves<ORDER, LEAF + 1>(cf, n_leaves, s_start, s_u, s_org, s_val);
+        }
+    }
+}
+
+template <int ORDER>
+__global__ void __launch_bounds__(kU1Threads)
+eval_sorted_1d_kernel(const TreeView tv, const U1Coef cf, const double *__restrict__ x, double *__restrict__ res,
+                      int64_t n, int64_t n_tiles) {
+    __shared__ double s_centre[kU1MaxNodes], s_ih[kU1MaxNodes];
+    __shared__ uint32_t s_child[kU1MaxNodes], s_root[kU1MaxBins];
+    __shared__ double s_u[kU1Tile], s_val[kU1Tile + 1];
+    __shared__ uint16_t s_org[kU1Tile];
+    __shared__ uint32_t s_tot[kU1MaxLeaves + 1], s_cur[kU1MaxLeaves + 1], s_start[kU1MaxLeaves + 2];
+    const uint32_t tid = threadIdx.x, lane = tid & 31;
+    const uint32_t L = tv.n_leaves;
+    for (uint32_t node = tid; node < tv.n_nodes; node += kU1Threads) {
+        const NodeHead h = load_head(tv.nodes, node);
+        const NodeTail t = load_tail(tv.nodes, node);
+        s_centre[node] = h.c0;
+        s_ih[node] = t.ih0;
+        s_child[node] = h.child0 == kLeafMark ? (kT1LeafBit | t.leaf_rank) : h.child0;
+    }
+    for (uint32_t b = tid; b < tv.n_bins; b += kU1Threads)
+        s_root[b] = __ldg(tv.bin_root + b);
+    const double lo = tv.lower_left[0], hi = tv.upper_right[0], inv_bin = tv.inv_bin_size[0];
+    const int last_bin = tv.n_sub[0] - 1;
+    const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t base = tile * kU1Tile;
+        const uint32_t m = (uint32_t)(n - base < kU1Tile ? n - base : kU1Tile); // points in this tile
+        if (tid <= kU1MaxLeaves)
+            s_tot[tid] = s_cur[tid] = 0;
+        __syncthreads(); // counters cleared; (first tile) node table staged; previous tile's stores have read s_val
+        // ---- A
+        double xv[kU1P], u[kU1P];
+        uint32_t key[kU1P], grp[kU1P];
+#pragma unroll
+        for (int j = 0; j < kU1P; ++j) {
+            const uint32_t t = j * kU1Threads + tid;
+            xv[j] = t < m ? __ldcs(x + base + t) : lo;
+        }
+#pragma unroll
+        for (int j = 0; j < kU1P; ++j) {
+            const bool out = (xv[j] < lo) || (xv[j] >= hi); // template.hpp:872-873; NaN compares false: "inside"
+            int b = __double2int_rz(__dmul_rn(__dsub_rn(xv[j], lo), inv_bin));
+            b = min(max(b, 0), last_bin);
+            uint32_t node = s_root[b];
+            double c = s_centre[node];
+            uint32_t ch = s_child[node];
+            while (!(ch & kT1LeafBit)) { // template.hpp:482-493
+                node = ch + (uint32_t)(xv[j] > c);
+                c = s_centre[node];
+                ch = s_child[node];
+            }
+            u[j] = __dmul_rn(__dsub_rn(xv[j], c), s_ih[node]);
+            key[j] = out ? L : (ch & ~kT1LeafBit);
+            if (j * kU1Threads + tid >= m)
+                key[j] = 0xFFFFFFFFu; // past the end of the batch: belongs to no run
+        }
+        // ---- B: histogram (one atomic per distinct key and warp)
+#pragma unroll
+        for (int j = 0; j < kU1P; ++j) {
+            grp[j] = __match_any_sync(0xffffffffu, key[j]);
+            if (key[j] != 0xFFFFFFFFu && (uint32_t)(__ffs(grp[j]) - 1) == lane)
+                atomicAdd(&s_tot[key[j]], (uint32_t)__popc(grp[j]));
+        }
+        __syncthreads();
+        if (tid < 32) { // exclusive scan over the L + 1 keys
+            uint32_t v = lane <= L ? s_tot[lane] : 0u, incl = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o)
+                    incl += y;
+            }
+            if (lane <= L + 1)
+                s_start[lane] = incl - v; // s_start[L + 1] = m
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < kU1P; ++j) {
+            const int leader = __ffs(grp[j]) - 1;
+            uint32_t at = 0;
+            if (key[j] != 0xFFFFFFFFu && (uint32_t)leader == lane)
+                at = atomicAdd(&s_cur[key[j]], (uint32_t)__popc(grp[j]));
+            at = __shfl_sync(0xffffffffu, at, leader);
+            if (key[j] != 0xFFFFFFFFu) {
+                const uint32_t pos = s_start[key[j]] + at + (uint32_t)__popc(grp[j] & ((1u << lane) - 1u));
+                s_u[pos] = u[j];
+                s_org[pos] = (uint16_t)(j * kU1Threads + tid);
+            }
+        }
+        __syncthreads();
+        // ---- C
+        u1_leaves<ORDER, 0>(cf, L, s_start, s_u, s_org, s_val);
+        for (uint32_t s = s_start[L] + tid; s < s_start[L + 1]; s += kU1Threads)
+            s_val[s_org[s]] = qnan; // outside [lower_left, upper_right): template.hpp:880-881
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < kU1P; ++j) {
+            const uint32_t t = j * kU1Threads + tid;
+            if (t < m)
+                __stcs(res + base + t, s_val[t]);
+        }
+    }
+}
+
+bool sorted_1d_fits(const DeviceTree &dt) {
+    const TreeView &tv = dt.view;
+    static const bool off = std::getenv("BAOBZI_B200_SORTED1D") && std::atoi(std::getenv("BAOBZI_B200_SORTED1D")) == 0;
+    if (const char *e = std::getenv("BAOBZI_B200_SORTED1D")) // tests flip it between calls
+        if (std::atoi(e) == 0)
+            return false;
+    (void)off;
+    return tv.dim == 1 && tv.n_leaves >= 1 && tv.n_leaves <= (uint32_t)kU1MaxLeaves && tv.n_nodes <= (uint32_t)kU1MaxNodes &&
+           tv.n_bins <= (uint32_t)kU1MaxBins && dt.leaf_coef_1d.size() == (size_t)tv.n_leaves * tv.order;
+}
+
+template <int ORDER>
+static int launch_sorted_order(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream) {
+    U1Coef cf;
+    for (int l = 0; l < kU1MaxLeaves; ++l)
+        for (int k = 0; k < 16; ++k)
+            cf.c[l][k] = (uint32_t)l < dt.view.n_leaves && k < ORDER ? dt.leaf_coef_1d[(size_t)l * ORDER + k] : 0.0;
+    auto kern = eval_sorted_1d_kernel<ORDER>;
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kU1Threads, 0);
+    if (e != cudaSuccess)
+        return (int)e;
+    if (per_sm < 1)
+        return (int)cudaErrorLaunchOutOfResources;
+    const int64_t n_tiles = (n + kU1Tile - 1) / kU1Tile;
+    int64_t grid = (int64_t)dt.sm_count * per_sm;
+    if (grid > n_tiles)
+        grid = n_tiles;
+    kern<<<(unsigned)grid, kU1Threads, 0, stream>>>(dt.view, cf, d_x, d_res, n, n_tiles);
+    return (int)cudaGetLastError();
+}
+
+int launch_eval_sorted_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream) {
+    switch (dt.view.order) {
+    case 6: return launch_sorted_order<6>(dt, d_x, d_res, n, stream);
+    case 8: return launch_sorted_order<8>(dt, d_x, d_res, n, stream);
+    case 10: return launch_sorted_order<10>(dt, d_x, d_res, n, stream);
+    case 12: return launch_sorted_order<12>(dt, d_x, d_res, n, stream);
+    case 14: return launch_sorted_order<14>(dt, d_x, d_res, n, stream);
+    case 16: return launch_sorted_order<16>(dt, d_x, d_res, n, stream);
+    default: return (int)cudaErrorInvalidValue;
+    }
+}
+
 static size_t table_1d_bytes(const TreeView &tv) {
     return 8 * (2 * (size_t)tv.n_nodes + (size_t)tv.order * tv.n_leaves) + 4 * ((size_t)tv.n_nodes + tv.n_bins);
 }
@@ -189,6 +395,8 @@ static int launch_table_order(const DeviceTree &dt, const double *d_x, double *d
 }
 
 int launch_eval_table_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream) {
+    if (sorted_1d_fits(dt)) // a handful of leaves: coefficients as constant-bank operands
+        return launch_eval_sorted_1d(dt, d_x, d_res, n, stream);
     switch (dt.view.order) {
     case 6: return launch_table_order<6>(dt, d_x, d_res, n, stream);
     case 8: return launch_table_order<8>(dt, d_x, d_res, n, stream);

@@ -4,20 +4,30 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C1..C5] [--points P]
   torchrun --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...      (one rank per GPU, NCCL only for the barrier)
 
-A "step" is one pass of the hot path over the whole batch of synthetic uniform points of the workload
-(default C3 = BASELINE.json configs[2]: 3D order 8 smooth function, 1e9 points per GPU, the configuration the
-north_star target "1e10 evals/s for a 3D order-8 tree on one B200" is quoted on).  Rank 0 prints ONE JSON line.
+A "step" is one pass of the hot path over the whole batch of synthetic uniform points of the workload.  Rank 0 prints
+ONE JSON line.  The headline workload is C3 = BASELINE.json configs[2] (3D order 8 smooth function, 1e9 points per GPU,
+the configuration the north_star target "1e10 evals/s for a 3D order-8 tree on one B200" is quoted on).  Without
+--workload the line also carries `workloads`: short runs of the other BASELINE.json configurations (C1, C2, C4, C5 at
+N=1; at every N the 8e9-point strong-scaling form of C5), each with its own clocks, roofline, cpu_baseline and parity.
 
   value     whole-job evals/s, points and results resident in HBM, CUDA-event timed on the launching stream
   e2e       the same through the reference-facing C ABI call baobzi_eval_multi with HOST (pinned) buffers:
-            H2D of the points and D2H of the results inside the timed region
-  roofline  for the dominant kernel, from per-launch CUDA events inside the timed region (baobzi_profile_*)
+            H2D of the points and D2H of the results inside the timed region; e2e.pageable = the same with plain
+            (malloc / numpy) memory, which is what an unmodified caller of the reference hands over; e2e.all_gpus =
+            one process, one call, every visible GPU (baobzi_set_host_devices)
+  roofline  per stage (sort: HBM bytes it must move; evaluation: flops or bytes, whichever binds) from per-launch
+            CUDA events inside the timed region (baobzi_profile_*); the top-level object is the dominant stage
+  parity    the TIMED output of this run (first `points` results of the device-resident batch) against the unmodified
+            reference (oracle/_ref, BAOBZI_ARCH=avx2) on the same saved tree and the same points: max ulp, node-index
+            and NaN mismatches -- measured, not quoted
   cpu_baseline  the reference's CPU path (oracle/_ref when built, else the oracle port) on a bounded sample
   --impl reference  times only that CPU path, on all host cores, and prints the same line shape
 """
 import argparse
 import ctypes as C
+import glob
 import json
+import math
 import os
 import subprocess
 import sys
@@ -43,7 +53,11 @@ WORKLOADS = {
     "C5": dict(desc="3D order 12, testfun_3d tol 1e-12", func="bench_fun_3d", dim=3, order=12, tol=1e-12,
                center=[1.5, 3.0, 1.5], hl=[1.0, 1.0, 1.0], data=None, points=1_000_000_000),
 }
+REF_FUNC = {"bench_fun_1d": "testfun_1d", "bench_fun_2d": "testfun_2d", "bench_fun_3d": "testfun_3d",
+            "bench_fun_2d_osc": "testfun_2d_osc"}
 METRIC = "FP64 evals/sec for baobzi_eval_multi"
+C5_TOTAL_POINTS = 8_000_000_000        # BASELINE.json configs[4]: 8e9 points sharded over 1/2/4/8 GPUs
+MIN_TIMED_SECONDS = 1.2                # extra workloads: long enough for >= 10 clock samples and stable clocks
 
 
 def flops_per_eval(dim, o):
@@ -58,6 +72,10 @@ def bytes_per_eval(dim):
     return 8 * (dim + 1)
 
 
+def sort_bytes_per_point(dim):
+    return 8 * dim + 4                 # the sort must read every point once and write one 4-byte slot index
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -65,27 +83,41 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def ncu_traffic(stage, points_per_launch):
-    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` summary (profiles/), scaled
-    to this run's points per launch; None when there is no capture of that kernel."""
-    import glob
-    pat = {"eval_grouped": "*_k4_ncu_summary.json", "sort": "*_sort_fused_ncu_summary.json"}.get(stage)
-    if not pat:
+def git_head():
+    try:
+        return subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], stdout=subprocess.PIPE,
+                              stderr=subprocess.DEVNULL, text=True).stdout.strip() or None
+    except Exception:
         return None
+
+
+def ncu_traffic(stage, dim, points_per_launch):
+    """DRAM bytes per launch of a kernel from the newest committed `ncu --set full` summary under profiles/, scaled to
+    this run's points per launch.  Returns (bytes or None, provenance string): the summary carries a `_meta` record
+    (git hash of the build that was profiled, points per profiled launch) written by scripts/ncu_summary.py."""
+    pat = {("eval_grouped", 3): "*_k4_ncu_summary.json", ("eval_grouped", 2): "*_eval2d_ncu_summary.json",
+           ("sort", 3): "*_sort_fused_ncu_summary.json", ("eval_direct", 1): "*_eval1d_ncu_summary.json"}.get((stage, dim))
+    if not pat:
+        return None, None
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", pat)))
     if not files:
-        return None
+        return None, None
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
     try:
-        rec = json.load(open(files[-1]))[0]
+        recs = json.load(open(files[-1]))
+        meta = next((r["_meta"] for r in recs if "_meta" in r), None)
+        rec = next(r for r in recs if "dram__bytes_read.sum" in r)
         tot = 0.0
         for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
             v, u = rec[k].split()
             tot += float(v) * unit[u]
-        captured_points = 33554432 / 4.0  # scripts/gpu_round.sh: 32 Mi points = 4 chunks of 2048 points per leaf
-        return tot * points_per_launch / captured_points
+        if meta and meta.get("points_per_launch"):
+            captured, src = float(meta["points_per_launch"]), "git %s" % meta.get("git")
+        else:  # round-1 captures (scripts/gpu_round.sh of commit 075c245: 32 Mi points = 4 launches)
+            captured, src = 33554432 / 4.0, "git 075c245 (round 1)"
+        return tot * points_per_launch / captured, "%s, %s, scaled by points per launch" % (os.path.basename(files[-1]), src)
     except Exception:
-        return None
+        return None, None
 
 
 def measured_peaks():
@@ -98,66 +130,102 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock, power and throttle reasons sampled DURING timed regions: NVML polled every 10 ms from a thread
+    (nvidia-smi -lms 50 as the fallback).  One sampler serves several regions: summary(t0, t1) picks its samples."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown"}
 
-    def __init__(self, gpu_index):
-        self.idx, self.proc, self.lines = gpu_index, None, []
+    def __init__(self, torch_device):
+        self.samples, self.stop_flag, self.thread, self.proc, self.how = [], False, None, None, None
+        self.max_mhz = None
+        self.dev = torch_device
 
     def start(self):
-        """Start sampling (nvidia-smi needs a moment to come up, so call this before the warm-up steps)."""
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            h = None
+            try:
+                uuid = str(torch.cuda.get_device_properties(self.dev).uuid)
+                h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid).encode() if not uuid.startswith("GPU-") else uuid.encode())
+            except Exception:
+                h = pynvml.nvmlDeviceGetHandleByIndex(self.dev.index or 0)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+
+            def poll():
+                while not self.stop_flag:
+                    try:
+                        mhz = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+                        pw = pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0
+                        rs = int(get_reasons(h))
+                        self.samples.append((time.perf_counter(), float(mhz), pw, rs))
+                    except Exception:
+                        pass
+                    time.sleep(0.01)
+            self.thread = threading.Thread(target=poll, daemon=True)
+            self.thread.start()
+            self.how = "nvml, 10 ms"
+            return
+        except Exception:
+            pass
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        bits = [0x8, 0x40, 0x20, 0x4]
+
         def reader():
             for ln in self.proc.stdout:
-                self.lines.append((time.perf_counter(), ln))
+                f = [t.strip() for t in ln.split(",")]
+                try:
+                    rs = sum(b for b, v in zip(bits, f[3:7]) if v.lower().startswith("active"))
+                    self.samples.append((time.perf_counter(), float(f[0]), float(f[2]), rs))
+                    self.max_mhz = float(f[1])
+                except (ValueError, IndexError):
+                    continue
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.dev.index or 0), "--query-gpu=" + q,
                                           "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=reader, daemon=True)
             self.thread.start()
+            self.how = "nvidia-smi, 50 ms"
         except Exception:
             self.proc = None
 
-    def stop(self, t_begin, t_end):
-        """Summarise the samples that arrived inside the timed region [t_begin, t_end] (perf_counter times)."""
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        self.thread.join(timeout=2)
-        sm, mx, pw, reasons = [], [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        inside = [ln for (ts, ln) in self.lines if t_begin <= ts <= t_end + 0.06]
-        for ln in inside:
-            f = [t.strip() for t in ln.split(",")]
-            if len(f) < 7:
-                continue
-            try:
-                sm.append(float(f[0]))
-                mx.append(float(f[1]))
-                pw.append(float(f[2]))
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples inside the timed region"],
-                    "samples": 0, "samples_total": len(self.lines)}
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
-                "samples": len(sm), "power_w_max": max(pw)}
+    def summary(self, t_begin, t_end):
+        inside = [s for s in list(self.samples) if t_begin <= s[0] <= t_end]
+        if not inside:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["no samples inside the timed region"],
+                    "samples": 0, "sampler": self.how}
+        mask = 0
+        for s in inside:
+            mask |= s[3]
+        return {"sm_mhz": float(np.median([s[1] for s in inside])), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(n for b, n in self.REASONS.items() if mask & b), "samples": len(inside),
+                "power_w_max": max(s[2] for s in inside), "sampler": self.how}
+
+    def stop(self):
+        self.stop_flag = True
+        if self.proc:
+            self.proc.terminate()
 
 
 # ------------------------------------------------------------------------------------------------ CPU side
-def cpu_reference_rate(tree_path, cfg, threads, pts_per_thread, repeats=1):
+def sample_points(cfg, n, seed=1):
+    rng = np.random.default_rng(seed)
+    return np.array(cfg["center"]) + (rng.random((n, cfg["dim"])) * 2 - 1) * np.array(cfg["hl"])
+
+
+def cpu_reference_rate(tree_path, cfg, threads, pts_per_thread, repeats=2):
     """The reference's CPU-dispatched baobzi_eval_multi (oracle/_ref, unmodified reference) -- or the oracle port
     when the reference could not be built -- on `threads` contiguous slices from `threads` host threads (legal:
-    eval is const in the reference).  Returns (evals/s, info dict).  Only executed for cpu_baseline / --impl reference."""
+    eval is const in the reference).  Best of `repeats` after one untimed pass.  Returns (evals/s, info dict).
+    Only executed for cpu_baseline / --impl reference."""
     from oracle import ref
-    dim = cfg["dim"]
-    rng = np.random.default_rng(1)
     n = threads * pts_per_thread
-    x = np.array(cfg["center"]) + (rng.random((n, dim)) * 2 - 1) * np.array(cfg["hl"])
+    x = sample_points(cfg, n)
     res = np.empty(n)
     if ref.have_ref():
         kind = "reference"
@@ -180,31 +248,68 @@ def cpu_reference_rate(tree_path, cfg, threads, pts_per_thread, repeats=1):
             xs, rs = x[s], res[s]
             lib.oracle_eval_multi(t.ptr, ref.dptr(xs), ref.dptr(rs), pts_per_thread, ref.ARITH_AVX2)
 
-    best = None
-    for _ in range(repeats + 1):  # first pass warms caches / page-faults the buffers
+    times = []
+    for it in range(repeats + 1):  # first pass warms caches / page-faults the buffers
         th = [threading.Thread(target=work, args=(k,)) for k in range(threads)]
         t0 = time.perf_counter()
         [t_.start() for t_ in th]
         [t_.join() for t_ in th]
-        dt = time.perf_counter() - t0
-        best = dt if best is None or _ == 0 else min(best, dt)
-        if _ == 0:
-            best = None
+        if it:
+            times.append(time.perf_counter() - t0)
+    best = min(times)
     isa = "n/a"
     try:
         flags = open("/proc/cpuinfo").read()
         isa = "avx512" if " avx512f" in flags else ("avx2" if " avx2" in flags else "generic")
     except OSError:
         pass
-    info = {"kind": kind, "cores": threads, "sample": "%d threads x %d uniform points, same saved tree, %s dispatch"
-            % (threads, pts_per_thread, isa), "seconds": best}
+    info = {"kind": kind, "cores": threads, "sample": "%d threads x %d uniform points, same saved tree, %s dispatch, best of %d"
+            % (threads, pts_per_thread, isa, repeats), "seconds": best}
     return n / best, info
 
 
-def cpu_sample_size(cfg, threads):
-    # ~10-30 s of CPU work in total: the reference runs ~2e6 (3D o8) .. 1e8 (1D) evals/s per core
+def cpu_sample_size(cfg, seconds):
+    """points per thread for about `seconds` of CPU work per pass: the reference runs ~1.5e6 (3D o8) .. 8e7 (1D)
+    evals/s per core"""
     per_core_rate = {1: 8e7, 2: 5e6, 3: 1.5e6}[cfg["dim"]] * (8.0 / cfg["order"]) ** cfg["dim"]
-    return int(max(2e5, min(2e7, per_core_rate * 0.6)))
+    return int(max(1e5, min(2e7, per_core_rate * seconds)))
+
+
+def cpu_baseline(tree_path, cfg, seconds):
+    threads = host_cores()
+    r1, _ = cpu_reference_rate(tree_path, cfg, 1, cpu_sample_size(cfg, seconds))
+    rT, infoT = cpu_reference_rate(tree_path, cfg, threads, cpu_sample_size(cfg, seconds))
+    return {"value": rT, "unit": "evals/s", "cores": threads, "kind": infoT["kind"], "sample": infoT["sample"],
+            "single_thread_value": r1}
+
+
+def parity_block(tree_path, cfg, xs, got, got_idx):
+    """`got` / `got_idx` = the GPU's values and node indices for the points xs: compared with the unmodified reference
+    pinned to its AVX2+FMA build (the flavour the kernels implement), else with the oracle port's AVX2 arithmetic."""
+    from oracle import ref
+    if ref.have_ref():
+        want = ref.ref_restore(tree_path, arch="avx2").eval_multi(xs)
+        ref.set_arch(None)
+        against = "reference (oracle/_ref, BAOBZI_ARCH=avx2)"
+    else:
+        want = ref.OracleTree(tree_path).eval_multi(xs, ref.ARITH_AVX2)
+        against = "oracle port (AVX2 arithmetic)"
+    if ref.have_ref() and os.path.exists(ref.REFIDX_SO):
+        widx = ref.ref_node_indices(tree_path, xs, cfg["dim"])[0]
+    else:
+        widx = ref.OracleTree(tree_path).node_indices(xs)
+    d = ref.ulp_diff(got, want)
+    finite = np.isfinite(d)
+    return {"points": int(len(xs)), "against": against,
+            "max_ulp": float(d[finite].max()) if finite.any() else 0.0,
+            "nan_mismatch": int((~finite).sum()), "nan_results": int(np.isnan(got).sum()),
+            "node_idx_mismatch": int((np.asarray(got_idx) != widx).sum())}
+
+
+def tree_stats_from_file(path):
+    from oracle import ref
+    t = ref.OracleTree(path)
+    return {"nodes": int(t.n_nodes), "leaves": int(t.n_leaves), "grid_cells": int(t.n_bins), "coeff_bytes": int(8 * t.n_coeffs)}
 
 
 def fit_tree_to_file(cfg, path):
@@ -218,24 +323,25 @@ def fit_tree_to_file(cfg, path):
     return b
 
 
-def run_reference_arm(args, cfg, rank, world):
+def run_reference_arm(args, cfg, tag, rank, world):
     """--impl reference: rank 0 alone times the reference's CPU path with every host core it can use."""
     if rank != 0:
         return
     from oracle import ref
     threads = host_cores()
-    pts = cpu_sample_size(cfg, threads)
+    pts = cpu_sample_size(cfg, 1.0)
     with tempfile.TemporaryDirectory() as td:
         path = os.path.join(td, "tree.baobzi")
         if ref.have_ref():  # the reference fits its own tree through its own baobzi_init
             subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"], check=True, stdout=subprocess.DEVNULL)
-            name = {"bench_fun_1d": "testfun_1d", "bench_fun_2d": "testfun_2d", "bench_fun_3d": "testfun_3d",
-                    "bench_fun_2d_osc": "testfun_2d_osc"}[cfg["func"]]
-            inp = ref.make_input(name, cfg["dim"], cfg["order"], cfg["tol"], data=cfg["data"])
+            inp = ref.make_input(REF_FUNC[cfg["func"]], cfg["dim"], cfg["order"], cfg["tol"], data=cfg["data"])
             ref.ref_init(inp, cfg["center"], cfg["hl"]).save(path)
+            fitted_by = "the reference's own baobzi_init"
         else:
             import baobzi_b200  # noqa: F401  (fitting needs our library; evaluation below is the oracle port)
             fit_tree_to_file(cfg, path).free()
+            fitted_by = "baobzi_b200 host fitter (reference not built)"
+        tree = tree_stats_from_file(path)
         rates = []
         for step in range(args.warmup + args.steps):
             r, info = cpu_reference_rate(path, cfg, threads, pts, repeats=1)
@@ -245,7 +351,8 @@ def run_reference_arm(args, cfg, rank, world):
     line = {"metric": METRIC, "value": value, "unit": "evals/s", "impl": "reference", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * threads * pts / value,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "%s: %s" % (args.workload, cfg["desc"]), "points_per_step": threads * pts,
+            "config": {"workload": "%s: %s" % (tag, cfg["desc"]), "points_per_step": threads * pts,
+                       "tree": dict(tree, fitted_by=fitted_by),
                        "timing": "host wall clock; bounded sample of the workload"},
             "cpu_baseline": {"value": value, "unit": "evals/s", "cores": info["cores"], "kind": info["kind"],
                              "sample": info["sample"]},
@@ -255,34 +362,99 @@ def run_reference_arm(args, cfg, rank, world):
 
 
 # ------------------------------------------------------------------------------------------------ GPU side
-def run_ours(args, cfg, rank, world, local_rank):
-    import torch
-    import baobzi_b200
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device -- the evaluation path exists only as sm_100a kernels")
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    if world > 1:
-        import torch.distributed as dist
-        # NCCL prints its version banner on stdout at the first collective: keep stdout for the ONE JSON line
-        sys.stdout.flush()
-        saved_stdout = os.dup(1)
-        os.dup2(2, 1)
-        try:
-            dist.init_process_group("nccl", device_id=dev)
-            warm = torch.zeros(1, device=dev)
-            dist.all_reduce(warm)
-            torch.cuda.synchronize()
-        finally:
-            os.dup2(saved_stdout, 1)
-            os.close(saved_stdout)
-    if not os.path.exists(baobzi_b200.library_path()):
-        baobzi_b200.build()
-    dim, order = cfg["dim"], cfg["order"]
-    n = int(args.points or cfg["points"])
+class Ctx:
+    """Per-process state shared by the workloads of one bench run."""
 
-    tmp = tempfile.TemporaryDirectory()
-    tree_path = os.path.join(tmp.name, "tree_rank%d.baobzi" % rank)
+    def __init__(self, args, rank, world, local_rank):
+        import torch
+        self.args, self.rank, self.world = args, rank, world
+        self.torch = torch
+        self.dev = torch.device("cuda", local_rank)
+        self.stream = torch.cuda.current_stream(self.dev)
+        self.sampler = ClockSampler(self.dev)
+        self.tmp = tempfile.TemporaryDirectory()
+        self.hbm_peak, self.hbm_src = measured_peaks()
+        self.fp64_peak = None
+
+    def barrier(self):
+        if self.world > 1:
+            self.torch.distributed.barrier()
+        self.torch.cuda.synchronize(self.dev)
+
+    def max_over_ranks(self, v):
+        if self.world == 1:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device=self.dev)
+        self.torch.distributed.all_reduce(t, op=self.torch.distributed.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(self, v):
+        if self.world == 1:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.int64, device=self.dev)
+        self.torch.distributed.all_reduce(t)
+        return int(t.item())
+
+    def uniform_points(self, cfg, n, seed, out=None):
+        """x_j = hl_j (2u - 1) + c_j (baobzi_timing.c:98-100), generated on the device in slabs"""
+        torch = self.torch
+        g = torch.Generator(device=self.dev).manual_seed(seed)
+        x = out if out is not None else torch.empty((n, cfg["dim"]), dtype=torch.float64, device=self.dev)
+        c = torch.tensor(cfg["center"], dtype=torch.float64, device=self.dev)
+        h = torch.tensor(cfg["hl"], dtype=torch.float64, device=self.dev)
+        slab = 1 << 24
+        for o in range(0, n, slab):
+            v = x[o:o + slab]
+            v.uniform_(0.0, 1.0, generator=g)
+            v.mul_(2.0).sub_(1.0).mul_(h).add_(c)
+        return x
+
+
+def stage_rooflines(ctx, cfg, stages, steps):
+    """One roofline record per profiled stage, each against ITS bound: the sort moves bytes (8 DIM + 4 per point) and
+    does no flops; an evaluation stage is measured against the FP64 pipe or HBM, whichever fraction is larger."""
+    dim, order = cfg["dim"], cfg["order"]
+    out = {}
+    total_ms = sum(v[0] for v in stages.values())
+    for name, (k_ms, k_launches, k_points) in stages.items():
+        if not k_launches:
+            continue
+        per_launch_s = k_ms * 1e-3 / k_launches
+        pts = k_points / k_launches
+        rec = {"kernel": name, "avg_launch_ms": per_launch_s * 1e3, "points_per_launch": pts, "launches": k_launches,
+               "share_of_step": k_ms / total_ms if total_ms else None, "ms_per_step": k_ms / steps}
+        if name in ("sort", "scan", "scatter"):
+            gb = sort_bytes_per_point(dim) * pts / per_launch_s / 1e9
+            rec.update({"bound": "hbm", "achieved": gb, "peak": ctx.hbm_peak, "unit": "GB/s", "frac": gb / ctx.hbm_peak,
+                        "peak_source": ctx.hbm_src, "algorithmic_bytes_per_point": sort_bytes_per_point(dim)})
+        else:
+            tf = flops_per_eval(dim, order) * pts / per_launch_s / 1e12
+            gb = bytes_per_eval(dim) * pts / per_launch_s / 1e9
+            f_fp = tf / ctx.fp64_peak if ctx.fp64_peak else 0.0
+            f_hbm = gb / ctx.hbm_peak
+            fp64_bound = dim == 3 or (dim == 2 and f_fp > f_hbm)
+            rec.update({"bound": "fp64" if fp64_bound else "hbm", "achieved": tf if fp64_bound else gb,
+                        "peak": ctx.fp64_peak if fp64_bound else ctx.hbm_peak, "unit": "TFLOP/s" if fp64_bound else "GB/s",
+                        "frac": f_fp if fp64_bound else f_hbm,
+                        "peak_source": "DFMA microbenchmark baobzi_b200_fp64_peak, measured in this run" if fp64_bound else ctx.hbm_src,
+                        "algorithmic_flops_per_eval": flops_per_eval(dim, order),
+                        "algorithmic_bytes_per_eval": bytes_per_eval(dim),
+                        "hbm_gbs_achieved": gb, "hbm_frac": f_hbm, "fp64_tflops_achieved": tf, "fp64_frac": f_fp})
+        traffic, src = ncu_traffic(name, dim, pts)
+        rec["traffic"] = traffic
+        if src:
+            rec["traffic_source"] = src
+        out[name] = rec
+    return out
+
+
+def run_workload(ctx, tag, cfg, n, steps, warmup, headline, cpu_seconds):
+    """Fit, generate, warm up, time `steps` steps (the extra workloads: at least MIN_TIMED_SECONDS), and collect
+    everything a bench record needs.  Returns the record (every rank; rank 0's is printed)."""
+    import baobzi_b200
+    torch, args = ctx.torch, ctx.args
+    dim, order = cfg["dim"], cfg["order"]
+    tree_path = os.path.join(ctx.tmp.name, "tree_%s_rank%d.baobzi" % (tag, ctx.rank))
     t0 = time.perf_counter()
     b = fit_tree_to_file(cfg, tree_path)      # host fit (callback on the host) + flatten + upload to this GPU
     fit_s = time.perf_counter() - t0
@@ -290,155 +462,289 @@ def run_ours(args, cfg, rank, world, local_rank):
         b.set_mode(args.mode, args.chunk)
     elif args.chunk:
         b.set_mode("auto", args.chunk)
+    if ctx.fp64_peak is None:
+        fp = C.c_double(0.0)
+        b._lib.baobzi_b200_fp64_peak(C.byref(fp))
+        ctx.fp64_peak = fp.value
 
-    # synthetic uniform points x_j = hl_j (2u - 1) + c_j (baobzi_timing.c:98-100), generated on the device,
-    # seeded per rank; generated in slabs so the temporaries stay small
-    g = torch.Generator(device=dev).manual_seed(1 + rank)
-    x = torch.empty((n, dim), dtype=torch.float64, device=dev)
-    c = torch.tensor(cfg["center"], dtype=torch.float64, device=dev)
-    h = torch.tensor(cfg["hl"], dtype=torch.float64, device=dev)
-    slab = 1 << 24
-    for o in range(0, n, slab):
-        v = x[o:o + slab]
-        v.uniform_(0.0, 1.0, generator=g)
-        v.mul_(2.0).sub_(1.0).mul_(h).add_(c)
-    res = torch.empty(n, dtype=torch.float64, device=dev)
-    stream = torch.cuda.current_stream(dev)
+    x = ctx.uniform_points(cfg, n, 1 + ctx.rank)
+    res = torch.empty(n, dtype=torch.float64, device=ctx.dev)
+    stream = ctx.stream
 
     def step():
         rc = b._lib.baobzi_eval_multi_device(b.ptr, x.data_ptr(), res.data_ptr(), n, stream.cuda_stream)
         if rc != 0:
             raise RuntimeError("baobzi_eval_multi_device: CUDA error %d" % rc)
 
-    def barrier():
-        if world > 1:
-            torch.distributed.barrier()
-        torch.cuda.synchronize(dev)
-
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step()
-    barrier()
+    ctx.barrier()
+    if not headline:  # size the timed region: at least MIN_TIMED_SECONDS (clock samples), at least `steps` steps
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(3):
+            step()
+        e1.record(stream)
+        torch.cuda.synchronize(ctx.dev)
+        est = max(e0.elapsed_time(e1) / 3 * 1e-3, 1e-6)
+        steps = int(min(200000, max(steps, math.ceil(MIN_TIMED_SECONDS / est))))
     launches0 = b.launches
-    if not args.no_profile:
-        b.profile_begin()                      # per-launch CUDA events inside the timed region (roofline)
+    profile = not args.no_profile
+    # per-launch events cost a few microseconds each: microsecond-scale steps are profiled in a separate short pass
+    profile_inline = profile and (headline or steps <= 2000)
+    if profile_inline:
+        b.profile_begin()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_begin = time.perf_counter()
     ev0.record(stream)
-    for _ in range(args.steps):
+    for _ in range(steps):
         step()
     ev1.record(stream)
-    barrier()
+    ctx.barrier()
     t_end = time.perf_counter()
     ms = ev0.elapsed_time(ev1)
-    stages = b.profile_end() if not args.no_profile else {}
+    stages = b.profile_end() if profile_inline else {}
     launches = b.launches - launches0
-    clocks = sampler.stop(t_begin, t_end)
-    if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-        ms = float(t.item())
-        lt = torch.tensor([launches], dtype=torch.int64, device=dev)
-        torch.distributed.all_reduce(lt)
-        launches = int(lt.item())
-    value = world * n * args.steps / (ms * 1e-3)
-    nan_count = int(torch.isnan(res[: min(n, 1 << 22)]).sum().item())
+    clocks = ctx.sampler.summary(t_begin, t_end)
+    profiled_steps = steps
+    if profile and not profile_inline:
+        profiled_steps = 200
+        b.profile_begin()
+        for _ in range(profiled_steps):
+            step()
+        stages = b.profile_end()
+    ms = ctx.max_over_ranks(ms)
+    launches = ctx.sum_over_ranks(launches)
+    value = ctx.world * n * steps / (ms * 1e-3)
 
-    # ---- e2e: the reference-facing call with HOST buffers (pinned), copies inside the timed region
-    e2e = None
-    if not args.no_e2e:
-        import psutil
-        need = n * (dim + 1) * 8
-        avail = psutil.virtual_memory().available / world  # every rank pins its own buffers at the same time
-        n_e = n if avail > 3 * need else max(1 << 20, int(avail / 3 / ((dim + 1) * 8)))
-        n_e = min(n_e, 2**31 - 1)
-        xh = torch.empty((n_e, dim), dtype=torch.float64, pin_memory=True)
-        yh = torch.empty(n_e, dtype=torch.float64, pin_memory=True)
-        xh.copy_(x[:n_e])
-        torch.cuda.synchronize(dev)
-        e_steps = max(1, min(args.steps, 3))
-        b._lib.baobzi_eval_multi(b.ptr, xh.data_ptr(), yh.data_ptr(), n_e)  # warm-up (allocates the pipeline slots)
-        barrier()
+    rec = {"value": value, "unit": "evals/s", "steps": steps, "warmup": warmup, "ms_per_step": ms / steps,
+           "points_per_gpu": n, "gpu_launches": launches, "clocks": clocks, "tree": b.tree_info(), "fit_seconds": fit_s}
+
+    # ---- parity of the TIMED output: first m results of the device-resident batch against the reference
+    parity = None
+    if ctx.rank == 0 and not args.no_parity:
+        m = min(n, 200_000 if dim < 3 else 100_000)
+        xs = x[:m].cpu().numpy()
+        got = res[:m].cpu().numpy()
+        got_idx = b.node_index(x[:m]).cpu().numpy()
+        parity = parity_block(tree_path, cfg, xs, got, got_idx)
+    rec["parity"] = parity
+
+    # ---- e2e: the reference-facing call with HOST buffers, copies inside the timed region (headline only)
+    if headline and not args.no_e2e:
+        rec["e2e"] = measure_e2e(ctx, b, cfg, x, res, n)
+    if ctx.rank == 0:
+        roofs = stage_rooflines(ctx, cfg, stages, profiled_steps) if stages else {}
+        rec["stages"] = roofs
+        if roofs:
+            top = max(roofs.values(), key=lambda r: r["ms_per_step"])
+            roof = dict(top)
+            roof["stages_ms_per_step"] = {k: v["ms_per_step"] for k, v in roofs.items()}
+            if top["bound"] == "fp64" and clocks.get("sm_mhz") and clocks.get("sm_max_mhz"):
+                at_clock = ctx.fp64_peak * clocks["sm_mhz"] / clocks["sm_max_mhz"]
+                roof["peak_at_step_clock"] = at_clock
+                roof["frac_at_step_clock"] = top["achieved"] / at_clock if at_clock else None
+            # whole step against the same bound (sort included): what the user gets per point
+            if top["bound"] == "fp64":
+                roof["whole_step_frac"] = flops_per_eval(dim, order) * value / ctx.world / 1e12 / ctx.fp64_peak
+            else:
+                roof["whole_step_frac"] = bytes_per_eval(dim) * value / ctx.world / 1e9 / ctx.hbm_peak
+            rec["roofline"] = roof
+        else:
+            rec["roofline"] = None
+        rec["cpu_baseline"] = cpu_baseline(tree_path, cfg, cpu_seconds) if not args.no_cpu else None
+        if rec["cpu_baseline"]:
+            rec["vs_cpu_baseline"] = {"all_cores": value / rec["cpu_baseline"]["value"],
+                                      "one_core": value / rec["cpu_baseline"]["single_thread_value"]}
+    del x, res
+    b.free()
+    torch.cuda.empty_cache()
+    return rec
+
+
+def measure_e2e(ctx, b, cfg, x, res, n):
+    """baobzi_eval_multi with HOST pointers: (1) pinned buffers (the contract's e2e), (2) pageable buffers -- what an
+    unmodified caller of the reference passes, (3) one call spread over every visible GPU (single process only)."""
+    import psutil
+    torch = ctx.torch
+    dim = cfg["dim"]
+    need = n * (dim + 1) * 8
+    avail = psutil.virtual_memory().available / ctx.world  # every rank pins its own buffers at the same time
+    n_e = n if avail > 3 * need else max(1 << 20, int(avail / 3 / ((dim + 1) * 8)))
+    n_e = min(n_e, 2**31 - 1)
+    xh = torch.empty((n_e, dim), dtype=torch.float64, pin_memory=True)
+    yh = torch.empty(n_e, dtype=torch.float64, pin_memory=True)
+    xh.copy_(x[:n_e])
+    torch.cuda.synchronize(ctx.dev)
+    e_steps = max(1, min(ctx.args.steps, 3))
+
+    def timed(xp, yp, count, reps):
+        b._lib.baobzi_eval_multi(b.ptr, xp, yp, count)  # warm-up (allocates the workers' buffers, touches the pages)
+        ctx.barrier()
         t0 = time.perf_counter()
-        for _ in range(e_steps):
-            b._lib.baobzi_eval_multi(b.ptr, xh.data_ptr(), yh.data_ptr(), n_e)
-        torch.cuda.synchronize(dev)
-        dt = time.perf_counter() - t0
-        if world > 1:
-            t = torch.tensor([dt], dtype=torch.float64, device=dev)
-            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-            dt = float(t.item())
-        same = bool(torch.equal(torch.nan_to_num(yh[:1 << 20]), torch.nan_to_num(res[:1 << 20].cpu())))
-        e2e = {"value": world * n_e * e_steps / dt, "unit": "evals/s", "h2d_bytes_per_step": n_e * dim * 8,
-               "d2h_bytes_per_step": n_e * 8, "points_per_step": n_e, "steps": e_steps,
-               "matches_device_path": same, "timing": "host wall clock around baobzi_eval_multi, pinned host buffers"}
-        del xh, yh
+        for _ in range(reps):
+            b._lib.baobzi_eval_multi(b.ptr, xp, yp, count)
+        torch.cuda.synchronize(ctx.dev)
+        return ctx.max_over_ranks(time.perf_counter() - t0)
 
+    dt = timed(xh.data_ptr(), yh.data_ptr(), n_e, e_steps)
+    ref_bits = res[:1 << 20].cpu()
+    same = bool(torch.equal(torch.nan_to_num(yh[:1 << 20]), torch.nan_to_num(ref_bits)))
+    e2e = {"value": ctx.world * n_e * e_steps / dt, "unit": "evals/s", "h2d_bytes_per_step": n_e * dim * 8,
+           "d2h_bytes_per_step": n_e * 8, "points_per_step": n_e, "steps": e_steps,
+           "matches_device_path": same, "timing": "host wall clock around baobzi_eval_multi, pinned host buffers"}
+    # (2) pageable: a bounded slice (page-faulting and copying 32 GB of numpy memory takes tens of seconds)
+    n_p = int(min(n_e, 200_000_000))
+    xp = np.empty((n_p, dim))
+    yp = np.empty(n_p)
+    xp[:] = xh[:n_p].numpy()
+    dtp = timed(xp.ctypes.data, yp.ctypes.data, n_p, 2)
+    e2e["pageable"] = {"value": ctx.world * n_p * 2 / dtp, "unit": "evals/s", "points_per_step": n_p, "steps": 2,
+                       "matches_device_path": bool(np.array_equal(np.nan_to_num(yp[:1 << 20]), np.nan_to_num(ref_bits.numpy()))),
+                       "buffers": "numpy (malloc) memory, staged through the library's pinned ring by host threads"}
+    del xp, yp
+    # (3) every visible GPU from ONE call (only meaningful in a single-process run)
+    n_vis = torch.cuda.device_count()
+    if ctx.world == 1 and n_vis > 1:
+        b.set_host_devices(0)
+        dta = timed(xh.data_ptr(), yh.data_ptr(), n_e, e_steps)
+        b.set_host_devices(1)
+        e2e["all_gpus"] = {"value": n_e * e_steps / dta, "unit": "evals/s", "devices": n_vis, "points_per_step": n_e,
+                           "matches_device_path": bool(torch.equal(torch.nan_to_num(yh[:1 << 20]), torch.nan_to_num(ref_bits)))}
+    else:
+        e2e["all_gpus"] = {"value": None, "devices": n_vis, "note": "one visible GPU" if n_vis == 1 else
+                           "multi-process run: every rank drives its own GPU"}
+    del xh, yh
+    return e2e
+
+
+def run_c5_total(ctx, cfg, warmup):
+    """BASELINE.json configs[4] as stated: 8e9 points in total, sharded by contiguous range over the ranks (strong
+    scaling).  Each rank evaluates its share in slabs of <= 1e9 points regenerated on the device (192 GB of points do
+    not fit beside the results); only the evaluations are timed (CUDA events per slab), generation is not."""
+    import baobzi_b200  # noqa: F401
+    torch = ctx.torch
+    dim = cfg["dim"]
+    share = C5_TOTAL_POINTS // ctx.world
+    slab = min(share, 1_000_000_000)
+    tree_path = os.path.join(ctx.tmp.name, "tree_c5t_rank%d.baobzi" % ctx.rank)
+    b = fit_tree_to_file(cfg, tree_path)
+    x = torch.empty((slab, dim), dtype=torch.float64, device=ctx.dev)
+    res = torch.empty(slab, dtype=torch.float64, device=ctx.dev)
+    stream = ctx.stream
+
+    def ev(m):
+        rc = b._lib.baobzi_eval_multi_device(b.ptr, x.data_ptr(), res.data_ptr(), m, stream.cuda_stream)
+        if rc != 0:
+            raise RuntimeError("baobzi_eval_multi_device: CUDA error %d" % rc)
+
+    ctx.uniform_points(cfg, slab, 1000 + ctx.rank, out=x)
+    for _ in range(warmup):
+        ev(min(slab, 1 << 26))
+    ctx.barrier()
+    total_ms, done, k, checksum = 0.0, 0, 0, 0
+    t_begin = time.perf_counter()
+    launches0 = b.launches
+    while done < share:
+        m = min(slab, share - done)
+        if k:
+            ctx.uniform_points(cfg, slab, 1000 + ctx.rank + 7919 * k, out=x)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        ev(m)
+        e1.record(stream)
+        torch.cuda.synchronize(ctx.dev)
+        total_ms += e0.elapsed_time(e1)
+        checksum ^= int(res[:m:9973].view(torch.int64).sum().item())
+        done += m
+        k += 1
+    ctx.barrier()
+    t_end = time.perf_counter()
+    launches = ctx.sum_over_ranks(b.launches - launches0)
+    total_ms = ctx.max_over_ranks(total_ms)
+    rec = {"value": C5_TOTAL_POINTS / (total_ms * 1e-3), "unit": "evals/s", "points_total": C5_TOTAL_POINTS,
+           "points_per_gpu": share, "slabs_per_gpu": k, "eval_ms_total": total_ms, "scaling": "strong",
+           "gpu_launches": launches, "clocks": ctx.sampler.summary(t_begin, t_end), "tree": b.tree_info(),
+           "timing": "sum of CUDA-event spans around the %d evaluations of each rank (max over ranks); the on-device "
+                     "regeneration of the points between slabs is not timed" % k,
+           "result_checksum_rank0": checksum}
+    del x, res
+    b.free()
+    torch.cuda.empty_cache()
+    return rec
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import baobzi_b200
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the evaluation path exists only as sm_100a kernels")
+    torch.cuda.set_device(local_rank)
+    ctx = Ctx(args, rank, world, local_rank)
     if world > 1:
-        barrier()
+        import torch.distributed as dist
+        # NCCL prints its version banner on stdout at the first collective: keep stdout for the ONE JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=ctx.dev)
+            warm = torch.zeros(1, device=ctx.dev)
+            dist.all_reduce(warm)
+            torch.cuda.synchronize()
+        finally:
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
+    if not os.path.exists(baobzi_b200.library_path()):
+        baobzi_b200.build()
+    ctx.sampler.start()
+
+    tag = args.workload or "C3"
+    cfg = WORKLOADS[tag]
+    if args.order and args.order != cfg["order"]:
+        cfg = dict(cfg, order=args.order, desc=cfg["desc"] + " [order overridden: %d]" % args.order)
+    if args.tol and args.tol != cfg["tol"]:
+        cfg = dict(cfg, tol=args.tol, desc=cfg["desc"] + " [tol overridden: %g]" % args.tol)
+    n = int(args.points or cfg["points"])
+    head = run_workload(ctx, tag, cfg, n, args.steps, args.warmup, True, cpu_seconds=1.5)
+
+    extra = {}
+    if not args.workload and not args.no_extra:
+        if world == 1:
+            for t2 in ("C1", "C2", "C4", "C5"):
+                c2 = WORKLOADS[t2]
+                extra[t2] = run_workload(ctx, t2, c2, int(c2["points"]), 3, 3, False, cpu_seconds=0.5)
+        extra["C5_8e9_sharded"] = run_c5_total(ctx, WORKLOADS["C5"], 3)
+
+    # the sustained FP64 rate (2 s of back-to-back DFMA): context for FP64-bound fractions measured inside long steps
+    fps = C.c_double(0.0)
+    if rank == 0 and cfg["dim"] > 1 and not args.no_profile:
+        lib = baobzi_b200.load_library()
+        lib.baobzi_b200_fp64_peak_sustained(C.byref(fps), C.c_double(2.0))
+    ctx.sampler.stop()
+    if world > 1:
+        ctx.barrier()
         torch.distributed.destroy_process_group()
     if rank != 0:
-        b.free()
         return
-    # ---- roofline of the dominant kernel
-    hbm_peak, hbm_src = measured_peaks()
-    fp = C.c_double(0.0)
-    b._lib.baobzi_b200_fp64_peak(C.byref(fp))
-    fps = C.c_double(0.0)   # the same DFMA kernel back to back for 2 s: what the pipe sustains under the board's power cap
-    if dim > 1 and not args.no_profile:
-        b._lib.baobzi_b200_fp64_peak_sustained(C.byref(fps), C.c_double(2.0))
-    roof = None
-    if stages:
-        name, (k_ms, k_launches, k_points) = max(stages.items(), key=lambda kv: kv[1][0])
-        total_ms = sum(v[0] for v in stages.values())
-        if k_launches:
-            per_launch_s = k_ms * 1e-3 / k_launches
-            pts_per_launch = k_points / k_launches
-            tf = flops_per_eval(dim, order) * pts_per_launch / per_launch_s / 1e12
-            gb = bytes_per_eval(dim) * pts_per_launch / per_launch_s / 1e9
-            fp64_bound = dim == 3 or (dim == 2 and tf / max(fp.value, 1e-9) > gb / hbm_peak)
-            roof = {"kernel": name, "bound": "fp64" if fp64_bound else "hbm",
-                    "achieved": tf if fp64_bound else gb, "peak": fp.value if fp64_bound else hbm_peak,
-                    "unit": "TFLOP/s" if fp64_bound else "GB/s",
-                    "frac": (tf / fp.value if fp.value else None) if fp64_bound else gb / hbm_peak,
-                    "traffic": ncu_traffic(name, pts_per_launch),
-                    "peak_source": "DFMA microbenchmark baobzi_b200_fp64_peak, measured in this run" if fp64_bound else hbm_src,
-                    "algorithmic_flops_per_eval": flops_per_eval(dim, order), "algorithmic_bytes_per_eval": bytes_per_eval(dim),
-                    "avg_launch_ms": per_launch_s * 1e3, "points_per_launch": pts_per_launch,
-                    "share_of_step": k_ms / total_ms if total_ms else None,
-                    "hbm_gbs_achieved": gb, "hbm_frac": gb / hbm_peak, "fp64_tflops_achieved": tf,
-                    "stages_ms_per_step": {k: v[0] / args.steps for k, v in stages.items() if v[1]}}
-            if fp64_bound and clocks and clocks.get("sm_mhz") and clocks.get("sm_max_mhz"):
-                # `peak` is the burst figure (boost clock); the step itself may run below it under sw_power_cap
-                at_clock = fp.value * clocks["sm_mhz"] / clocks["sm_max_mhz"]
-                roof["peak_at_step_clock"] = at_clock
-                roof["frac_at_step_clock"] = tf / at_clock if at_clock else None
-            if fp64_bound and fps.value:
-                roof["peak_sustained_2s"] = fps.value
-    # ---- CPU baseline on this box's host cores (bounded sample)
-    cpu = None
-    if not args.no_cpu:
-        threads = host_cores()
-        r1, info1 = cpu_reference_rate(tree_path, cfg, 1, cpu_sample_size(cfg, 1) // 2)
-        rT, infoT = cpu_reference_rate(tree_path, cfg, threads, cpu_sample_size(cfg, threads) // 2)
-        cpu = {"value": rT, "unit": "evals/s", "cores": threads, "kind": infoT["kind"], "sample": infoT["sample"],
-               "single_thread_value": r1}
-    line = {"metric": METRIC, "value": value, "unit": "evals/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+    dim = cfg["dim"]
+    roof = head.get("roofline")
+    if roof and fps.value and roof.get("bound") == "fp64":
+        roof["peak_sustained_2s"] = fps.value
+    line = {"metric": METRIC, "value": head["value"], "unit": "evals/s", "n_gpus": world, "steps": head["steps"],
+            "warmup": head["warmup"], "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "%s: %s" % (args.workload, cfg["desc"]), "points_per_gpu": n,
+            "config": {"workload": "%s: %s" % (tag, cfg["desc"]), "points_per_gpu": n,
                        "inputs": "uniform on the domain, device resident, %.1f GB per GPU (larger than L2, no flush needed)"
                                  % (n * (dim + 1) * 8 / 1e9),
                        "parallelism": "tree replicated, points sharded by contiguous range, no collective",
-                       "tree": {"nodes": int(b._lib.baobzi_launch_count(b.ptr) * 0 + 0) or None}, "fit_seconds": fit_s,
-                       "mode": args.mode or "auto", "nan_results_in_sample": nan_count,
-                       "parity": "bit-exact vs reference BAOBZI_ARCH=avx2 (tests/)"},
-            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
-            "fp64_peak_tflops_measured": fp.value}
-    line["config"].pop("tree")
+                       "tree": head["tree"], "fit_seconds": head["fit_seconds"], "mode": args.mode or "auto",
+                       "parity": head["parity"], "git": git_head()},
+            "e2e": head.get("e2e"), "gpu_launches": head["gpu_launches"], "clocks": head["clocks"], "roofline": roof,
+            "stages": head.get("stages"), "cpu_baseline": head.get("cpu_baseline"),
+            "vs_cpu_baseline": head.get("vs_cpu_baseline"), "fp64_peak_tflops_measured": ctx.fp64_peak,
+            "workloads": extra or None}
     print(json.dumps(line), flush=True)
-    b.free()
 
 
 def main():
@@ -447,13 +753,16 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="", choices=[""] + sorted(WORKLOADS),
+                    help="one workload only (default: C3 as the headline + short runs of the others)")
     ap.add_argument("--points", type=int, default=0, help="points per GPU (default: the workload's)")
     ap.add_argument("--mode", default="", choices=["", "auto", "direct", "binned", "bucketed"])
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the `workloads` block")
     ap.add_argument("--order", type=int, default=0, help="experiments: the workload's function at another order")
     ap.add_argument("--tol", type=float, default=0.0, help="experiments: another fit tolerance")
     args = ap.parse_args()
@@ -461,15 +770,16 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    cfg = WORKLOADS[args.workload]
-    if args.order and args.order != cfg["order"]:
-        cfg = dict(cfg, order=args.order, desc=cfg["desc"] + " [order overridden: %d]" % args.order)
-    if args.tol and args.tol != cfg["tol"]:
-        cfg = dict(cfg, tol=args.tol, desc=cfg["desc"] + " [tol overridden: %g]" % args.tol)
     if args.impl == "reference":
-        run_reference_arm(args, cfg, rank, world)
+        tag = args.workload or "C3"
+        cfg = WORKLOADS[tag]
+        if args.order and args.order != cfg["order"]:
+            cfg = dict(cfg, order=args.order, desc=cfg["desc"] + " [order overridden: %d]" % args.order)
+        if args.tol and args.tol != cfg["tol"]:
+            cfg = dict(cfg, tol=args.tol, desc=cfg["desc"] + " [tol overridden: %g]" % args.tol)
+        run_reference_arm(args, cfg, tag, rank, world)
     else:
-        run_ours(args, cfg, rank, world, local_rank)
+        run_ours(args, rank, world, local_rank)
 
 
 if __name__ == "__main__":

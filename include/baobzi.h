@@ -104,7 +104,10 @@ void baobzi_eval(const baobzi_t func, const double *x, double *y);
 
 /* Batched: x[ntrg][DIM] (point-major) -> res[ntrg], first output component (reference baobzi.cpp:63-65,
  * baobzi_template.hpp:866-889).  x / res are HOST pointers (pageable or pinned); the call pipelines
- * H2D copy, kernels and D2H copy in chunks and returns when res is complete. */
+ * H2D copy, kernels and D2H copy in chunks and returns when res is complete.
+ * Alignment: none beyond that of a double (8 bytes), as in the reference -- also for device pointers and for the
+ * device entries below (a 2D point array that starts on an odd double is evaluated by kernels that load 8 bytes at
+ * a time instead of the 16-byte point loads of the fast 2D paths). */
 void baobzi_eval_multi(const baobzi_t func, const double *x, double *res, int ntrg);
 
 /* Print a summary to stdout (reference baobzi.cpp:118-122); NULL-safe. */
@@ -117,7 +120,10 @@ baobzi_t baobzi_free(baobzi_t func);
 
 /* Batched evaluation with DEVICE pointers on the device that owns d_x (must be a device the handle
  * has a replica on; replicas are created lazily).  Asynchronous on `cuda_stream` (a cudaStream_t,
- * NULL = legacy default stream).  64-bit count.  Returns 0 or a cudaError_t value. */
+ * NULL = legacy default stream).  64-bit count.  Returns 0 or a cudaError_t value.
+ * The first call on a device, and any call that needs a larger sort workspace than the calls before it, allocates
+ * device memory (cudaMalloc / cudaFree: synchronous, not capturable in a CUDA graph); calls of the same or a smaller
+ * size afterwards only enqueue kernels. */
 int baobzi_eval_multi_device(const baobzi_t func, const double *d_x, double *d_res, int64_t ntrg, void *cuda_stream);
 
 /* All output components of a 1D multi-output tree, batched (extension): d_res[i * OUTPUT_DIM + k] is
@@ -160,6 +166,18 @@ int baobzi_sync(const baobzi_t func);
  *   before a thread-per-point evaluation: trees larger than L2).  BAOBZI_B200_MODE=auto|direct|binned|bucketed.
  *   chunk: points per binned chunk (0 = default).  BAOBZI_B200_CHUNK. */
 int baobzi_set_mode(baobzi_t func, int mode, int64_t chunk);
+
+/* Size of the fitted tree behind the handle: info[0] = nodes, [1] = leaves, [2] = grid cells (subtrees),
+ * [3] = doubles in the coefficient store, [4] = bytes of one device replica.  What baobzi_stats prints
+ * (reference baobzi_template.hpp:582-603), machine readable.  Returns 0. */
+int baobzi_tree_info(const baobzi_t func, int64_t info[5]);
+
+/* How many GPUs a HOST-pointer baobzi_eval_multi call is spread over: 1 (default) = the current device only,
+ * n = the current device and the next n - 1 visible ones, 0 = every visible device.  The call is cut into chunks
+ * that worker threads on the chosen devices take from a shared counter (tree replicated lazily, no collective), so
+ * an unmodified caller on an 8-GPU box uses eight PCIe links instead of one.  Also BAOBZI_B200_DEVICES=<n>|all at
+ * init / restore.  Returns 0, or 1 for a negative count. */
+int baobzi_set_host_devices(baobzi_t func, int n_devices);
 
 /* Counters for tests / benchmarks: number of kernel launches issued through this handle so far. */
 int64_t baobzi_launch_count(const baobzi_t func);

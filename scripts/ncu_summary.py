@@ -1,5 +1,7 @@
 """Summarise an .ncu-rep (one or more launches of one kernel) into the JSON kept under profiles/.
-usage: python scripts/ncu_summary.py gpurun_out/prof_k4.ncu-rep profiles/r01_k4_ncu_summary.json"""
+usage: python scripts/ncu_summary.py gpurun_out/prof_k4.ncu-rep profiles/r02_k4_ncu_summary.json [points_per_launch] [git]
+The optional arguments stamp the summary with a `_meta` record (points one profiled launch processed, git hash of the
+build that was profiled): bench.py scales `roofline.traffic` from it and reports where the figure comes from."""
 import csv
 import io
 import json
@@ -20,7 +22,7 @@ KEEP = [
 ]
 
 
-def main(rep, out):
+def main(rep, out, points_per_launch=None, git=None):
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], stdout=subprocess.PIPE, text=True, check=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     head, units = rows[0], rows[1]
@@ -37,10 +39,12 @@ def main(rep, out):
                 if float(v) >= 0.05:
                     s[k] = v
         result.append(s)
+    if points_per_launch:
+        result.append({"_meta": {"points_per_launch": float(points_per_launch), "git": git, "report": rep}})
     with open(out, "w") as f:
         json.dump(result, f, indent=1)
     print(out, len(result), "launch(es)")
 
 
 if __name__ == "__main__":
-    main(sys.argv[1], sys.argv[2])
+    main(*sys.argv[1:5])

@@ -1,7 +1,10 @@
 """Every kernel path once at small sizes, for compute-sanitizer (memcheck / racecheck / synccheck):
     compute-sanitizer --tool memcheck python scripts/sanitize_paths.py
-Uses the golden fixtures only (no oracle): exercises direct, 1D table, binned (2D, 3D incl. one heavy leaf), bucketed,
-node index, multi-output, dot, scalar and host-pointer entry points."""
+Uses the golden fixtures only (no oracle): exercises direct, 1D table and few-leaf sorted kernels, binned (2D, 3D incl.
+one heavy leaf; single-launch cooperative sort, the split sort over >= 3 chunks with its rotating histogram buffers,
+and the four-kernel fallback), bucketed, node index, multi-output, dot, scalar, host-pointer entry points (direct and
+staged through the pinned ring, several worker threads), an 8-byte-aligned 2D input and two caller streams on one
+handle."""
 import os
 import sys
 
@@ -21,15 +24,76 @@ def domain(path):
     return x.min(axis=0), x.max(axis=0)
 
 
+def extra_cases(rng):
+    """Paths the mode loop below does not reach."""
+    # two caller streams on one handle (the per-device workspace is chained through an event)
+    path = os.path.join(G, "t3d_o8.baobzi")
+    lo, hi = domain(path)
+    b = baobzi_b200.Baobzi(filename=path, mode="binned")
+    xs = [torch.from_numpy(lo + rng.random((40_000, 3)) * (hi - lo)).cuda() for _ in range(2)]
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    torch.cuda.synchronize()
+    outs = []
+    for rep in range(3):
+        for x, st in zip(xs, streams):
+            with torch.cuda.stream(st):
+                outs.append(b(x, stream=st.cuda_stream))
+    torch.cuda.synchronize()
+    print("two streams", float(outs[-1][-1]), flush=True)
+    # host pointers staged through the pinned ring by several worker threads (forced on at this small size)
+    os.environ["BAOBZI_B200_STAGE"] = "1"
+    xh = lo + rng.random((300_000, 3)) * (hi - lo)
+    yh = b(xh)
+    os.environ.pop("BAOBZI_B200_STAGE")
+    print("staged host path", float(yh[-1]), flush=True)
+    b.free()
+    # 2D points that start on an odd double
+    path = os.path.join(G, "t2d_o8.baobzi")
+    lo, hi = domain(path)
+    b = baobzi_b200.Baobzi(filename=path)
+    flat = torch.empty(2 * 50_000 + 1, dtype=torch.float64, device="cuda")
+    flat[1:] = torch.from_numpy(lo + rng.random((50_000, 2)) * (hi - lo)).cuda().reshape(-1)
+    for mode in ("auto", "binned", "bucketed"):
+        b.set_mode(mode)
+        y = b(flat[1:].view(50_000, 2))
+    torch.cuda.synchronize()
+    print("odd-aligned 2D", float(y[-1]), flush=True)
+    b.free()
+    # 3D binned with the four-kernel fallback sort
+    os.environ["BAOBZI_B200_FUSED_SORT"] = "0"
+    path = os.path.join(G, "t3d_o6.baobzi")
+    lo, hi = domain(path)
+    b = baobzi_b200.Baobzi(filename=path, mode="binned")
+    b.set_mode("binned", 20_011)
+    y = b(torch.from_numpy(lo + rng.random((60_001, 3)) * (hi - lo)).cuda())
+    torch.cuda.synchronize()
+    os.environ.pop("BAOBZI_B200_FUSED_SORT")
+    print("four-kernel sort", float(y[-1]), flush=True)
+    b.free()
+
+
 def main():
     rng = np.random.default_rng(3)
     os.environ["BAOBZI_B200_TABLE1D_MIN"] = "0"
+    extra_cases(rng)
+    # the mode loop twice: single cooperative sort launch, then the split sort forced on (3 chunks: every one of the
+    # three rotating histogram buffers is filled, scanned and cleared)
+    for split in ("0", "1"):
+        os.environ["BAOBZI_B200_SORT_SPLIT"] = split
+        print("--- BAOBZI_B200_SORT_SPLIT=" + split, flush=True)
+        mode_loop(rng, split == "1")
+    print("sanitize_paths: done")
+
+
+def mode_loop(rng, binned_only):
     for name, modes in (("t1d_o16", ["direct"]), ("tc_1d2", ["direct"]), ("t2d_o8", ["direct", "binned", "bucketed"]),
                         ("osc_2d", ["bucketed", "binned"]), ("t3d_o8", ["direct", "binned", "bucketed"]),
                         ("t3d_o12", ["binned"]), ("t3d_o6", ["binned"])):
         path = os.path.join(G, name + ".baobzi")
         lo, hi = domain(path)
         for mode in modes:
+            if binned_only and mode == "direct":
+                continue
             b = baobzi_b200.Baobzi(filename=path, mode=mode)
             n = 60_001
             x = lo + rng.random((n, b.dim)) * (hi - lo)
@@ -56,7 +120,6 @@ def main():
             torch.cuda.synchronize()
             print(name, mode, float(y[-1]), float(s), int(idx[-1]), float(np.asarray(yh)[-1]), np.asarray(ys)[0], flush=True)
             b.free()
-    print("sanitize_paths: done")
 
 
 if __name__ == "__main__":

@@ -141,7 +141,12 @@ def test_fitter_meets_reference_test_tolerances(ref, hostlib, tmp_path, func, di
         assert np.all(rel < (tol if i < 2 else 10 * tol)), (i, p, rel)
 
 
-@pytest.mark.parametrize("func,dim,order,tol,center,hl,data,od", FIT_CASES[:3])
+STRUCT_CASES = FIT_CASES[:3] + [  # + the 3D benchmark function (BASELINE.json configs[2] at a looser tolerance)
+    ("testfun_3d", 3, 8, 1e-6, [1.5, 3.0, 1.5], [1.0, 1.0, 1.0], None, 1),
+]
+
+
+@pytest.mark.parametrize("func,dim,order,tol,center,hl,data,od", STRUCT_CASES)
 def test_fitter_tree_matches_reference_structure(ref, have_reference, hostlib, tmp_path, func, dim, order, tol,
                                                  center, hl, data, od):
     """Geometry is computed with the reference's expressions, so wherever accept/refine decisions agree the trees

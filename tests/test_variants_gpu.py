@@ -109,9 +109,12 @@ def test_eval_all_multi_output_1d(gpu_lib, ref):
 ONE_D = ["t1d_o6", "t1d_o8", "t1d_o10", "t1d_o12", "t1d_o14", "t1d_o16", "deep_1d", "tc_1d2"]
 
 
+@pytest.mark.parametrize("kernel", ["table", "sorted"])
 @pytest.mark.parametrize("name", ONE_D)
-def test_table_1d_kernel_bits(gpu_lib, ref, name):
-    """The shared-memory 1D kernel (eval1d.cu) forced on from the first point: golden points (edge cases included)
+def test_table_1d_kernel_bits(gpu_lib, ref, name, kernel, monkeypatch):
+    """The shared-memory 1D kernels (eval1d.cu) forced on from the first point -- "table": the whole tree in shared
+    memory, coefficients per lane; "sorted": trees of at most 16 leaves (6 of these 8 fixtures; the others fall through
+    to the table kernel), CTA-local sort by leaf and coefficients as constant-bank operands: golden points (edge cases included)
     and seeded points over and slightly beyond the domain, 0 ulp against the reference's AVX2+FMA values, ragged
     sizes around the tile size, an odd (8-byte aligned only) input offset, and the generic kernel's bits."""
     import torch
@@ -128,6 +131,7 @@ def test_table_1d_kernel_bits(gpu_lib, ref, name):
     gx = np.ascontiguousarray(g["x"]).reshape(-1, 1)
     gwant = t.eval_multi(gx, ref.ARITH_AVX2)
     old = os.environ.get("BAOBZI_B200_TABLE1D_MIN")
+    monkeypatch.setenv("BAOBZI_B200_SORTED1D", "1" if kernel == "sorted" else "0")
     try:
         b = gpu_lib.Baobzi(filename=path, mode="direct")
         os.environ["BAOBZI_B200_TABLE1D_MIN"] = "-1"       # generic direct kernel
