@@ -579,6 +579,9 @@ baobzi_t make_handle(std::unique_ptr<Function> f) {
     if (report(cudaGetDevice(&dev), "device query (is a CUDA device visible? there is no CPU evaluation path)"))
         return nullptr;
     f->mode.store(env_mode());
+    if (const char *g = std::getenv("BAOBZI_B200_L2_FETCH")) // experiment knob: L2 fetch granularity hint (32 / 64 / 128 bytes)
+        if (std::atoi(g) > 0)
+            cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(g));
     if (const char *d = std::getenv("BAOBZI_B200_DEVICES"))
         f->host_devices = !std::strcmp(d, "all") ? 0 : std::max(1, std::atoi(d));
     if (!get_replica(f.get(), dev))

@@ -23,6 +23,7 @@
 #include "baobzi/cheb.cuh"
 #include "device_tree.hpp"
 #include "baobzi/lookup.cuh"
+#include "sort_common.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -85,6 +86,105 @@ __device__ __forceinline__ double dot_packets_one(const double (&a)[O], const do
     }
 }
 
+// One tile: 32 * P slots of ONE leaf whose coefficient block / node record sit in shared memory (coeff_s / node_s) and
+// whose gathered points sit in pts_s ([coordinate][slot]) with their result indices in idx_s.  Shared by every 3D
+// variant below (per-warp block copies, CTA-shared TMA-staged block), so the arithmetic -- and the bits -- are one.
+template <int O, int P, bool TZFLY, bool TYKEEP>
+__device__ __forceinline__ void eval_tile3d(const double2 *coeff_s, const double2 *node_s, const double *pts_s,
+                                            const uint32_t *idx_s, uint32_t lane, double *__restrict__ res) {
+    constexpr int TILE = 32 * P;
+    constexpr int NTZ = TZFLY ? 1 : O;
+    const double2 n0 = node_s[0], n1 = node_s[1], n2 = node_s[2], n3 = node_s[3];
+    const double c0 = n0.x, c1 = n0.y, c2c = n1.x, ih0 = n2.x, ih1 = n2.y, ih2 = n3.x;
+    double Tz[P][NTZ], Tyk[P][TYKEEP ? O : 1], acc[P][O];
+    double v[P], w[P], x2[P], w2[P], tx[P], tx_prev[P], val[P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+        const bool ok = idx_s[p * 32 + lane] != kInvalidSlotE;
+        const double px = ok ? pts_s[0 * TILE + p * 32 + lane] : c0; // padding lanes evaluate the leaf centre
+        const double py = ok ? pts_s[1 * TILE + p * 32 + lane] : c1;
+        const double pz = ok ? pts_s[2 * TILE + p * 32 + lane] : c2c;
+        const double u = __dmul_rn(__dsub_rn(px, c0), ih0);
+        v[p] = __dmul_rn(__dsub_rn(py, c1), ih1);
+        w[p] = __dmul_rn(__dsub_rn(pz, c2c), ih2);
+        if constexpr (TZFLY)
+            w2[p] = __dadd_rn(w[p], w[p]);
+        else
+            cheb_T<O>(w[p], Tz[p]);
+        if constexpr (TYKEEP)
+            cheb_T<O>(v[p], Tyk[p]);
+        x2[p] = __dadd_rn(u, u);
+        tx_prev[p] = u; // T_{-1} = T_1
+        tx[p] = 1.0;
+        val[p] = 0.0;
+    }
+#pragma unroll 1
+    for (int i = 0; i < O; ++i) {
+        const double2 *cc = coeff_s + i * (O * O / 2);
+        // acc[p][r] = sum_k C_i(r,k) Tz[p][k]: row chains in k order; the k = 0 product is C_i(r,0) itself
+        double tk[P], tkm[P];
+#pragma unroll
+        for (int k = 1; k < O; ++k) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                if constexpr (TZFLY) {
+                    if (k == 1) {
+                        tkm[p] = 1.0;
+                        tk[p] = w[p];
+                    } else {
+                        const double tn = __fma_rn(w2[p], tk[p], -tkm[p]);
+                        tkm[p] = tk[p];
+                        tk[p] = tn;
+                    }
+                } else {
+                    tk[p] = Tz[p][k];
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < O; r += 2) {
+                const double2 c = cc[(k * O + r) / 2];
+                if (k == 1) {
+                    const double2 cz = cc[r / 2];
+#pragma unroll
+                    for (int p = 0; p < P; ++p) {
+                        acc[p][r] = __fma_rn(c.x, tk[p], cz.x);
+                        acc[p][r + 1] = __fma_rn(c.y, tk[p], cz.y);
+                    }
+                } else {
+#pragma unroll
+                    for (int p = 0; p < P; ++p) {
+                        acc[p][r] = __fma_rn(c.x, tk[p], acc[p][r]);
+                        acc[p][r + 1] = __fma_rn(c.y, tk[p], acc[p][r + 1]);
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            double d;
+            if constexpr (TYKEEP) {
+                d = dot_packets_one<O>(Tyk[p], acc[p]);
+            } else {
+                double vv = v[p];
+                asm volatile("" : "+d"(vv)); // opaque per slab: T(y) is rebuilt here, not hoisted and kept live
+                double Ty[O];
+                cheb_T<O>(vv, Ty);
+                d = dot_packets_one<O>(Ty, acc[p]);
+            }
+            val[p] = __fma_rn(tx[p], d, val[p]);
+            const double tn = __fma_rn(x2[p], tx[p], -tx_prev[p]);
+            tx_prev[p] = tx[p];
+            tx[p] = tn;
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+        const uint32_t id = idx_s[p * 32 + lane];
+        if (id != kInvalidSlotE)
+            res[id] = val[p];
+    }
+}
+
 // TZFLY: T_k(z) advanced inside the k loop (costs O-2 extra FMAs per point and slab, frees (O-3)*P doubles).
 // TYKEEP: T(y) computed once per tile and kept live (O*P doubles) instead of rebuilt after every slab.
 // RUN: every warp walks a contiguous run of tiles (tiles of one leaf are adjacent) and keeps ONE copy of the current
@@ -106,7 +206,6 @@ bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__res
                   const uint32_t *__restrict__ n_tiles_p) {
     constexpr int TILE = 32 * P;
     constexpr int BLK2 = O * O * O / 2;
-    constexpr int NTZ = TZFLY ? 1 : O;
     using Stage = PipeStage<O, P>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t n_tiles = __ldg(n_tiles_p);
@@ -190,97 +289,425 @@ bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__res
         const double *pts_s = pts_of(cur);
         const uint32_t *idx_s = idx_of(cur);
 
-        const double2 n0 = node_s[0], n1 = node_s[1], n2 = node_s[2], n3 = node_s[3];
-        const double c0 = n0.x, c1 = n0.y, c2c = n1.x, ih0 = n2.x, ih1 = n2.y, ih2 = n3.x;
-        double Tz[P][NTZ], Tyk[P][TYKEEP ? O : 1], acc[P][O];
-        double v[P], w[P], x2[P], w2[P], tx[P], tx_prev[P], val[P];
-#pragma unroll
-        for (int p = 0; p < P; ++p) {
-            const bool ok = idx_s[p * 32 + lane] != kInvalidSlotE;
-            const double px = ok ? pts_s[0 * TILE + p * 32 + lane] : c0; // padding lanes evaluate the leaf centre
-            const double py = ok ? pts_s[1 * TILE + p * 32 + lane] : c1;
-            const double pz = ok ? pts_s[2 * TILE + p * 32 + lane] : c2c;
-            const double u = __dmul_rn(__dsub_rn(px, c0), ih0);
-            v[p] = __dmul_rn(__dsub_rn(py, c1), ih1);
-            w[p] = __dmul_rn(__dsub_rn(pz, c2c), ih2);
-            if constexpr (TZFLY)
-                w2[p] = __dadd_rn(w[p], w[p]);
-            else
-                cheb_T<O>(w[p], Tz[p]);
-            if constexpr (TYKEEP)
-                cheb_T<O>(v[p], Tyk[p]);
-            x2[p] = __dadd_rn(u, u);
-            tx_prev[p] = u; // T_{-1} = T_1
-            tx[p] = 1.0;
-            val[p] = 0.0;
-        }
-#pragma unroll 1
-        for (int i = 0; i < O; ++i) {
-            const double2 *cc = coeff_s + i * (O * O / 2);
-            // acc[p][r] = sum_k C_i(r,k) Tz[p][k]: row chains in k order; the k = 0 product is C_i(r,0) itself
-            double tk[P], tkm[P];
-#pragma unroll
-            for (int k = 1; k < O; ++k) {
-#pragma unroll
-                for (int p = 0; p < P; ++p) {
-                    if constexpr (TZFLY) {
-                        if (k == 1) {
-                            tkm[p] = 1.0;
-                            tk[p] = w[p];
-                        } else {
-                            const double tn = __fma_rn(w2[p], tk[p], -tkm[p]);
-                            tkm[p] = tk[p];
-                            tk[p] = tn;
-                        }
-                    } else {
-                        tk[p] = Tz[p][k];
-                    }
-                }
-#pragma unroll
-                for (int r = 0; r < O; r += 2) {
-                    const double2 c = cc[(k * O + r) / 2];
-                    if (k == 1) {
-                        const double2 cz = cc[r / 2];
-#pragma unroll
-                        for (int p = 0; p < P; ++p) {
-                            acc[p][r] = __fma_rn(c.x, tk[p], cz.x);
-                            acc[p][r + 1] = __fma_rn(c.y, tk[p], cz.y);
-                        }
-                    } else {
-#pragma unroll
-                        for (int p = 0; p < P; ++p) {
-                            acc[p][r] = __fma_rn(c.x, tk[p], acc[p][r]);
-                            acc[p][r + 1] = __fma_rn(c.y, tk[p], acc[p][r + 1]);
-                        }
-                    }
-                }
-            }
-#pragma unroll
-            for (int p = 0; p < P; ++p) {
-                double d;
-                if constexpr (TYKEEP) {
-                    d = dot_packets_one<O>(Tyk[p], acc[p]);
-                } else {
-                    double vv = v[p];
-                    asm volatile("" : "+d"(vv)); // opaque per slab: T(y) is rebuilt here, not hoisted and kept live
-                    double Ty[O];
-                    cheb_T<O>(vv, Ty);
-                    d = dot_packets_one<O>(Ty, acc[p]);
-                }
-                val[p] = __fma_rn(tx[p], d, val[p]);
-                const double tn = __fma_rn(x2[p], tx[p], -tx_prev[p]);
-                tx_prev[p] = tx[p];
-                tx[p] = tn;
-            }
-        }
-#pragma unroll
-        for (int p = 0; p < P; ++p) {
-            const uint32_t id = idx_s[p * 32 + lane];
-            if (id != kInvalidSlotE)
-                res[id] = val[p];
-        }
+        eval_tile3d<O, P, TZFLY, TYKEEP>(coeff_s, node_s, pts_s, idx_s, lane, res);
     }
     cp_async_wait<0>();
+}
+
+// ------------------------------------------------------------------------------------------ K4 + sort side jobs
+// The sort of a chunk is latency / request-rate bound and uses no FP64; the evaluation is FP64 bound and leaves most
+// issue slots and nearly all of the memory system idle -- but its CTA holds ~62 K of the SM's 64 K registers, so no
+// sort CTA can ever be resident beside it (two streams, round 1: 18.1 ms against 13.6 back to back).  Registers are
+// only full DURING a tile, though: between two tiles a warp holds a handful of values.  So the evaluation warps carry
+// the sort of the FOLLOWING chunks themselves, one slice per tile, in the gap between tiles:
+//     launch c:  evaluation of chunk c   +   phase B (scan + scatter) of chunk c+1   +   phase A (lookup + histogram)
+//                of chunk c+2
+// with kernel boundaries as the only global synchronisation (no grid barrier, no spinning): phase A of a chunk ends
+// with the launch that carried it (histogram flushed, per-CTA bases saved), phase B of that chunk runs in the next
+// launch, its evaluation in the one after.  The data the side jobs need is requested BEFORE the tile's arithmetic
+// (cp.async of the slice's points into a per-warp stage, the slice's 16-bit keys into two registers) and consumed
+// after it, so their latency hides behind ~3.6 us of DFMAs.  Per tile and lane: ~60 extra FP64-pipe instructions (the
+// floor transform and bounds test of 4 points) against ~2300, ~8 shared atomics, 8 stores.
+// Every CTA owns the same contiguous point range of a chunk in both phases (as in the split sort of binned.cu, whose
+// standalone kernels start the pipeline for chunks 0 and 1).
+constexpr int kPiggySlice = 128; // points (phase A) / keys (phase B) per warp and tile
+
+template <int O, int P, int WARPS, bool TZFLY, bool TYKEEP>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+bin_eval3d_piggy_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                        const uint32_t *__restrict__ perm, const uint2 *__restrict__ tile_info,
+                        const uint32_t *__restrict__ n_tiles_p, const PiggyArgs pg) {
+    constexpr int TILE = 32 * P;
+    constexpr int BLK2 = O * O * O / 2;
+    constexpr int KS = kPiggySlice / 32; // per lane
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint4 big[kBigLeafCap];
+    __shared__ uint32_t n_big;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t nl = tv.n_leaves;
+    RunSmem<O, P> &rs = reinterpret_cast<RunSmem<O, P> *>(smem_raw)[warp];
+    uint32_t *tbl_b = reinterpret_cast<uint32_t *>(smem_raw + sizeof(RunSmem<O, P>) * WARPS);
+    uint32_t *hist_a = tbl_b + nl;
+    double *stage_a = reinterpret_cast<double *>(hist_a + nl + (nl & 1)) + (size_t)warp * 3 * kPiggySlice;
+    uint16_t *sbin = reinterpret_cast<uint16_t *>(reinterpret_cast<double *>(hist_a + nl + (nl & 1)) + (size_t)WARPS * 3 * kPiggySlice);
+
+    // ---- side-job setup (CTA wide)
+    if (tid == 0)
+        n_big = 0;
+    for (uint32_t l = tid; l < nl; l += WARPS * 32) {
+        hist_a[l] = 0;
+        tbl_b[l] = pg.nb ? pg.base_b[(size_t)blockIdx.x * nl + l] : 0u;
+    }
+    for (uint32_t l = tid; l < pg.sbin_n; l += WARPS * 32)
+        sbin[l] = (uint16_t)__ldg(tv.bin_leaf + l); // kNotLeaf -> 0xFFFF
+    __syncthreads();
+    if (pg.nb) // padded scan of chunk c+1's histogram: tbl_b[l] = first free slot of this CTA inside leaf l; descriptors
+        sort_scan_describe<false>(tv, tbl_b, pg.count_b, pg.count_clear, pg.cshift, (uint32_t)TILE, pg.perm_b, pg.tile_leaf_b,
+                                  pg.tile_info_b, pg.n_tiles_b, nl, nullptr, warp_sums, big, &n_big);
+    __syncthreads();
+
+    // this warp's slices: the CTA's range of the chunk (multiples of 8, as in the split sort), cut into WARPS pieces of
+    // whole slices
+    auto warp_range = [&](uint32_t n, uint32_t &lo, uint32_t &hi) {
+        const uint32_t clo = (uint32_t)(((uint64_t)blockIdx.x * n) / gridDim.x) & ~7u;
+        const uint32_t chi = blockIdx.x + 1 != gridDim.x ? (uint32_t)(((uint64_t)(blockIdx.x + 1) * n) / gridDim.x) & ~7u : n;
+        const uint32_t per = ((chi - clo + WARPS - 1) / WARPS + kPiggySlice - 1) / kPiggySlice * kPiggySlice;
+        lo = min(clo + warp * per, chi);
+        hi = min(lo + per, chi);
+    };
+    uint32_t a_pos = 0, a_end = 0, b_pos = 0, b_end = 0;
+    if (pg.na)
+        warp_range(pg.na, a_pos, a_end);
+    if (pg.nb)
+        warp_range(pg.nb, b_pos, b_end);
+
+    // phase A, first half: request the slice's points (raw copy of 3 * 128 contiguous doubles)
+    auto a_request = [&]() {
+        if (a_pos < a_end) {
+            const uint32_t m3 = 3u * min((uint32_t)kPiggySlice, a_end - a_pos);
+            const double *src = pg.xa + 3ull * a_pos;
+#pragma unroll
+            for (int j = 0; j < 3 * KS; ++j)
+                if (j * 32 + lane < m3)
+                    cp_async8(stage_a + j * 32 + lane, src + j * 32 + lane);
+        }
+        cp_async_commit();
+    };
+    // phase A, second half (the copy has landed): leaf of every point, key, histogram, NaN for points outside
+    auto a_consume = [&]() {
+        if (a_pos >= a_end)
+            return;
+        const uint32_t m = min((uint32_t)kPiggySlice, a_end - a_pos);
+        uint32_t leaf[KS];
+#pragma unroll
+        for (int j = 0; j < KS; ++j) {
+            const uint32_t q = j * 32 + lane;
+            leaf[j] = kNotLeaf;
+            if (q < m) {
+                const double p[3] = {stage_a[3 * q], stage_a[3 * q + 1], stage_a[3 * q + 2]};
+                if (!outside<3>(tv, p)) {
+                    const uint32_t lin = linear_bin<3>(tv, p);
+                    uint32_t v;
+                    if (pg.sbin_n) {
+                        v = sbin[lin];
+                        v = v == 0xFFFFu ? kNotLeaf : v;
+                    } else {
+                        v = __ldg(tv.bin_leaf + lin);
+                    }
+                    leaf[j] = v != kNotLeaf ? v : walk_to_leaf<3>(tv, lin, p);
+                } else {
+                    pg.resa[a_pos + q] = __longlong_as_double(0x7ff8000000000000ll);
+                }
+                pg.key_a[a_pos + q] = (uint16_t)leaf[j]; // kNotLeaf -> 0xFFFF
+            }
+        }
+        const bool heavy = keys_repeat(leaf[0], lane);
+#pragma unroll
+        for (int j = 0; j < KS; ++j)
+            grouped_add(hist_a, leaf[j], heavy, lane);
+        a_pos += m;
+    };
+    // phase B: four keys per lane (one 8-byte load, requested before the tile), slot = next free one of the leaf
+    auto b_request = [&]() -> uint2 {
+        if (b_pos + 4 * lane < b_end) // ranges are multiples of 8 except the chunk's very end (the buffer is padded)
+            return __ldcs(reinterpret_cast<const uint2 *>(pg.key_b + b_pos) + lane);
+        return make_uint2(~0u, ~0u);
+    };
+    auto b_consume = [&](const uint2 kk) {
+        if (b_pos >= b_end)
+            return;
+        const uint32_t w[2] = {kk.x, kk.y};
+        uint32_t k[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t v = (w[j / 2] >> (16 * (j & 1))) & 0xFFFFu;
+            k[j] = v == 0xFFFFu || b_pos + 4 * lane + j >= b_end ? kNotLeaf : v;
+        }
+        const uint32_t i0 = b_pos + 4 * lane;
+        if (!keys_repeat(k[0], lane)) {
+            uint32_t slot[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                slot[j] = k[j] != kNotLeaf ? atomicAdd(tbl_b + k[j], 1u) : 0u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (k[j] != kNotLeaf)
+                    pg.perm_b[slot[j]] = i0 + j;
+        } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t slot = grouped_add(tbl_b, k[j], true, lane);
+                if (k[j] != kNotLeaf)
+                    pg.perm_b[slot] = i0 + j;
+            }
+        }
+        b_pos = min(b_pos + (uint32_t)kPiggySlice, b_end);
+    };
+
+    // ---- evaluation of chunk c: exactly the per-warp-run kernel above
+    const uint32_t n_tiles = __ldg(n_tiles_p);
+    const uint32_t nw = gridDim.x * WARPS, wid = blockIdx.x * WARPS + warp;
+    uint32_t t = (uint32_t)(((uint64_t)n_tiles * wid) / nw);
+    const uint32_t t_end = (uint32_t)(((uint64_t)n_tiles * (wid + 1)) / nw);
+    auto load_meta = [&](uint32_t tt, uint2 &info, uint32_t (&id)[P]) {
+        if (tt < t_end) {
+            info = __ldg(tile_info + tt);
+#pragma unroll
+            for (int p = 0; p < P; ++p)
+                id[p] = __ldg(perm + (size_t)tt * TILE + p * 32 + lane);
+        } else {
+            info = make_uint2(0, 0);
+#pragma unroll
+            for (int p = 0; p < P; ++p)
+                id[p] = kInvalidSlotE;
+        }
+    };
+    auto fetch_leaf = [&](const uint2 &info) {
+        const double2 *Cg = reinterpret_cast<const double2 *>(tv.coeffs + 2ull * info.y);
+#pragma unroll 4
+        for (int j = lane; j < BLK2; j += 32)
+            cp_async16(&rs.coeff[j], Cg + j);
+        if (lane < 4)
+            cp_async16(&rs.node[lane], reinterpret_cast<const double2 *>(tv.nodes + info.x) + lane);
+    };
+    auto issue = [&](uint32_t tt, const uint32_t (&id)[P], int sidx) {
+        if (tt < t_end) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                rs.idx[sidx][p * 32 + lane] = id[p];
+                if (id[p] != kInvalidSlotE) {
+                    const double *q = x + 3ull * id[p];
+                    cp_async8(&rs.pts[sidx][0 * TILE + p * 32 + lane], q);
+                    cp_async8(&rs.pts[sidx][1 * TILE + p * 32 + lane], q + 1);
+                    cp_async8(&rs.pts[sidx][2 * TILE + p * 32 + lane], q + 2);
+                }
+            }
+        }
+        cp_async_commit();
+    };
+
+    uint2 info_n, info_cur;
+    uint32_t idx_n[P];
+    load_meta(t, info_n, idx_n);
+    issue(t, idx_n, 0);
+    info_cur = info_n;
+    load_meta(t + 1, info_n, idx_n);
+    uint32_t cur_node = 0xFFFFFFFFu;
+    int cur = 0;
+    for (; t < t_end; ++t, cur ^= 1) {
+        __syncwarp(); // every lane is done reading stage cur^1, the coefficient block and the side-job stage
+        issue(t + 1, idx_n, cur ^ 1);
+        const uint2 info_next = info_n;
+        load_meta(t + 2, info_n, idx_n);
+        a_request();                 // the slice's points: land while this tile computes
+        const uint2 kk = b_request(); // ... and its keys
+        if (info_cur.x != cur_node) { // warp uniform: a new leaf starts here
+            cur_node = info_cur.x;
+            fetch_leaf(info_cur);
+            cp_async_commit();
+            cp_async_wait<0>();
+        } else {
+            cp_async_wait<2>(); // this tile's points; the next tile's and the slice may still be in flight
+        }
+        __syncwarp();
+        info_cur = info_next;
+        eval_tile3d<O, P, TZFLY, TYKEEP>(rs.coeff, rs.node, rs.pts[cur], rs.idx[cur], lane, res);
+        cp_async_wait<0>();
+        __syncwarp();
+        b_consume(kk);
+        a_consume();
+    }
+    cp_async_wait<0>();
+    // whatever the tiles did not cover (chunks with few tiles: most points outside the domain, a short last chunk)
+    while (b_pos < b_end) {
+        const uint2 kk = b_request();
+        b_consume(kk);
+    }
+    while (a_pos < a_end) {
+        __syncwarp();
+        a_request();
+        cp_async_wait<0>();
+        __syncwarp();
+        a_consume();
+    }
+    // ---- phase A epilogue: reserve this CTA's share of every leaf, save the bases for the launch that scatters
+    if (pg.na) {
+        __syncthreads();
+        for (uint32_t lb = tid; lb < nl; lb += kSortBatch * WARPS * 32) {
+            uint32_t h[kSortBatch], r[kSortBatch];
+#pragma unroll
+            for (int j = 0; j < kSortBatch; ++j) {
+                const uint32_t l = lb + j * WARPS * 32;
+                h[j] = l < nl ? hist_a[l] : 0u;
+            }
+#pragma unroll
+            for (int j = 0; j < kSortBatch; ++j)
+                r[j] = h[j] ? atomicAdd(pg.count_a + ((size_t)(lb + j * WARPS * 32) << pg.cshift), h[j]) : 0u;
+#pragma unroll
+            for (int j = 0; j < kSortBatch; ++j) {
+                const uint32_t l = lb + j * WARPS * 32;
+                if (l < nl)
+                    pg.base_a[(size_t)blockIdx.x * nl + l] = r[j];
+            }
+        }
+    }
+}
+
+// shared memory of the piggy kernel for a tree of nl leaves (sbin_n table entries)
+template <int O, int P, int WARPS>
+static size_t piggy_smem(uint32_t nl, uint32_t sbin_n) {
+    return sizeof(RunSmem<O, P>) * WARPS + sizeof(uint32_t) * (2 * (size_t)nl + (nl & 1)) +
+           sizeof(double) * 3 * kPiggySlice * WARPS + sizeof(uint16_t) * (((size_t)sbin_n + 7) / 8 * 8);
+}
+
+// ------------------------------------------------------------------------------------------ K4, CTA-shared block
+// High orders (block = 13.8 KB at order 12, 22 KB at 14, 32 KB at 16; reference cheb_eval<3>, template.hpp:179-194):
+// a private copy of the block per warp is what limited the kernel above to 4 warps per SM at order 16 -- one warp
+// per scheduler.  A chunk holds hundreds to thousands of tiles per leaf at these orders, so here the whole CTA works
+// in ONE leaf at a time: the CTA owns a contiguous run of tiles, its warps take them round-robin, and the leaf's block
+// (plus its 64-byte node record) is staged ONCE per CTA by the TMA engine -- one elected thread arms an mbarrier with
+// the byte count and issues two cp.async.bulk copies (SASS: UBLKCP), every thread then waits on the barrier's phase.
+// A segment (= the CTA's tiles of one leaf) ends with one __syncthreads, after which the same buffer takes the next
+// leaf; at <= 3 segments per CTA and chunk the exposed copy latency is noise, so there is no second buffer.
+// Which tile starts the next segment is found by the warps themselves: each one reports its first tile outside the
+// current leaf (shared atomicMin); tiles are ordered by leaf, so the minimum is the next segment's first tile.
+template <int O, int P>
+struct SharedWarpStage { // per warp: gathered points of two tiles in flight
+    static constexpr int TILE = 32 * P;
+    double pts[2][3 * TILE];
+    uint32_t idx[2][TILE];
+};
+constexpr int kSharedHeader = 128; // node record (64 B) + mbarrier (8 B) + two segment cursors, behind the block
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t done = 0;
+    while (!done)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(done)
+                     : "r"(smem_u32(bar)), "r"(parity)
+                     : "memory");
+}
+
+template <int O, int P, int WARPS, bool TZFLY, bool TYKEEP>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+bin_eval3d_shared_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
+                         const uint32_t *__restrict__ perm, const uint2 *__restrict__ tile_info,
+                         const uint32_t *__restrict__ n_tiles_p) {
+    constexpr int TILE = 32 * P;
+    constexpr uint32_t BLK_BYTES = O * O * O * 8;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double2 *coeff_s = reinterpret_cast<double2 *>(smem_raw);
+    double2 *node_s = reinterpret_cast<double2 *>(smem_raw + BLK_BYTES);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + BLK_BYTES + 64);
+    uint32_t *s_next = reinterpret_cast<uint32_t *>(smem_raw + BLK_BYTES + 72);
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    SharedWarpStage<O, P> &st = reinterpret_cast<SharedWarpStage<O, P> *>(smem_raw + BLK_BYTES + kSharedHeader)[warp];
+    const uint32_t n_tiles = __ldg(n_tiles_p);
+    const uint32_t T0 = (uint32_t)(((uint64_t)n_tiles * blockIdx.x) / gridDim.x);
+    const uint32_t T1 = (uint32_t)(((uint64_t)n_tiles * (blockIdx.x + 1)) / gridDim.x);
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        s_next[0] = T0;
+        s_next[1] = 0xFFFFFFFFu;
+    }
+    __syncthreads();
+
+    auto load_meta = [&](uint32_t tt, uint2 &info, uint32_t (&id)[P]) {
+        if (tt < T1) {
+            info = __ldg(tile_info + tt);
+#pragma unroll
+            for (int p = 0; p < P; ++p)
+                id[p] = __ldg(perm + (size_t)tt * TILE + p * 32 + lane);
+        } else {
+            info = make_uint2(0, 0);
+#pragma unroll
+            for (int p = 0; p < P; ++p)
+                id[p] = kInvalidSlotE;
+        }
+    };
+    auto issue = [&](uint32_t tt, const uint32_t (&id)[P], int sidx) {
+        if (tt < T1) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                st.idx[sidx][p * 32 + lane] = id[p];
+                if (id[p] != kInvalidSlotE) {
+                    const double *q = x + 3ull * id[p];
+                    cp_async8(&st.pts[sidx][0 * TILE + p * 32 + lane], q);
+                    cp_async8(&st.pts[sidx][1 * TILE + p * 32 + lane], q + 1);
+                    cp_async8(&st.pts[sidx][2 * TILE + p * 32 + lane], q + 2);
+                }
+            }
+        }
+        cp_async_commit();
+    };
+
+    uint32_t t = T0 + warp; // this warp's tiles: T0 + warp, + WARPS, ...
+    uint2 info_cur, info_n;
+    uint32_t idx_n[P];
+    load_meta(t, info_cur, idx_n);
+    issue(t, idx_n, 0);
+    load_meta(t + WARPS, info_n, idx_n);
+    int cur = 0;
+    for (uint32_t seg = 0;; ++seg) {
+        const uint32_t first = s_next[seg & 1]; // CTA uniform: first tile of this segment
+        if (first >= T1)
+            break;
+        const uint2 sinfo = __ldg(tile_info + first);
+        if (threadIdx.x == 0) {
+            s_next[(seg + 1) & 1] = 0xFFFFFFFFu; // nobody reports into it before the copy below has landed
+            mbar_expect_tx(bar, BLK_BYTES + 64);
+            tma_bulk_g2s(coeff_s, tv.coeffs + 2ull * sinfo.y, BLK_BYTES, bar);
+            tma_bulk_g2s(node_s, tv.nodes + sinfo.x, 64, bar);
+        }
+        mbar_wait(bar, seg & 1);
+        while (t < T1 && info_cur.x == sinfo.x) { // warp uniform
+            __syncwarp(); // every lane is done reading stage cur^1
+            issue(t + WARPS, idx_n, cur ^ 1);
+            const uint2 info_next = info_n;
+            load_meta(t + 2 * WARPS, info_n, idx_n); // lands while this tile computes
+            cp_async_wait<1>();
+            __syncwarp();
+            eval_tile3d<O, P, TZFLY, TYKEEP>(coeff_s, node_s, st.pts[cur], st.idx[cur], lane, res);
+            info_cur = info_next;
+            t += WARPS;
+            cur ^= 1;
+        }
+        if (lane == 0 && t < T1)
+            atomicMin(&s_next[(seg + 1) & 1], t);
+        __syncthreads(); // the block may be overwritten; the next segment's first tile is known
+    }
+    cp_async_wait<0>();
+}
+
+template <int O, int P, int WARPS, bool TZFLY, bool TYKEEP>
+static int launch_k4_shared(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
+    auto kern = bin_eval3d_shared_kernel<O, P, WARPS, TZFLY, TYKEEP>;
+    constexpr size_t smem = (size_t)O * O * O * 8 + kSharedHeader + sizeof(SharedWarpStage<O, P>) * WARPS;
+    static_assert(smem <= 227 * 1024, "shared block + point stages exceed the shared memory of an SM");
+    static bool configured[kMaxDevices] = {};
+    if (dt.device < 0 || dt.device >= kMaxDevices || !configured[dt.device]) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess)
+            return (int)e;
+        if (dt.device >= 0 && dt.device < kMaxDevices)
+            configured[dt.device] = true;
+    }
+    kern<<<dt.sm_count, WARPS * 32, smem, st>>>(dt.view, d_x, d_res, ws.perm, ws.tile_info, ws.n_tiles);
+    return (int)cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------ K4, 2D
@@ -643,9 +1070,61 @@ static int launch_k4_mma8(const DeviceTree &dt, const BinWorkspace &ws, const do
 }
 
 // ------------------------------------------------------------------------------------------ host side
+template <int O, int P, int WARPS, bool TZFLY, bool TYKEEP>
+static int launch_k4_piggy(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st,
+                           const PiggyArgs &pg) {
+    auto kern = bin_eval3d_piggy_kernel<O, P, WARPS, TZFLY, TYKEEP>;
+    const size_t smem = piggy_smem<O, P, WARPS>(dt.view.n_leaves, pg.sbin_n);
+    if (smem > 227 * 1024)
+        return (int)cudaErrorInvalidConfiguration;
+    static size_t configured[kMaxDevices] = {}; // largest size asked for so far, per device
+    if (dt.device < 0 || dt.device >= kMaxDevices || configured[dt.device] < smem) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess)
+            return (int)e;
+        if (dt.device >= 0 && dt.device < kMaxDevices)
+            configured[dt.device] = smem;
+    }
+    kern<<<dt.sm_count, WARPS * 32, smem, st>>>(dt.view, d_x, d_res, ws.perm, ws.tile_info, ws.n_tiles, pg);
+    return (int)cudaGetLastError();
+}
+
+// The piggy kernel exists for the default variant of every order (what bin_eval_select returns without an override).
+#define BZ_PIGGY_CASES(X) X(6, 4, 8, false, true) X(8, 4, 8, false, true) X(10, 3, 8, false, false) X(12, 3, 8, false, false) \
+    X(14, 2, 8, false, true) X(16, 2, 4, false, true)
+
+int bin_eval_piggy_P(int order) { // points per lane of the piggy kernel: the workspace's tile size must be 32 * this
+    switch (order) {
+#define X(O_, P_, W_, F_, Y_) case O_: return P_;
+        BZ_PIGGY_CASES(X)
+#undef X
+    default: return -1;
+    }
+}
+
+size_t bin_eval_piggy_smem(int order, uint32_t n_leaves, uint32_t sbin_n) {
+    switch (order) {
+#define X(O_, P_, W_, F_, Y_) case O_: return piggy_smem<O_, P_, W_>(n_leaves, sbin_n);
+        BZ_PIGGY_CASES(X)
+#undef X
+    default: return ~size_t(0);
+    }
+}
+
+int launch_bin_eval3d_piggy(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st,
+                            const PiggyArgs &pg) {
+    switch (dt.view.order) {
+#define X(O_, P_, W_, F_, Y_) case O_: return launch_k4_piggy<O_, P_, W_, F_, Y_>(dt, ws, d_x, d_res, st, pg);
+        BZ_PIGGY_CASES(X)
+#undef X
+    default: return (int)cudaErrorInvalidValue;
+    }
+}
+
 struct K4Variant {
     int order, P, warps;
-    bool tzfly, tykeep, run;
+    bool tzfly, tykeep;
+    int run; // 0: tiles strided over the grid, block per tile; 1: per-warp runs, block per warp; 2: CTA-shared block (TMA)
     int (*launch)(const DeviceTree &, const BinWorkspace &, const double *, double *, cudaStream_t);
     const void *func; // for cudaFuncGetAttributes
     size_t smem;
@@ -671,14 +1150,18 @@ static int launch_k4(const DeviceTree &dt, const BinWorkspace &ws, const double 
 #define BZ_K4(O_, P_, W_, F_, Y_, R_)                                                                                  \
     {O_, P_, W_, F_, Y_, R_, launch_k4<O_, P_, W_, F_, Y_, R_>, (const void *)bin_eval3d_kernel<O_, P_, W_, F_, Y_, R_>, \
      R_ ? sizeof(RunSmem<O_, P_>) * W_ : sizeof(PipeStage<O_, P_>) * 2 * W_}
+#define BZ_K4S(O_, P_, W_, F_, Y_)                                                                                     \
+    {O_, P_, W_, F_, Y_, 2, launch_k4_shared<O_, P_, W_, F_, Y_>, (const void *)bin_eval3d_shared_kernel<O_, P_, W_, F_, Y_>, \
+     (size_t)O_ * O_ * O_ * 8 + kSharedHeader + sizeof(SharedWarpStage<O_, P_>) * W_}
 #define BZ_K4M(W_, D_)                                                                                                 \
-    {8, D_ ? 5 : 4, W_, true, true, false, launch_k4_mma8<W_, D_>, (const void *)bin_eval3d_mma8_kernel<W_, D_>,       \
+    {8, D_ ? 5 : 4, W_, true, true, 0, launch_k4_mma8<W_, D_>, (const void *)bin_eval3d_mma8_kernel<W_, D_>,       \
      sizeof(MmaStage) * 2 * W_}
 // first entry of an order = its default
 static const K4Variant kVariants[] = {
     BZ_K4(6, 4, 8, false, true, true),    BZ_K4(6, 4, 8, false, true, false),   BZ_K4(6, 4, 12, false, true, true),
     BZ_K4(8, 4, 8, false, true, true),    BZ_K4(8, 4, 8, false, true, false),   BZ_K4(8, 4, 8, false, false, false),
     BZ_K4(8, 3, 12, false, false, false), BZ_K4(8, 3, 12, false, false, true),  BZ_K4(8, 2, 16, false, true, false),
+    BZ_K4(8, 4, 8, true, true, true),     BZ_K4(8, 4, 12, true, false, true),   BZ_K4(8, 3, 12, true, true, true),
     // tzfly && tykeep together = the DMMA kernel (P = 5 in the selector: deferred quad reduction)
     BZ_K4M(16, false), BZ_K4M(12, false), BZ_K4M(16, true),
     BZ_K4(10, 3, 8, false, false, true),  BZ_K4(10, 2, 8, false, true, false),  BZ_K4(10, 3, 8, false, false, false),
@@ -687,20 +1170,31 @@ static const K4Variant kVariants[] = {
     BZ_K4(12, 2, 8, false, true, true),   BZ_K4(12, 2, 12, false, false, true),
     BZ_K4(14, 2, 8, false, true, true),   BZ_K4(14, 2, 4, false, true, false),  BZ_K4(14, 3, 8, true, false, true),
     BZ_K4(16, 2, 4, false, true, true),   BZ_K4(16, 2, 2, false, true, false),  BZ_K4(16, 2, 6, false, false, true),
+    // CTA-shared, TMA-staged block (run = 2)
+    BZ_K4S(12, 3, 8, false, false),  BZ_K4S(12, 3, 12, true, false),  BZ_K4S(12, 2, 12, false, true),
+    BZ_K4S(14, 2, 8, false, true),   BZ_K4S(14, 3, 8, true, false),   BZ_K4S(14, 2, 12, true, false),
+    BZ_K4S(16, 2, 8, false, true),   BZ_K4S(16, 2, 8, false, false),  BZ_K4S(16, 2, 12, true, false),
 };
+#undef BZ_K4S
 #undef BZ_K4
 #undef BZ_K4M
 
 static const K4Variant *find_variant(int order, int P, int warps, int tzfly, int tykeep, int run) {
     for (const K4Variant &v : kVariants)
         if (v.order == order && (P < 0 || (v.P == P && v.warps == warps && v.tzfly == (tzfly != 0) &&
-                                           v.tykeep == (tykeep != 0) && v.run == (run != 0))))
+                                           v.tykeep == (tykeep != 0) && v.run == run)))
             return &v;
     return nullptr;
 }
 
 // Variant for a 3D tree of this order: the default, or BAOBZI_B200_K4="P,warps,tzfly,tykeep[,run]" (benchmarks).
 // Returns the points per lane (tile = 32 * P slots) and an opaque index for launch_bin_eval3d; -1 if unsupported.
+bool bin_eval_is_default(int variant) {
+    if (variant < 0 || variant >= (int)(sizeof(kVariants) / sizeof(kVariants[0])))
+        return false;
+    return &kVariants[variant] == find_variant(kVariants[variant].order, -1, 0, 0, 0, 0);
+}
+
 int bin_eval_select(int order, int *P) {
     const K4Variant *v = find_variant(order, -1, 0, 0, 0, 0);
     if (const char *e = std::getenv("BAOBZI_B200_K4")) {

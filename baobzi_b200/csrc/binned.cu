@@ -28,12 +28,12 @@
 #include <utility>
 
 #include "baobzi/lookup.cuh"
+#include "sort_common.cuh"
 
 #include <cooperative_groups.h>
 
 namespace bz {
 
-constexpr uint32_t kInvalidSlot = 0xFFFFFFFFu;
 constexpr int kBinThreads = 256;
 
 int bin_eval_select(int order, int *P);
@@ -41,6 +41,11 @@ int bin_eval2d_P(int order);
 int launch_bin_eval2d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st);
 bool bin_eval_footprint(int variant, int *cta_regs, size_t *cta_smem);
 int launch_bin_eval3d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st);
+bool bin_eval_is_default(int variant);
+int bin_eval_piggy_P(int order);
+size_t bin_eval_piggy_smem(int order, uint32_t n_leaves, uint32_t sbin_n);
+int launch_bin_eval3d_piggy(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st,
+                            const PiggyArgs &pg);
 
 // ------------------------------------------------------------------------------------------ K1
 template <int DIM>
@@ -78,38 +83,10 @@ bin_lookup_kernel(const TreeView tv, const double *__restrict__ x, double *__res
 constexpr int kSortThreads = 512;
 constexpr int kSortThreadsA = 768; // most threads the lookup launch of the split sort may be given
 constexpr size_t kFusedSortMaxSmem = 160 * 1024;
-constexpr int kSortBatch = 6; // histogram counters (loads / atomics) in flight per thread in the scan phases
 constexpr int kSortSplitDefault = 1;
 constexpr int64_t kSortSplitMinLeaves = 2048;
 constexpr int64_t kSortSplitMinLeaves2D = 128; // split sort (phase A of the next chunk beside the scatter of this one): CTAs per SM and kernel, 0 = off
 constexpr int kSortPts = 4; // independent lookups in flight per thread (the lookup is latency bound, not issue bound)
-
-// BYBIN (the bucketed path of large 1D / 2D trees): the key is the grid cell number >> bshift instead of the leaf,
-// so the sort touches no tree data; TILE is 1 and no tile descriptors are written (tile_info == nullptr).
-constexpr uint32_t kBigLeafCap = 128;
-
-// Shared-memory counter increment for a warp whose lanes may hold the same key (k == kNotLeaf: no increment).
-// Returns the value the lane's own atomicAdd(tbl + k, 1) would have returned, up to the order inside the warp.
-// `heavy` (warp uniform) says most lanes share keys -- clustered or ordered input, where 32 same-address ATOMS
-// per warp and 16 warps on one bank made the sort 5x slower than on uniform points: the lanes of each key then
-// elect a leader that adds the group's size once.  All 32 lanes must call this together.
-__device__ __forceinline__ uint32_t grouped_add(uint32_t *tbl, uint32_t k, bool heavy, uint32_t lane) {
-    if (!heavy)
-        return k != kNotLeaf ? atomicAdd(tbl + k, 1u) : 0u;
-    const uint32_t grp = __match_any_sync(0xffffffffu, k);
-    const int leader = __ffs(grp) - 1;
-    uint32_t base = 0;
-    if ((int)lane == leader && k != kNotLeaf)
-        base = atomicAdd(tbl + k, (uint32_t)__popc(grp));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    return base + (uint32_t)__popc(grp & ((1u << lane) - 1u));
-}
-
-// warp uniform: do at least half of the lanes hold the key of their right neighbour?
-__device__ __forceinline__ bool keys_repeat(uint32_t k, uint32_t lane) {
-    const uint32_t nb = __shfl_sync(0xffffffffu, k, (lane + 1) & 31);
-    return __popc(__ballot_sync(0xffffffffu, nb == k && k != kNotLeaf)) >= 16;
-}
 
 template <int DIM, bool BYBIN, int PHASE = 0>
 __global__ void __launch_bounds__(PHASE == 1 ? kSortThreadsA : kSortThreads)
@@ -239,113 +216,12 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         cooperative_groups::this_grid().sync();
     }
 
-    // ---- phase B: padded exclusive scan of the global histogram, thread t owns leaves [t*per, (t+1)*per)
+    // ---- phase B: padded exclusive scan of the global histogram, padding slots, tile descriptors (sort_common.cuh)
+    sort_scan_describe<BYBIN>(tv, tbl, count, count_next, cshift, TILE, perm, tile_leaf, tile_info, n_tiles, nl, key_start,
+                              warp_sums, big, &n_big);
+    const uint32_t lane = tid & 31, warp = tid >> 5;
     const uint32_t per = (nl + nthr - 1) / nthr;
     const uint32_t l0 = min(tid * per, nl), l1 = min(l0 + per, nl);
-    uint32_t mine = 0;
-    for (uint32_t lb = l0; lb < l1; lb += kSortBatch) { // kSortBatch counters requested together, not one by one
-        uint32_t c[kSortBatch];
-#pragma unroll
-        for (int j = 0; j < kSortBatch; ++j)
-            c[j] = lb + j < l1 ? __ldcg(count + ((size_t)(lb + j) << cshift)) : 0u;
-#pragma unroll
-        for (int j = 0; j < kSortBatch; ++j)
-            mine += (c[j] + TILE - 1) / TILE * TILE;
-    }
-    const uint32_t lane = tid & 31, warp = tid >> 5;
-    uint32_t incl = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o)
-            incl += t;
-    }
-    if (lane == 31)
-        warp_sums[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-        uint32_t w = lane < nthr / 32 ? warp_sums[lane] : 0u;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, w, o);
-            if (lane >= o)
-                w += t;
-        }
-        if (lane < nthr / 32)
-            warp_sums[lane] = w;
-    }
-    __syncthreads();
-    uint32_t start = (warp ? warp_sums[warp - 1] : 0u) + incl - mine;
-    // A leaf holding a large share of the chunk (clustered input: up to every tile of it) gets its tile descriptors
-    // from the whole grid, not from one thread: 65 K tiles of one leaf took 0.6 ms per chunk that way.  "Large" is
-    // more than 1/kBigLeafCap of all tiles, so the list below cannot overflow and is the same in every CTA.
-    const uint32_t big_tiles = max(256u, warp_sums[nthr / 32 - 1] / TILE / kBigLeafCap);
-    const uint32_t start0 = start;
-    bool any_big = false;
-    for (uint32_t lb = l0; lb < l1; lb += kSortBatch) {
-      uint32_t cb[kSortBatch];
-#pragma unroll
-      for (int j = 0; j < kSortBatch; ++j)
-          cb[j] = lb + j < l1 ? __ldcg(count + ((size_t)(lb + j) << cshift)) : 0u;
-#pragma unroll
-      for (int j = 0; j < kSortBatch; ++j) {
-        const uint32_t l = lb + j;
-        if (l >= l1)
-            break;
-        const uint32_t c = cb[j];
-        const uint32_t padded = (c + TILE - 1) / TILE * TILE;
-        const bool is_big = !BYBIN && padded / TILE > big_tiles;
-        any_big = any_big || is_big;
-        if (l % gridDim.x == blockIdx.x) { // this CTA's leaves: padding slots, tile descriptors, counter reset
-            if (!BYBIN) {
-                for (uint32_t s = start + c; s < start + padded; ++s)
-                    perm[s] = kInvalidSlot;
-                if (!is_big) {
-                    const uint32_t node = __ldg(tv.leaf_node + l);
-                    const uint2 info = make_uint2(node, load_head(tv.nodes, node).coeff16);
-                    for (uint32_t t = start / TILE; t < (start + padded) / TILE; ++t) {
-                        tile_leaf[t] = l;
-                        tile_info[t] = info;
-                    }
-                }
-            }
-            count_next[(size_t)l << cshift] = 0; // the buffer the NEXT chunk histograms into
-        }
-        if (BYBIN && blockIdx.x == 0)
-            key_start[l] = start; // first slot of every bucket, for the evaluation kernel
-        tbl[l] += start;
-        start += padded;
-      }
-    }
-    if (any_big) { // rare: list this thread's big leaves (kept out of the loop above: an atomic there serialises its loads)
-        uint32_t s2 = start0;
-        for (uint32_t l = l0; l < l1; ++l) {
-            const uint32_t c = __ldcg(count + ((size_t)l << cshift));
-            const uint32_t padded = (c + TILE - 1) / TILE * TILE;
-            if (padded / TILE > big_tiles) // every CTA lists the same (fewer than kBigLeafCap) leaves
-                big[atomicAdd(&n_big, 1u)] = make_uint4(l, s2 / TILE, padded / TILE, __ldg(tv.leaf_node + l));
-            s2 += padded;
-        }
-    }
-    if (blockIdx.x == 0 && tid == nthr - 1) {
-        *n_tiles = (warp_sums[nthr / 32 - 1]) / TILE;
-        if (BYBIN) {
-            key_start[nl] = warp_sums[nthr / 32 - 1];
-            n_tiles[1] = 0; // work queue of the evaluation kernel
-        }
-    }
-    __syncthreads();
-    if (!BYBIN) {
-        for (uint32_t e = 0; e < n_big; ++e) {
-            const uint4 b = big[e]; // {leaf, first tile, tiles, node}
-            const uint2 info = make_uint2(b.w, load_head(tv.nodes, b.w).coeff16);
-            for (uint32_t t = blockIdx.x * nthr + tid; t < b.z; t += gridDim.x * nthr) {
-                tile_leaf[b.y + t] = b.x;
-                tile_info[b.y + t] = info;
-            }
-        }
-    }
-
     // ---- scatter
     if (coalesce) {
         uint32_t mine2 = 0;
@@ -794,6 +670,23 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         int per = nl >= min_leaves ? kSortSplitDefault : 0;
         if (const char *sp = std::getenv("BAOBZI_B200_SORT_SPLIT"))
             per = std::atoi(sp);
+        // Piggyback schedule (3D): the evaluation launch of chunk c carries phase B of chunk c+1 and phase A of chunk
+        // c+2 (bin_eval.cu).  Needs the split sort's buffers (one CTA per SM and phase) whatever the leaf count, a
+        // second set of perm / tile arrays, and the two shared-memory tables beside the evaluation's stages.
+        bool want_piggy = !is2d && nl < 0xFFFF && bin_eval_is_default(ws.variant) && bin_eval_piggy_P(dt.view.order) == P;
+        if (const char *pe = std::getenv("BAOBZI_B200_PIGGY"))
+            want_piggy = want_piggy && std::atoi(pe) != 0;
+        uint32_t piggy_sbin = 0;
+        if (want_piggy) {
+            piggy_sbin = dt.view.n_bins;
+            if (bin_eval_piggy_smem(dt.view.order, (uint32_t)nl, piggy_sbin) > 227 * 1024)
+                piggy_sbin = 0;
+            if (bin_eval_piggy_smem(dt.view.order, (uint32_t)nl, 0) > 227 * 1024)
+                want_piggy = false;
+        }
+        const bool split_wanted = per > 0;
+        if (want_piggy)
+            per = 1; // the standalone phase launches that start the pipeline use one CTA per SM, like the side jobs
         if (per > 0 && nl < 0xFFFF) { // 16-bit keys between the two launches
             const size_t hist = (size_t)nl * sizeof(uint32_t);
             const size_t tblb = ((size_t)dt.view.n_bins * sizeof(uint16_t) + 15) / 16 * 16;
@@ -801,7 +694,9 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             ws.split_smem_a = hist + (ws.split_sbin ? tblb : 0);
             ws.split_smem_b = hist;
             ws.split_ctas = dt.sm_count * per;
-            ws.split = true;
+            ws.split = split_wanted;
+            ws.piggy = want_piggy;
+            ws.piggy_sbin = piggy_sbin;
             cudaFuncAttributes fa;
             if (cudaFuncGetAttributes(&fa, sort_fn) == cudaSuccess) {
                 // both phases' CTAs must be resident together; never below 32 KB (a carve-out sized for a tree with a
@@ -819,7 +714,22 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
                     cudaFuncSetAttribute(fa2, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
                 }
             }
+            {   // trees above ~10 K leaves: the phase launches need more than the 48 KB a kernel gets without opting in
+                const void *fa1 = is2d ? (const void *)bin_sort_fused_kernel<2, false, 1> : (const void *)bin_sort_fused_kernel<3, false, 1>;
+                const void *fa2 = is2d ? (const void *)bin_sort_fused_kernel<2, false, 2> : (const void *)bin_sort_fused_kernel<3, false, 2>;
+                cudaFuncSetAttribute(fa1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
+                cudaFuncSetAttribute(fa2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
+            }
             e = alloc_split_buffers(ws, cwords, chunk, (size_t)nl);
+            if (e == cudaSuccess && ws.piggy) {
+                e = cudaMalloc((void **)&ws.alt_perm, sizeof(uint32_t) * ws.perm_capacity);
+                if (e == cudaSuccess)
+                    e = cudaMalloc((void **)&ws.alt_tile_leaf, sizeof(uint32_t) * ws.tile_capacity);
+                if (e == cudaSuccess)
+                    e = cudaMalloc((void **)&ws.alt_tile_info, sizeof(uint2) * ws.tile_capacity);
+                if (e == cudaSuccess)
+                    e = cudaMalloc((void **)&ws.alt_n_tiles, sizeof(uint32_t));
+            }
         }
     }
     if (e == cudaSuccess && ws.overlap) {
@@ -1010,12 +920,14 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
 
 // One phase of the split sort for one chunk (ordinary launch: the kernel never reaches its grid barrier).
 static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t phase, const double *d_x, double *d_res,
-                             uint32_t n, uint32_t *key, uint32_t *cur, uint32_t *next, uint32_t *base, cudaStream_t st) {
+                             uint32_t n, uint32_t *key, uint32_t *cur, uint32_t *next, uint32_t *base, cudaStream_t st,
+                             bool full_grid = false) {
     const TreeView &tv = dt.view;
     uint32_t grid = (uint32_t)ws.split_ctas;
     const uint32_t per_cta = (uint32_t)kSortThreads * kSortPts;
     const uint32_t useful = (n + per_cta - 1) / per_cta;
-    grid = grid < useful ? grid : (useful ? useful : 1u); // a function of n alone: the same for both phases of a chunk
+    if (!full_grid) // (the piggyback schedule pairs these launches with side jobs of a fixed grid: one CTA per SM)
+        grid = grid < useful ? grid : (useful ? useful : 1u); // a function of n alone: the same for both phases of a chunk
     const bool bybin = ws.bucketed; // bucketed path: key = grid cell >> bshift, no tile descriptors, no table
     const uint32_t TILE = bybin ? 1u : 32u * (uint32_t)ws.P;
     const size_t smem = phase == 1 ? ws.split_smem_a : ws.split_smem_b;
@@ -1120,6 +1032,93 @@ static int launch_eval_split(const DeviceTree &dt, BinWorkspace &ws, const doubl
     return rc ? rc : (int)cudaGetLastError();
 }
 
+// Piggyback schedule: after three standalone sort launches (phases A and B of chunk 0, phase A of chunk 1), launch c
+// evaluates chunk c and, between its tiles, scatters chunk c+1 and looks up chunk c+2.  One stream, no events; the
+// per-chunk cost is one launch.
+static int launch_eval_piggy(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
+                             cudaStream_t stream, int64_t *launches) {
+    const int dim = dt.view.dim;
+    const int64_t step = ws.chunk_limit > 0 && ws.chunk_limit < ws.chunk_capacity ? ws.chunk_limit : ws.chunk_capacity;
+    const int64_t nc = (n + step - 1) / step;
+    uint32_t *hist[3] = {ws.count, ws.cursor, ws.count3};
+    uint32_t *keys[2] = {ws.key, ws.alt_key};
+    uint32_t *perms[2] = {ws.perm, ws.alt_perm}, *tleaf[2] = {ws.tile_leaf, ws.alt_tile_leaf},
+             *ntl[2] = {ws.n_tiles, ws.alt_n_tiles};
+    uint2 *tinfo[2] = {ws.tile_info, ws.alt_tile_info};
+    auto use_set = [&](int k) {
+        ws.perm = perms[k];
+        ws.tile_leaf = tleaf[k];
+        ws.tile_info = tinfo[k];
+        ws.n_tiles = ntl[k];
+    };
+    auto chunk_n = [&](int64_t c) { return (uint32_t)(n - c * step < step ? n - c * step : step); };
+    StageProfile *pf = ws.prof;
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    if (pf) {
+        ev[0] = pf->get();
+        ev[1] = pf->get();
+        cudaEventRecord(ev[0], stream);
+    }
+    const int rot = ws.rot;
+    use_set(0);
+    int rc = launch_sort_phase(dt, ws, 1, d_x, d_res, chunk_n(0), keys[0], hist[rot % 3], nullptr, ws.base_tbl[0], stream, true);
+    if (rc == 0)
+        rc = launch_sort_phase(dt, ws, 2, d_x, d_res, chunk_n(0), keys[0], hist[rot % 3], hist[(rot + 2) % 3], ws.base_tbl[0],
+                               stream, true);
+    if (rc == 0 && nc > 1)
+        rc = launch_sort_phase(dt, ws, 1, d_x + dim * step, d_res + step, chunk_n(1), keys[1], hist[(rot + 1) % 3], nullptr,
+                               ws.base_tbl[1], stream, true);
+    if (launches)
+        *launches += nc > 1 ? 3 : 2;
+    if (pf) {
+        cudaEventRecord(ev[1], stream);
+        pf->spans.push_back({kStageLookup, ev[0], ev[1], (int64_t)chunk_n(0) + (nc > 1 ? (int64_t)chunk_n(1) : 0)});
+    }
+    for (int64_t c = 0; c < nc && rc == 0; ++c) {
+        PiggyArgs pg{};
+        pg.cshift = ws.cshift;
+        pg.sbin_n = ws.piggy_sbin;
+        if (c + 1 < nc) {
+            const int k = (int)((c + 1) & 1);
+            pg.nb = chunk_n(c + 1);
+            pg.key_b = reinterpret_cast<const uint16_t *>(keys[k]);
+            pg.count_b = hist[(rot + c + 1) % 3];
+            pg.count_clear = hist[(rot + c + 3) % 3];
+            pg.base_b = ws.base_tbl[k];
+            pg.perm_b = perms[k];
+            pg.tile_leaf_b = tleaf[k];
+            pg.tile_info_b = tinfo[k];
+            pg.n_tiles_b = ntl[k];
+        }
+        if (c + 2 < nc) {
+            const int k = (int)(c & 1);
+            pg.na = chunk_n(c + 2);
+            pg.xa = d_x + dim * (c + 2) * step;
+            pg.resa = d_res + (c + 2) * step;
+            pg.key_a = reinterpret_cast<uint16_t *>(keys[k]);
+            pg.count_a = hist[(rot + c + 2) % 3];
+            pg.base_a = ws.base_tbl[k];
+        }
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (pf) {
+            e0 = pf->get();
+            e1 = pf->get();
+            cudaEventRecord(e0, stream);
+        }
+        use_set((int)(c & 1));
+        rc = launch_bin_eval3d_piggy(dt, ws, d_x + dim * c * step, d_res + c * step, stream, pg);
+        if (pf) {
+            cudaEventRecord(e1, stream);
+            pf->spans.push_back({kStageEval, e0, e1, (int64_t)chunk_n(c)});
+        }
+        if (launches)
+            *launches += 1;
+    }
+    use_set(0);
+    ws.rot = (int)((rot + nc) % 3);
+    return rc ? rc : (int)cudaGetLastError();
+}
+
 int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
                        cudaStream_t stream, int64_t *launches) {
     if (n <= 0)
@@ -1128,6 +1127,8 @@ int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x
         return (int)cudaErrorInvalidValue;
     {   // the split sort pays when there is a next chunk to overlap with; a single chunk takes the one-launch sort
         const int64_t step = ws.chunk_limit > 0 && ws.chunk_limit < ws.chunk_capacity ? ws.chunk_limit : ws.chunk_capacity;
+        if (ws.piggy && n > step && dt.view.dim == 3)
+            return launch_eval_piggy(dt, ws, d_x, d_res, n, stream, launches);
         if (ws.split && n > step)
             return launch_eval_split(dt, ws, d_x, d_res, n, stream, launches);
     }

@@ -92,14 +92,36 @@ struct BinWorkspace {
     // key / alt_key and base_tbl[2] alternate between chunks; three histogram buffers rotate (A of chunk c fills
     // hist3[(rot+c)%3], B of chunk c reads it and clears hist3[(rot+c+2)%3], which chunk c+2 fills next).
     bool split = false;
+    bool piggy = false;        // the evaluation launches carry the sort of the following chunks (launch_eval_piggy)
     int split_ctas = 0;
-    uint32_t split_sbin = 0;
+    uint32_t split_sbin = 0, piggy_sbin = 0;
     size_t split_smem_a = 0, split_smem_b = 0;
     uint32_t *count3 = nullptr, *base_tbl[2] = {nullptr, nullptr};
     int rot = 0;
     uint32_t *alt_key = nullptr, *alt_perm = nullptr, *alt_tile_leaf = nullptr, *alt_n_tiles = nullptr;
     uint2 *alt_tile_info = nullptr;
 };
+
+// Side jobs an evaluation launch of chunk c carries for the chunks behind it (bin_eval.cu: bin_eval3d_piggy_kernel).
+struct PiggyArgs {
+    // phase B of chunk c+1 (nb == 0: none)
+    uint32_t nb;
+    const uint16_t *key_b;
+    const uint32_t *count_b;  // complete histogram of chunk c+1
+    uint32_t *count_clear;    // the buffer chunk c+3 will histogram into
+    const uint32_t *base_b;   // [CTA][leaf] bases reserved by phase A of chunk c+1
+    uint32_t *perm_b, *tile_leaf_b, *n_tiles_b;
+    uint2 *tile_info_b;
+    // phase A of chunk c+2 (na == 0: none)
+    uint32_t na;
+    const double *xa;
+    double *resa;
+    uint16_t *key_a;
+    uint32_t *count_a, *base_a;
+    int cshift;
+    uint32_t sbin_n; // entries of the 16-bit bin_leaf table staged in shared memory (0: gathered through L1)
+};
+
 
 struct DeviceTree {
     int device = -1;

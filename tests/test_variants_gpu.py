@@ -21,6 +21,11 @@ VARIANTS = [
     {"BAOBZI_B200_SORT_SPLIT": "1"},         # split sort forced (the default only from 2048 leaves; fixtures are smaller)
     {"BAOBZI_B200_SORT_SPLIT": "2"},         # split sort, two CTAs per SM and phase
     {"BAOBZI_B200_SORT_SBIN": "0"},          # bin_leaf gathered through L1 instead of shared memory
+    {"BAOBZI_B200_PIGGY": "0"},              # sort launches of their own instead of side jobs of the evaluation (round 1 schedule)
+    {"BAOBZI_B200_PIGGY": "0", "BAOBZI_B200_SORT_SPLIT": "1"},
+    {"BAOBZI_B200_K4": "4,8,1,1,1"},         # T(z) advanced on the fly
+    {"BAOBZI_B200_K4": "3,12,1,1,1"},
+    {"BAOBZI_B200_K4": "4,12,1,0,1"},
 ]
 
 
@@ -53,6 +58,70 @@ def test_variant_bits(gpu_lib, ref, env):
                 os.environ.pop(k, None)
             else:
                 os.environ[k] = v
+
+
+SHARED = [("t3d_o12", "3,8,0,0,2"), ("t3d_o12", "2,12,0,1,2"), ("t3d_o12", "3,12,1,0,2"),
+          ("t3d_o14", "2,8,0,1,2"), ("t3d_o14", "3,8,1,0,2"), ("t3d_o14", "2,12,1,0,2"),
+          ("t3d_o16", "2,8,0,1,2"), ("t3d_o16", "2,8,0,0,2"), ("t3d_o16", "2,12,1,0,2")]
+
+
+@pytest.mark.parametrize("name,k4", SHARED)
+def test_cta_shared_tma_block_variants(gpu_lib, ref, name, k4, monkeypatch):
+    """High orders with the leaf block staged once per CTA by the TMA engine (cp.async.bulk + mbarrier, run = 2): same
+    bits as the oracle, over one chunk and several, with points outside the domain and ragged sizes."""
+    import torch
+    from conftest import load_golden
+    from test_parity_gpu import ulp
+    path, g = load_golden(name)
+    t = ref.OracleTree(path)
+    a = t.arrays()
+    rng = np.random.default_rng(13)
+    n = 150_001
+    x = a["lower_left"] + rng.random((n, 3)) * (a["upper_right"] - a["lower_left"]) * 1.01 - 0.005
+    want = t.eval_multi(x, ref.ARITH_AVX2)
+    xd = torch.from_numpy(x).cuda()
+    monkeypatch.setenv("BAOBZI_B200_K4", k4)
+    b = gpu_lib.Baobzi(filename=path, mode="binned")
+    for chunk, m in ((0, n), (40_003, n), (0, 97), (0, 1)):
+        b.set_mode("binned", chunk)
+        y = b(xd[:m].contiguous())
+        torch.cuda.synchronize()
+        assert ulp(ref, y.cpu().numpy(), want[:m]) == 0, (k4, chunk, m)
+    assert ulp(ref, b(torch.from_numpy(g["x"]).cuda()).cpu().numpy(), g["y_avx2"]) == 0   # the golden edge points
+    b.free()
+
+
+def test_piggyback_schedule_ragged_chunks(gpu_lib, ref):
+    """The evaluation launches carry the sort of the following chunks: chunk counts 2, 3, many; a last chunk of one
+    point; most points outside the domain (few tiles: the side jobs finish in the tail loops); every point in one leaf."""
+    import torch
+    from conftest import load_golden
+    from test_parity_gpu import ulp
+    for name in ("t3d_o8", "t3d_o12", "tc_3d"):
+        path, g = load_golden(name)
+        t = ref.OracleTree(path)
+        a = t.arrays()
+        lo, hi = a["lower_left"], a["upper_right"]
+        rng = np.random.default_rng(29)
+        n = 200_001
+        cases = {
+            "uniform": lo + rng.random((n, 3)) * (hi - lo),
+            "mostly_outside": lo + (rng.random((n, 3)) * 3.0 - 1.0) * (hi - lo),
+            "one_leaf": lo + (0.4 + 1e-6 * rng.random((n, 3))) * (hi - lo),
+        }
+        b = gpu_lib.Baobzi(filename=path, mode="binned")
+        for tag, x in cases.items():
+            want = t.eval_multi(x, ref.ARITH_AVX2)
+            xd = torch.from_numpy(np.ascontiguousarray(x)).cuda()
+            for chunk in (100_001, 66_667, 50_000, 9_973):   # 2 chunks, 3 + one point, 4 + one point, 21
+                b.set_mode("binned", chunk)
+                y = b(xd)
+                torch.cuda.synchronize()
+                assert ulp(ref, y.cpu().numpy(), want) == 0, (name, tag, chunk)
+                y2 = b(xd)                                    # again: the rotating buffers carry over between calls
+                torch.cuda.synchronize()
+                assert torch.equal(y2.view(torch.int64), y.view(torch.int64)), (name, tag, chunk)
+        b.free()
 
 
 def test_bucketed_on_refined_tree(gpu_lib, ref):
