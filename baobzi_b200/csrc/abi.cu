@@ -36,8 +36,9 @@ struct ExecContext {
     double *h_x = nullptr, *h_res = nullptr; // pinned staging for pageable caller memory
     int64_t staged_points = 0;
     BinWorkspace ws;
-    double *pinned = nullptr; // scalar eval scratch: x[3] then y[out_dim]
+    double *pinned = nullptr; // scalar eval scratch: x[3], completion word, y[out_dim]
     size_t pinned_doubles = 0;
+    unsigned long long scalar_seq = 0;
     bool busy = false;
 };
 
@@ -288,6 +289,11 @@ int eval_device(Function *f, Replica *r, BinWorkspace &ws, const double *d_x, do
     return rc;
 }
 
+int env_int(const char *name, int dflt) {
+    const char *s = std::getenv(name);
+    return s && *s ? std::atoi(s) : dflt;
+}
+
 void fill_nan(double *res, int64_t n) {
     for (int64_t i = 0; i < n; ++i)
         res[i] = NAN;
@@ -324,29 +330,48 @@ void fn_eval(const void *obj, const double *x, double *y) {
     }
     DeviceGuard g(r->dt.device);
     bool bad = false;
-    if (c->pinned_doubles < (size_t)(3 + od)) {
+    // scratch in mapped pinned memory: x[3] | completion word | y[od]
+    if (c->pinned_doubles < (size_t)(4 + od)) {
         if (c->pinned)
             cudaFreeHost(c->pinned);
         c->pinned = nullptr;
-        bad = report(cudaHostAlloc((void **)&c->pinned, sizeof(double) * (3 + od), cudaHostAllocMapped), "pinned alloc");
-        c->pinned_doubles = bad ? 0 : (size_t)(3 + od);
+        bad = report(cudaHostAlloc((void **)&c->pinned, sizeof(double) * (4 + od), cudaHostAllocMapped), "pinned alloc");
+        c->pinned_doubles = bad ? 0 : (size_t)(4 + od);
+        c->scalar_seq = 0;
+        if (!bad)
+            std::memset(c->pinned, 0, sizeof(double) * (4 + od));
     }
     if (!bad) {
-        // zero-copy: the kernel reads the point from and writes the values to mapped pinned memory
+        // zero-copy: the kernel reads the point from and writes the values to mapped pinned memory, then publishes a
+        // sequence number there; the host polls that word (no driver call on the way back) and only falls back to a
+        // stream synchronisation when it does not show up -- which is also how a launch error surfaces
+        static const bool spin = env_int("BAOBZI_B200_SCALAR_SPIN", 1) != 0;
+        volatile unsigned long long *done = reinterpret_cast<volatile unsigned long long *>(c->pinned + 3);
+        double *yv = c->pinned + 4;
         for (int j = 0; j < f->host.dim; ++j)
             c->pinned[j] = x[j];
         for (int k = 0; k < od; ++k)
-            c->pinned[3 + k] = NAN;
+            yv[k] = NAN;
+        const unsigned long long seq = ++c->scalar_seq;
         int64_t launches = 0;
-        int rc = launch_eval_scalar(r->dt, c->pinned, c->pinned + 3, c->stream, &launches);
+        int rc = launch_eval_scalar(r->dt, c->pinned, yv, c->stream, &launches,
+                                    spin ? const_cast<unsigned long long *>(done) : nullptr, seq);
         f->launches += launches;
-        bad = report((cudaError_t)rc, "scalar eval launch") || report(cudaStreamSynchronize(c->stream), "scalar eval");
+        bad = report((cudaError_t)rc, "scalar eval launch");
+        bool seen = false;
+        if (!bad && spin) {
+            for (int it = 0; it < 2000000 && !seen; ++it) // ~ a few hundred ms at most, normally < 10 us
+                seen = *done == seq;
+            std::atomic_thread_fence(std::memory_order_acquire);
+        }
+        if (!bad && !seen)
+            bad = report(cudaStreamSynchronize(c->stream), "scalar eval");
+        if (!bad)
+            for (int k = 0; k < od; ++k)
+                y[k] = yv[k];
     }
     if (bad)
         fill_nan(y, od);
-    else
-        for (int k = 0; k < od; ++k)
-            y[k] = c->pinned[3 + k];
     release(f, c);
 }
 
@@ -448,11 +473,6 @@ bool is_pageable(const void *p) {
         return true;
     }
     return a.type == cudaMemoryTypeUnregistered;
-}
-
-int env_int(const char *name, int dflt) {
-    const char *s = std::getenv(name);
-    return s && *s ? std::atoi(s) : dflt;
 }
 
 void fn_eval_multi(const void *obj, const double *x, double *res, int ntrg) {

@@ -161,7 +161,8 @@ int launch_eval_all_1d(const DeviceTree &dt, const double *d_x, double *d_res, i
 int measure_fp64_peak(double *tflops, int repeats);
 int measure_fp64_peak_sustained(double *tflops, double seconds);
 // Scalar twin: x[dim] -> y[out_dim] (reference Function::eval(x, res), template.hpp:851-860).
-int launch_eval_scalar(const DeviceTree &dt, const double *d_x, double *d_y, cudaStream_t stream, int64_t *launches);
+int launch_eval_scalar(const DeviceTree &dt, const double *d_x, double *d_y, cudaStream_t stream, int64_t *launches,
+                       unsigned long long *d_done = nullptr, unsigned long long seq = 0);
 // Binned path over n points in chunks of ws.chunk_capacity: sort by leaf (lookup+histogram, padded scan, scatter), evaluation.
 int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
                        cudaStream_t stream, int64_t *launches);

@@ -199,7 +199,7 @@ eval_bucket_kernel(const TreeView tv, const double *__restrict__ x, double *__re
 // ORDER... the reference indexes `coeffs + coeff_offset + k*ORDER` for every DIM; only DIM == 1 is
 // meaningful and for DIM > 1 we evaluate component 0 only.
 template <int DIM, int ORDER>
-__global__ void eval_scalar_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ y) {
+__device__ __forceinline__ void eval_scalar_body(const TreeView &tv, const double *__restrict__ x, double *__restrict__ y) {
     const uint32_t k = threadIdx.x;
     if (k >= tv.out_dim)
         return;
@@ -222,6 +222,22 @@ __global__ void eval_scalar_kernel(const TreeView tv, const double *__restrict__
     } else {
         if (k == 0)
             y[0] = eval_leaf<DIM, ORDER>(tv, node, head, p);
+    }
+}
+
+// `done` (optional, mapped pinned memory like x and y): set to `seq` once every component is written and visible to
+// the host, which polls it instead of paying a stream synchronisation per point.
+template <int DIM, int ORDER>
+__global__ void eval_scalar_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ y,
+                                   volatile unsigned long long *done, unsigned long long seq) {
+    eval_scalar_body<DIM, ORDER>(tv, x, y);
+    if (done) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            *done = seq;
+            __threadfence_system();
+        }
     }
 }
 
@@ -338,9 +354,11 @@ int launch_eval_all_1d(const DeviceTree &dt, const double *d_x, double *d_res, i
     return (int)cudaGetLastError();
 }
 
-int launch_eval_scalar(const DeviceTree &dt, const double *d_x, double *d_y, cudaStream_t stream, int64_t *launches) {
+int launch_eval_scalar(const DeviceTree &dt, const double *d_x, double *d_y, cudaStream_t stream, int64_t *launches,
+                       unsigned long long *d_done, unsigned long long seq) {
     const unsigned threads = dt.view.out_dim < 1 ? 1 : (dt.view.out_dim > 1024 ? 1024 : dt.view.out_dim);
-    BZ_DISPATCH(dt.view.dim, dt.view.order, (eval_scalar_kernel<D, O><<<1, threads, 0, stream>>>(dt.view, d_x, d_y)));
+    BZ_DISPATCH(dt.view.dim, dt.view.order,
+                (eval_scalar_kernel<D, O><<<1, threads, 0, stream>>>(dt.view, d_x, d_y, d_done, seq)));
     if (launches)
         *launches += 1;
     return (int)cudaGetLastError();

@@ -1,6 +1,5 @@
 # round 2, GPU call B: new kernels -- parity first, then A/B sweeps (all device-resident, 2e8 points unless noted)
 set -o pipefail
-timeout 1500 python -m pytest tests/test_variants_gpu.py tests/test_scale_gpu.py tests/test_parity_gpu.py -m gpu -q -x --durations=8 > gpurun_out/r2b_pytest.log 2>&1; tail -12 gpurun_out/r2b_pytest.log
 B="python bench.py --no-cpu --no-e2e --no-extra --no-parity --steps 3"
 run() { # label, env..., -- args
   label=$1; shift
