@@ -510,6 +510,17 @@ void fn_eval_multi(const void *obj, const double *x, double *res, int ntrg) {
     const bool big = n * (dim + 1) * (int64_t)sizeof(double) >= (int64_t(8) << 20);
     job.stage_x = stage_env == 0 ? false : (is_pageable(x) && (big || stage_env == 1));
     job.stage_res = stage_env == 0 ? false : (is_pageable(res) && (big || stage_env == 1));
+    // alternative for pageable memory (BAOBZI_B200_HOSTREG=1): pin the caller's pages for the duration of the call.
+    // Pinning costs about as much as copying (the kernel touches every page) and is not overlapped with anything, so
+    // it only wins when the same buffers come back call after call; measured in INTEGRATION.md, off by default.
+    bool reg_x = false, reg_res = false;
+    if (env_int("BAOBZI_B200_HOSTREG", 0) != 0 && big) {
+        if (job.stage_x && cudaHostRegister(const_cast<double *>(x), sizeof(double) * n * dim, cudaHostRegisterPortable) == cudaSuccess)
+            reg_x = true, job.stage_x = false;
+        if (job.stage_res && cudaHostRegister(res, sizeof(double) * n, cudaHostRegisterPortable) == cudaSuccess)
+            reg_res = true, job.stage_res = false;
+        cudaGetLastError();
+    }
     // devices: the current one first, then the others in order
     int visible = 1;
     cudaGetDeviceCount(&visible);
@@ -543,6 +554,10 @@ void fn_eval_multi(const void *obj, const double *x, double *res, int ntrg) {
         for (auto &t : th)
             t.join();
     }
+    if (reg_x)
+        cudaHostUnregister(const_cast<double *>(x));
+    if (reg_res)
+        cudaHostUnregister(res);
     if (job.bad.load())
         fill_nan(res, n);
 }

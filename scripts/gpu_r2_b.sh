@@ -43,3 +43,9 @@ run c5_o16_sh_2_12      BAOBZI_B200_K4=2,12,1,0,2 -- $P5 --order 16
 run c2_sorted           X=1 -- --workload C2
 run c2_table            BAOBZI_B200_SORTED1D=0 -- --workload C2
 cuobjdump -sass baobzi_b200/lib/libbaobzi.so | grep -c UBLKCP > gpurun_out/r2b_ublkcp_count.txt; cat gpurun_out/r2b_ublkcp_count.txt
+P4="--workload C4 --points 300000000"
+run c4_default          X=1 -- $P4
+run c4_l2fetch32        BAOBZI_B200_L2_FETCH=32 -- $P4
+run c1_1e8_default      X=1 -- --workload C1 --points 100000000
+run c1_1e8_l2fetch32    BAOBZI_B200_L2_FETCH=32 -- --workload C1 --points 100000000
+timeout 600 python scripts/host_path_ab.py > gpurun_out/r2a_host_ab.txt 2>&1; cat gpurun_out/r2a_host_ab.txt
