@@ -399,49 +399,41 @@ bin_eval3d_piggy_kernel(const TreeView tv, const double *__restrict__ x, double 
                 } else {
                     pg.resa[a_pos + q] = __longlong_as_double(0x7ff8000000000000ll);
                 }
-                pg.key_a[a_pos + q] = (uint16_t)leaf[j]; // kNotLeaf -> 0xFFFF
             }
         }
         const bool heavy = keys_repeat(leaf[0], lane);
 #pragma unroll
-        for (int j = 0; j < KS; ++j)
-            grouped_add(hist_a, leaf[j], heavy, lane);
+        for (int j = 0; j < KS; ++j) {
+            const uint32_t rank = grouped_add(hist_a, leaf[j], heavy, lane); // rank inside (CTA, leaf)
+            const uint32_t q = j * 32 + lane;
+            if (q < m)
+                pg.key_a[a_pos + q] = leaf[j] == kNotLeaf ? kKeyNoLeaf : (leaf[j] | (rank << kKeyLeafBits));
+        }
         a_pos += m;
     };
-    // phase B: four keys per lane (one 8-byte load, requested before the tile), slot = next free one of the leaf
-    auto b_request = [&]() -> uint2 {
+    // phase B: four packed keys per lane (one 16-byte load, requested before the tile); slot = tbl_b[leaf] + rank, no atomics
+    auto b_request = [&]() -> uint4 {
         if (b_pos + 4 * lane < b_end) // ranges are multiples of 8 except the chunk's very end (the buffer is padded)
-            return __ldcs(reinterpret_cast<const uint2 *>(pg.key_b + b_pos) + lane);
-        return make_uint2(~0u, ~0u);
+            return __ldcs(reinterpret_cast<const uint4 *>(pg.key_b + b_pos) + lane);
+        return make_uint4(kKeyNoLeaf, kKeyNoLeaf, kKeyNoLeaf, kKeyNoLeaf);
     };
-    auto b_consume = [&](const uint2 kk) {
+    auto b_consume = [&](const uint4 kk) {
         if (b_pos >= b_end)
             return;
-        const uint32_t w[2] = {kk.x, kk.y};
-        uint32_t k[4];
+        const uint32_t w[4] = {kk.x, kk.y, kk.z, kk.w};
+        const uint32_t i0 = b_pos + 4 * lane;
+        uint32_t slot[4];
+        bool ok[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const uint32_t v = (w[j / 2] >> (16 * (j & 1))) & 0xFFFFu;
-            k[j] = v == 0xFFFFu || b_pos + 4 * lane + j >= b_end ? kNotLeaf : v;
+            const uint32_t leaf = w[j] & kKeyNoLeaf;
+            ok[j] = leaf != kKeyNoLeaf && i0 + j < b_end;
+            slot[j] = ok[j] ? tbl_b[leaf] + (w[j] >> kKeyLeafBits) : 0u;
         }
-        const uint32_t i0 = b_pos + 4 * lane;
-        if (!keys_repeat(k[0], lane)) {
-            uint32_t slot[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-                slot[j] = k[j] != kNotLeaf ? atomicAdd(tbl_b + k[j], 1u) : 0u;
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-                if (k[j] != kNotLeaf)
-                    pg.perm_b[slot[j]] = i0 + j;
-        } else {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const uint32_t slot = grouped_add(tbl_b, k[j], true, lane);
-                if (k[j] != kNotLeaf)
-                    pg.perm_b[slot] = i0 + j;
-            }
-        }
+        for (int j = 0; j < 4; ++j)
+            if (ok[j])
+                pg.perm_b[slot[j]] = i0 + j;
         b_pos = min(b_pos + (uint32_t)kPiggySlice, b_end);
     };
 
@@ -501,7 +493,7 @@ bin_eval3d_piggy_kernel(const TreeView tv, const double *__restrict__ x, double 
         const uint2 info_next = info_n;
         load_meta(t + 2, info_n, idx_n);
         a_request();                 // the slice's points: land while this tile computes
-        const uint2 kk = b_request(); // ... and its keys
+        const uint4 kk = b_request(); // ... and its keys
         if (info_cur.x != cur_node) { // warp uniform: a new leaf starts here
             cur_node = info_cur.x;
             fetch_leaf(info_cur);
@@ -521,7 +513,7 @@ bin_eval3d_piggy_kernel(const TreeView tv, const double *__restrict__ x, double 
     cp_async_wait<0>();
     // whatever the tiles did not cover (chunks with few tiles: most points outside the domain, a short last chunk)
     while (b_pos < b_end) {
-        const uint2 kk = b_request();
+        const uint4 kk = b_request();
         b_consume(kk);
     }
     while (a_pos < a_end) {
@@ -1168,12 +1160,15 @@ static const K4Variant kVariants[] = {
     BZ_K4(10, 3, 12, false, false, true),
     BZ_K4(12, 3, 8, false, false, true),  BZ_K4(12, 2, 4, false, true, false),  BZ_K4(12, 3, 4, false, false, false),
     BZ_K4(12, 2, 8, false, true, true),   BZ_K4(12, 2, 12, false, false, true),
+    // orders 14 and 16 default to the CTA-shared, TMA-staged block (run = 2): measured on B200 with the order-12 benchmark
+    // function at these orders, 1e8 points (profiles/r02_sweep.txt): order 14 0.727 of the FP64 peak with P = 3, T(z) on the
+    // fly (4.22e9 evals/s; per-warp copies, 8 warps: 3.9e9), order 16 0.727 with P = 2, 8 warps (2.95e9; per-warp copies
+    // allow 4 warps: 2.70e9).  Order 12 gains nothing (0.723 against 0.727) and keeps its per-warp copies.
+    BZ_K4S(14, 3, 8, true, false),   BZ_K4S(14, 2, 8, false, true),   BZ_K4S(14, 2, 12, true, false),
     BZ_K4(14, 2, 8, false, true, true),   BZ_K4(14, 2, 4, false, true, false),  BZ_K4(14, 3, 8, true, false, true),
-    BZ_K4(16, 2, 4, false, true, true),   BZ_K4(16, 2, 2, false, true, false),  BZ_K4(16, 2, 6, false, false, true),
-    // CTA-shared, TMA-staged block (run = 2)
-    BZ_K4S(12, 3, 8, false, false),  BZ_K4S(12, 3, 12, true, false),  BZ_K4S(12, 2, 12, false, true),
-    BZ_K4S(14, 2, 8, false, true),   BZ_K4S(14, 3, 8, true, false),   BZ_K4S(14, 2, 12, true, false),
     BZ_K4S(16, 2, 8, false, true),   BZ_K4S(16, 2, 8, false, false),  BZ_K4S(16, 2, 12, true, false),
+    BZ_K4(16, 2, 4, false, true, true),   BZ_K4(16, 2, 2, false, true, false),  BZ_K4(16, 2, 6, false, false, true),
+    BZ_K4S(12, 3, 8, false, false),  BZ_K4S(12, 3, 12, true, false),  BZ_K4S(12, 2, 12, false, true),
 };
 #undef BZ_K4S
 #undef BZ_K4

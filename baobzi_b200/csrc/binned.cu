@@ -171,9 +171,11 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
 #pragma unroll
         for (int u = 0; u < kSortPts; ++u) {
             const uint32_t i = i0 + u * nthr;
+            // rank of the point inside (this CTA, its leaf): what the histogram update returns (lanes past the end hold kNotLeaf)
+            const uint32_t rank = grouped_add(tbl, leaf[u], heavy, lane_id);
             if (have[u]) {
-                if (PHASE == 1)
-                    reinterpret_cast<uint16_t *>(key)[i] = (uint16_t)leaf[u]; // n_leaves < 0xFFFF in split mode
+                if (PHASE == 1) // split mode: leaf and rank travel together, the scatter launch needs no atomics
+                    key[i] = leaf[u] == kNotLeaf ? kKeyNoLeaf : (leaf[u] | (rank << kKeyLeafBits));
                 else if (use_skey && !coalesce)
                     skey[i - lo] = (uint16_t)leaf[u]; // kNotLeaf -> 0xFFFF (n_leaves < 0xFFFF when skey_cap > 0)
                 else
@@ -181,7 +183,6 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
                 if (leaf[u] == kNotLeaf)
                     res[i] = __longlong_as_double(0x7ff8000000000000ll);
             }
-            grouped_add(tbl, leaf[u], heavy, lane_id); // lanes past the end hold kNotLeaf
         }
     }
     __syncthreads();
@@ -270,45 +271,36 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     }
     if constexpr (PHASE == 2) {
         // Keys come from global memory (written by phase A's launch, mostly evicted from L2 by the points it streamed
-        // afterwards): eight 16-bit keys per 128-bit load, requested two iterations ahead.  With one 4-byte key per
-        // load and no lookahead this loop sat on the load (ncu: half of the kernel's stall samples on its first use).
-        const uint16_t *k16 = reinterpret_cast<const uint16_t *>(key);
+        // afterwards), eight per thread and iteration as two 128-bit loads requested two iterations ahead.  A key carries
+        // the leaf AND the point's rank inside (CTA, leaf) -- the value phase A's histogram atomic returned -- so the slot is
+        // tbl[leaf] + rank: a plain shared-memory load.  (Round 1 took a second shared atomic per point here; at 2 cycles
+        // per lane the two atomics per point WERE the sort's duration: 16.8 M of them per 8.4 M-point chunk = 115 us.)
         constexpr uint32_t KPT = 8;
         const uint32_t per_it = KPT * nthr;
-        auto ld = [&](uint32_t b) -> uint4 {
-            const uint32_t i = b + KPT * tid;
-            return b < hi && i < hi ? __ldcs(reinterpret_cast<const uint4 *>(k16 + i)) : make_uint4(~0u, ~0u, ~0u, ~0u);
+        auto ld = [&](uint32_t b, int half) -> uint4 {
+            const uint32_t i = b + KPT * tid + 4 * half;
+            return b < hi && i < hi ? __ldcs(reinterpret_cast<const uint4 *>(key + i)) : make_uint4(kKeyNoLeaf, kKeyNoLeaf, kKeyNoLeaf, kKeyNoLeaf);
         };
-        uint4 q0 = ld(lo), q1 = ld(lo + per_it);
+        uint4 q0a = ld(lo, 0), q0b = ld(lo, 1), q1a = ld(lo + per_it, 0), q1b = ld(lo + per_it, 1);
         for (uint32_t b0 = lo; b0 < hi; b0 += per_it) {
-            const uint4 q = q0;
-            q0 = q1;
-            q1 = ld(b0 + 2 * per_it);
-            const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+            const uint32_t w[KPT] = {q0a.x, q0a.y, q0a.z, q0a.w, q0b.x, q0b.y, q0b.z, q0b.w};
+            q0a = q1a;
+            q0b = q1b;
+            q1a = ld(b0 + 2 * per_it, 0);
+            q1b = ld(b0 + 2 * per_it, 1);
             const uint32_t i0 = b0 + KPT * tid;
-            uint32_t k[KPT];
+            uint32_t slot[KPT];
+            bool ok[KPT];
 #pragma unroll
             for (int j = 0; j < (int)KPT; ++j) {
-                const uint32_t v = (w[j / 2] >> (16 * (j & 1))) & 0xFFFFu;
-                k[j] = v == 0xFFFFu || i0 + j >= hi ? kNotLeaf : v;
+                const uint32_t leaf = w[j] & kKeyNoLeaf;
+                ok[j] = leaf != kKeyNoLeaf && i0 + j < hi;
+                slot[j] = ok[j] ? tbl[leaf] + (w[j] >> kKeyLeafBits) : 0u;
             }
-            if (!keys_repeat(k[0], lane)) { // the usual case, kept free of branches: eight atomics in flight, then eight stores
-                uint32_t slot[KPT];
 #pragma unroll
-                for (int j = 0; j < (int)KPT; ++j)
-                    slot[j] = k[j] != kNotLeaf ? atomicAdd(tbl + k[j], 1u) : 0u;
-#pragma unroll
-                for (int j = 0; j < (int)KPT; ++j)
-                    if (k[j] != kNotLeaf)
-                        perm[slot[j]] = i0 + j;
-            } else {
-#pragma unroll
-                for (int j = 0; j < (int)KPT; ++j) {
-                    const uint32_t slot = grouped_add(tbl, k[j], true, lane);
-                    if (k[j] != kNotLeaf)
-                        perm[slot] = i0 + j;
-                }
-            }
+            for (int j = 0; j < (int)KPT; ++j)
+                if (ok[j])
+                    perm[slot[j]] = i0 + j;
         }
         return;
     }
@@ -673,9 +665,14 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         // Piggyback schedule (3D): the evaluation launch of chunk c carries phase B of chunk c+1 and phase A of chunk
         // c+2 (bin_eval.cu).  Needs the split sort's buffers (one CTA per SM and phase) whatever the leaf count, a
         // second set of perm / tile arrays, and the two shared-memory tables beside the evaluation's stages.
-        bool want_piggy = !is2d && nl < 0xFFFF && bin_eval_is_default(ws.variant) && bin_eval_piggy_P(dt.view.order) == P;
-        if (const char *pe = std::getenv("BAOBZI_B200_PIGGY"))
-            want_piggy = want_piggy && std::atoi(pe) != 0;
+        // packed keys (sort_common.cuh): 15 bits of leaf, 17 bits of rank inside (CTA, leaf)
+        const bool keys_fit = nl < (int64_t)kKeyNoLeaf && chunk / dt.sm_count + 16 < (int64_t(1) << (32 - kKeyLeafBits));
+        bool want_piggy = !is2d && keys_fit && bin_eval_is_default(ws.variant) && bin_eval_piggy_P(dt.view.order) == P;
+        // Opt-in (BAOBZI_B200_PIGGY=1): measured slower than the split sort (DESIGN.md 4.2d has the numbers and why)
+        {
+            const char *pe = std::getenv("BAOBZI_B200_PIGGY");
+            want_piggy = want_piggy && pe && std::atoi(pe) != 0;
+        }
         uint32_t piggy_sbin = 0;
         if (want_piggy) {
             piggy_sbin = dt.view.n_bins;
@@ -687,7 +684,7 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
         const bool split_wanted = per > 0;
         if (want_piggy)
             per = 1; // the standalone phase launches that start the pipeline use one CTA per SM, like the side jobs
-        if (per > 0 && nl < 0xFFFF) { // 16-bit keys between the two launches
+        if (per > 0 && keys_fit) { // leaf + rank in one 32-bit key between the two launches
             const size_t hist = (size_t)nl * sizeof(uint32_t);
             const size_t tblb = ((size_t)dt.view.n_bins * sizeof(uint16_t) + 15) / 16 * 16;
             ws.split_sbin = nl < 0xFFFFu && hist + tblb <= kFusedSortMaxSmem ? dt.view.n_bins : 0u;
@@ -1081,7 +1078,7 @@ static int launch_eval_piggy(const DeviceTree &dt, BinWorkspace &ws, const doubl
         if (c + 1 < nc) {
             const int k = (int)((c + 1) & 1);
             pg.nb = chunk_n(c + 1);
-            pg.key_b = reinterpret_cast<const uint16_t *>(keys[k]);
+            pg.key_b = keys[k];
             pg.count_b = hist[(rot + c + 1) % 3];
             pg.count_clear = hist[(rot + c + 3) % 3];
             pg.base_b = ws.base_tbl[k];
@@ -1095,7 +1092,7 @@ static int launch_eval_piggy(const DeviceTree &dt, BinWorkspace &ws, const doubl
             pg.na = chunk_n(c + 2);
             pg.xa = d_x + dim * (c + 2) * step;
             pg.resa = d_res + (c + 2) * step;
-            pg.key_a = reinterpret_cast<uint16_t *>(keys[k]);
+            pg.key_a = keys[k];
             pg.count_a = hist[(rot + c + 2) % 3];
             pg.base_a = ws.base_tbl[k];
         }
@@ -1268,7 +1265,7 @@ int alloc_bucket_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws
         int per = (int64_t)ws.n_keys >= kSortSplitMinLeaves ? kSortSplitDefault : 0;
         if (const char *sp = std::getenv("BAOBZI_B200_SORT_SPLIT"))
             per = std::atoi(sp);
-        if (per > 0 && ws.n_keys < 0xFFFF) {
+        if (per > 0 && ws.n_keys < kKeyNoLeaf && chunk / dt.sm_count + 16 < (int64_t(1) << (32 - kKeyLeafBits))) {
             const size_t hist = (size_t)ws.n_keys * sizeof(uint32_t);
             ws.split_sbin = 0;
             ws.split_smem_a = ws.split_smem_b = hist;

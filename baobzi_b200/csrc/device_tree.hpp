@@ -106,7 +106,7 @@ struct BinWorkspace {
 struct PiggyArgs {
     // phase B of chunk c+1 (nb == 0: none)
     uint32_t nb;
-    const uint16_t *key_b;
+    const uint32_t *key_b;    // packed keys (sort_common.cuh: leaf | rank << 15)
     const uint32_t *count_b;  // complete histogram of chunk c+1
     uint32_t *count_clear;    // the buffer chunk c+3 will histogram into
     const uint32_t *base_b;   // [CTA][leaf] bases reserved by phase A of chunk c+1
@@ -116,7 +116,7 @@ struct PiggyArgs {
     uint32_t na;
     const double *xa;
     double *resa;
-    uint16_t *key_a;
+    uint32_t *key_a;
     uint32_t *count_a, *base_a;
     int cshift;
     uint32_t sbin_n; // entries of the 16-bit bin_leaf table staged in shared memory (0: gathered through L1)

@@ -162,6 +162,7 @@ eval_table_1d_kernel(const TreeView tv, const double *__restrict__ x, double *__
 constexpr int kU1MaxLeaves = 16;
 constexpr int kU1Threads = 256, kU1P = 4, kU1Tile = kU1Threads * kU1P;
 constexpr int kU1MaxNodes = 64, kU1MaxBins = 64;
+constexpr int kU1MinCtas = 6; // resident CTAs per SM asked of ptxas (register budget 42)
 
 struct U1Coef { // by value: lives in the constant bank of the launch
     double c[kU1MaxLeaves][16];
@@ -191,26 +192,29 @@ __device__ __forceinline__ void u1_run(const U1Coef &cf, const double *s_u, cons
     }
 }
 
+// the runs of the leaves one after the other; `run` = first slot of leaf LEAF (CTA uniform, carried along)
 template <int ORDER, int LEAF>
-__device__ __forceinline__ void u1_leaves(const U1Coef &cf, uint32_t n_leaves, const uint32_t *s_start, const double *s_u,
-                                          const uint16_t *s_org, double *s_val) {
+__device__ __forceinline__ uint32_t u1_leaves(const U1Coef &cf, uint32_t n_leaves, const uint32_t *s_tot, uint32_t run,
+                                              const double *s_u, const uint16_t *s_org, double *s_val) {
     if constexpr (LEAF < kU1MaxLeaves) {
         if (LEAF < n_leaves) { // CTA uniform
-            u1_run<ORDER, LEAF>(cf, s_u, s_org, s_val, s_start[LEAF], s_start[LEAF + 1]);
-            u1_leaves<ORDER, LEAF + 1>(cf, n_leaves, s_start, s_u, s_org, s_val);
+            const uint32_t end = run + s_tot[LEAF];
+            u1_run<ORDER, LEAF>(cf, s_u, s_org, s_val, run, end);
+            return u1_leaves<ORDER, LEAF + 1>(cf, n_leaves, s_tot, end, s_u, s_org, s_val);
         }
     }
+    return run;
 }
 
-template <int ORDER>
-__global__ void __launch_bounds__(kU1Threads)
+template <int ORDER, int MINCTAS>
+__global__ void __launch_bounds__(kU1Threads, MINCTAS)
 eval_sorted_1d_kernel(const TreeView tv, const U1Coef cf, const double *__restrict__ x, double *__restrict__ res,
                       int64_t n, int64_t n_tiles) {
     __shared__ double s_centre[kU1MaxNodes], s_ih[kU1MaxNodes];
     __shared__ uint32_t s_child[kU1MaxNodes], s_root[kU1MaxBins];
     __shared__ double s_u[kU1Tile], s_val[kU1Tile + 1];
     __shared__ uint16_t s_org[kU1Tile];
-    __shared__ uint32_t s_tot[kU1MaxLeaves + 1], s_cur[kU1MaxLeaves + 1], s_start[kU1MaxLeaves + 2];
+    __shared__ uint32_t s_tot[2][kU1MaxLeaves + 2]; // per-key counts of the tile, double buffered by tile parity
     const uint32_t tid = threadIdx.x, lane = tid & 31;
     const uint32_t L = tv.n_leaves;
     for (uint32_t node = tid; node < tv.n_nodes; node += kU1Threads) {
@@ -222,24 +226,36 @@ eval_sorted_1d_kernel(const TreeView tv, const U1Coef cf, const double *__restri
     }
     for (uint32_t b = tid; b < tv.n_bins; b += kU1Threads)
         s_root[b] = __ldg(tv.bin_root + b);
+    if (tid < 2 * (kU1MaxLeaves + 2))
+        (&s_tot[0][0])[tid] = 0;
+    __syncthreads();
     const double lo = tv.lower_left[0], hi = tv.upper_right[0], inv_bin = tv.inv_bin_size[0];
     const int last_bin = tv.n_sub[0] - 1;
     const double qnan = __longlong_as_double(0x7ff8000000000000ll);
 
-    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    auto load_tile = [&](int64_t tile, double (&v)[kU1P]) {
         const int64_t base = tile * kU1Tile;
-        const uint32_t m = (uint32_t)(n - base < kU1Tile ? n - base : kU1Tile); // points in this tile
-        if (tid <= kU1MaxLeaves)
-            s_tot[tid] = s_cur[tid] = 0;
-        __syncthreads(); // counters cleared; (first tile) node table staged; previous tile's stores have read s_val
-        // ---- A
-        double xv[kU1P], u[kU1P];
-        uint32_t key[kU1P], grp[kU1P];
 #pragma unroll
         for (int j = 0; j < kU1P; ++j) {
-            const uint32_t t = j * kU1Threads + tid;
-            xv[j] = t < m ? __ldcs(x + base + t) : lo;
+            const int64_t i = base + j * kU1Threads + tid;
+            v[j] = tile < n_tiles && i < n ? __ldcs(x + i) : lo;
         }
+    };
+    double xv[kU1P], xn[kU1P];
+    load_tile(blockIdx.x, xv);
+    int par = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, par ^= 1) {
+        const int64_t base = tile * kU1Tile;
+        const uint32_t m = (uint32_t)(n - base < kU1Tile ? n - base : kU1Tile); // points in this tile
+        load_tile(tile + gridDim.x, xn); // the next tile's points travel while this one is sorted and evaluated
+        if (tid == 0 && tile + 2 * (int64_t)gridDim.x + 1 < n_tiles) { // ... and the one after is asked into L2
+            const uintptr_t a = (reinterpret_cast<uintptr_t>(x + (tile + 2 * (int64_t)gridDim.x) * kU1Tile) + 15) & ~uintptr_t(15);
+            prefetch_l2_bulk(reinterpret_cast<const void *>(a), (uint32_t)(kU1Tile * 8));
+        }
+        uint32_t *tot = s_tot[par];
+        // ---- A: leaf and u of every point
+        double u[kU1P];
+        uint32_t key[kU1P], at[kU1P];
 #pragma unroll
         for (int j = 0; j < kU1P; ++j) {
             const bool out = (xv[j] < lo) || (xv[j] >= hi); // template.hpp:872-873; NaN compares false: "inside"
@@ -258,43 +274,42 @@ eval_sorted_1d_kernel(const TreeView tv, const U1Coef cf, const double *__restri
             if (j * kU1Threads + tid >= m)
                 key[j] = 0xFFFFFFFFu; // past the end of the batch: belongs to no run
         }
-        // ---- B: histogram (one atomic per distinct key and warp)
+        // ---- B: one shared atomic per distinct key and warp; what it returns is the group's offset inside the key's run
 #pragma unroll
         for (int j = 0; j < kU1P; ++j) {
-            grp[j] = __match_any_sync(0xffffffffu, key[j]);
-            if (key[j] != 0xFFFFFFFFu && (uint32_t)(__ffs(grp[j]) - 1) == lane)
-                atomicAdd(&s_tot[key[j]], (uint32_t)__popc(grp[j]));
-        }
-        __syncthreads();
-        if (tid < 32) { // exclusive scan over the L + 1 keys
-            uint32_t v = lane <= L ? s_tot[lane] : 0u, incl = v;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o)
-                    incl += y;
-            }
-            if (lane <= L + 1)
-                s_start[lane] = incl - v; // s_start[L + 1] = m
-        }
-        __syncthreads();
-#pragma unroll
-        for (int j = 0; j < kU1P; ++j) {
-            const int leader = __ffs(grp[j]) - 1;
-            uint32_t at = 0;
+            const uint32_t grp = __match_any_sync(0xffffffffu, key[j]);
+            const int leader = __ffs(grp) - 1;
+            uint32_t base_g = 0;
             if (key[j] != 0xFFFFFFFFu && (uint32_t)leader == lane)
-                at = atomicAdd(&s_cur[key[j]], (uint32_t)__popc(grp[j]));
-            at = __shfl_sync(0xffffffffu, at, leader);
-            if (key[j] != 0xFFFFFFFFu) {
-                const uint32_t pos = s_start[key[j]] + at + (uint32_t)__popc(grp[j] & ((1u << lane) - 1u));
-                s_u[pos] = u[j];
-                s_org[pos] = (uint16_t)(j * kU1Threads + tid);
-            }
+                base_g = atomicAdd(&tot[key[j]], (uint32_t)__popc(grp));
+            at[j] = __shfl_sync(0xffffffffu, base_g, leader) + (uint32_t)__popc(grp & ((1u << lane) - 1u));
         }
+        __syncthreads(); // the counts of the tile are complete
+        {   // every thread walks the <= 17 counts itself: first slot of each of its keys
+            uint32_t run = 0, first[kU1P];
+#pragma unroll
+            for (int j = 0; j < kU1P; ++j)
+                first[j] = 0;
+            for (uint32_t l = 0; l <= L; ++l) {
+                const uint32_t t = tot[l];
+#pragma unroll
+                for (int j = 0; j < kU1P; ++j)
+                    first[j] = key[j] == l ? run : first[j];
+                run += t;
+            }
+#pragma unroll
+            for (int j = 0; j < kU1P; ++j)
+                if (key[j] != 0xFFFFFFFFu) {
+                    s_u[first[j] + at[j]] = u[j];
+                    s_org[first[j] + at[j]] = (uint16_t)(j * kU1Threads + tid);
+                }
+        }
+        if (tid < kU1MaxLeaves + 2)
+            s_tot[par ^ 1][tid] = 0; // the next tile's counters (last read before the previous tile's final barrier)
         __syncthreads();
-        // ---- C
-        u1_leaves<ORDER, 0>(cf, L, s_start, s_u, s_org, s_val);
-        for (uint32_t s = s_start[L] + tid; s < s_start[L + 1]; s += kU1Threads)
+        // ---- C: one pass per leaf, coefficients from the constant bank; then the points outside the domain
+        const uint32_t in_end = u1_leaves<ORDER, 0>(cf, L, tot, 0u, s_u, s_org, s_val);
+        for (uint32_t s = in_end + tid; s < m; s += kU1Threads)
             s_val[s_org[s]] = qnan; // outside [lower_left, upper_right): template.hpp:880-881
         __syncthreads();
 #pragma unroll
@@ -302,6 +317,7 @@ eval_sorted_1d_kernel(const TreeView tv, const U1Coef cf, const double *__restri
             const uint32_t t = j * kU1Threads + tid;
             if (t < m)
                 __stcs(res + base + t, s_val[t]);
+            xv[j] = xn[j];
         }
     }
 }
@@ -323,7 +339,9 @@ static int launch_sorted_order(const DeviceTree &dt, const double *d_x, double *
     for (int l = 0; l < kU1MaxLeaves; ++l)
         for (int k = 0; k < 16; ++k)
             cf.c[l][k] = (uint32_t)l < dt.view.n_leaves && k < ORDER ? dt.leaf_coef_1d[(size_t)l * ORDER + k] : 0.0;
-    auto kern = eval_sorted_1d_kernel<ORDER>;
+    // resident CTAs per SM asked of ptxas: 6 (40 registers) or 5 (48); BAOBZI_B200_SORTED1D_CTAS picks
+    static const int want = std::getenv("BAOBZI_B200_SORTED1D_CTAS") ? std::atoi(std::getenv("BAOBZI_B200_SORTED1D_CTAS")) : kU1MinCtas;
+    auto kern = want == 5 ? eval_sorted_1d_kernel<ORDER, 5> : eval_sorted_1d_kernel<ORDER, 6>;
     int per_sm = 0;
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kU1Threads, 0);
     if (e != cudaSuccess)

@@ -8,6 +8,11 @@
 namespace bz {
 
 constexpr uint32_t kInvalidSlot = 0xFFFFFFFFu;
+// Key format between the two launches of the split sort (and the side jobs of the piggyback schedule): leaf rank in
+// the low 15 bits (kKeyNoLeaf = outside the domain), the point's rank inside (CTA, leaf) above them.  Limits, checked
+// where the workspace is built: fewer than 32 767 leaves, at most 2^17 points per CTA and chunk.
+constexpr int kKeyLeafBits = 15;
+constexpr uint32_t kKeyNoLeaf = (1u << kKeyLeafBits) - 1u;
 constexpr int kSortBatch = 6; // histogram counters (loads / atomics) in flight per thread in the scan phases
 
 // BYBIN (the bucketed path of large 1D / 2D trees): the key is the grid cell number >> bshift instead of the leaf,

@@ -84,7 +84,7 @@ def test_reference_cpp_wrapper(gpu_lib, tmp_path):
 PY_USER = r"""
 import sys, numpy as np
 import baobzi                                   # the reference's src/python/__init__.py, unmodified
-assert 'baobzi_b200' in baobzi.baobzi_path.replace('\\', '/') or 'pyref' in baobzi.baobzi_path, baobzi.baobzi_path
+assert baobzi.baobzi_path.endswith('prefix/lib/libbaobzi.so'), baobzi.baobzi_path   # found by ITS OWN search
 def f(x, y, data):                              # its INPUT_FUNC signature (ctypes pointers)
     y[0] = np.exp(np.cos(3.0 * x[0]) * np.sin(2.0 * x[1]))
 c, hl = np.array([0.5, -0.25]), np.array([1.0, 0.5])
@@ -142,8 +142,8 @@ def test_scalar_eval_latency_and_pageable_throughput(gpu_lib):
     rng = np.random.default_rng(2)
     n = 20_000_000
     x = 0.5 + rng.random((n, 2)) * np.array([2.0, 2.0]) + np.array([0.0, 1.5])
-    res = np.empty(n)
-    b(x[:1 << 20], out=res[:1 << 20])
+    res = np.zeros(n)
+    b(x, out=res)                       # first call of this size: the workers allocate their pinned / device buffers
     t0 = time.perf_counter()
     b(x, out=res)
     rate = n / (time.perf_counter() - t0)

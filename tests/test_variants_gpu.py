@@ -21,8 +21,7 @@ VARIANTS = [
     {"BAOBZI_B200_SORT_SPLIT": "1"},         # split sort forced (the default only from 2048 leaves; fixtures are smaller)
     {"BAOBZI_B200_SORT_SPLIT": "2"},         # split sort, two CTAs per SM and phase
     {"BAOBZI_B200_SORT_SBIN": "0"},          # bin_leaf gathered through L1 instead of shared memory
-    {"BAOBZI_B200_PIGGY": "0"},              # sort launches of their own instead of side jobs of the evaluation (round 1 schedule)
-    {"BAOBZI_B200_PIGGY": "0", "BAOBZI_B200_SORT_SPLIT": "1"},
+    {"BAOBZI_B200_PIGGY": "1"},              # the evaluation launches carry the sort of the following chunks (opt-in)
     {"BAOBZI_B200_K4": "4,8,1,1,1"},         # T(z) advanced on the fly
     {"BAOBZI_B200_K4": "3,12,1,1,1"},
     {"BAOBZI_B200_K4": "4,12,1,0,1"},
@@ -91,12 +90,13 @@ def test_cta_shared_tma_block_variants(gpu_lib, ref, name, k4, monkeypatch):
     b.free()
 
 
-def test_piggyback_schedule_ragged_chunks(gpu_lib, ref):
-    """The evaluation launches carry the sort of the following chunks: chunk counts 2, 3, many; a last chunk of one
+def test_piggyback_schedule_ragged_chunks(gpu_lib, ref, monkeypatch):
+    """The evaluation launches carry the sort of the following chunks (opt-in): chunk counts 2, 3, many; a last chunk of one
     point; most points outside the domain (few tiles: the side jobs finish in the tail loops); every point in one leaf."""
     import torch
     from conftest import load_golden
     from test_parity_gpu import ulp
+    monkeypatch.setenv("BAOBZI_B200_PIGGY", "1")
     for name in ("t3d_o8", "t3d_o12", "tc_3d"):
         path, g = load_golden(name)
         t = ref.OracleTree(path)
