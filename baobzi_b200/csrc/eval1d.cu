@@ -322,6 +322,149 @@ eval_sorted_1d_kernel(const TreeView tv, const U1Coef cf, const double *__restri
     }
 }
 
+// ------------------------------------------------------------------------------------------ one or two leaves
+// The smallest trees (BASELINE.json configs[1]: 1.5 log x on [1,3] at order 16 is TWO leaves) need neither a table walk per
+// coefficient nor a sort: the leaf of a point is one predicate, and a coefficient is SEL(c_leaf0[k], c_leaf1[k], predicate)
+// with both candidates coming from the launch's constant bank -- no load instruction at all in the recurrence.  Per
+// coefficient and point: two 32-bit selects (ALU pipe) + DADD + DFMA (FP64 pipe), the two pipes evenly loaded, against
+// 8 bytes of shared-memory write-back in the table kernel.  Same operations in the same order as cheb_eval_1d, so the
+// same bits.  Streaming structure of the table kernel: P loads per thread in flight, L2 bulk prefetch two tiles ahead.
+template <int ORDER, int P>
+__global__ void __launch_bounds__(256, 2)
+eval_two_leaf_1d_kernel(const TreeView tv, const U1Coef cf, const double *__restrict__ x, double *__restrict__ res,
+                        int64_t n, int64_t n_tiles) {
+    __shared__ double s_centre[kU1MaxNodes], s_ih[kU1MaxNodes];
+    __shared__ uint32_t s_child[kU1MaxNodes], s_root[kU1MaxBins];
+    for (uint32_t node = threadIdx.x; node < tv.n_nodes; node += blockDim.x) {
+        const NodeHead h = load_head(tv.nodes, node);
+        const NodeTail t = load_tail(tv.nodes, node);
+        s_centre[node] = h.c0;
+        s_ih[node] = t.ih0;
+        s_child[node] = h.child0 == kLeafMark ? (kT1LeafBit | t.leaf_rank) : h.child0;
+    }
+    for (uint32_t b = threadIdx.x; b < tv.n_bins; b += blockDim.x)
+        s_root[b] = __ldg(tv.bin_root + b);
+    __syncthreads();
+    const double lo = tv.lower_left[0], hi = tv.upper_right[0], inv_bin = tv.inv_bin_size[0];
+    const int last_bin = tv.n_sub[0] - 1;
+    const int64_t tile_pts = (int64_t)blockDim.x * P;
+    const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+    // both candidate blocks live in registers for the whole kernel (opaque to the compiler, which would otherwise
+    // re-read them from the constant bank with predicated loads at every use: three LDC per coefficient and point)
+    double ca[ORDER], cb[ORDER];
+#pragma unroll
+    for (int k = 0; k < ORDER; ++k) {
+        ca[k] = cf.c[0][k];
+        cb[k] = cf.c[1][k];
+        asm volatile("" : "+d"(ca[k]), "+d"(cb[k]));
+    }
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t base = tile * tile_pts;
+        if (threadIdx.x == 0) {
+            const int64_t ahead = tile + 2 * (int64_t)gridDim.x;
+            if (ahead + 1 < n_tiles) {
+                const uintptr_t a = (reinterpret_cast<uintptr_t>(x + ahead * tile_pts) + 15) & ~uintptr_t(15);
+                prefetch_l2_bulk(reinterpret_cast<const void *>(a), (uint32_t)(tile_pts * 8));
+            }
+        }
+        const bool full = base + tile_pts <= n; // CTA uniform: whole tiles carry no per-point guards, so that the P
+                                                // recurrences stay interleaved instead of sinking into P branches
+        double xv[P];
+#pragma unroll
+        for (int j = 0; j < P; ++j) {
+            const int64_t i = base + (int64_t)j * blockDim.x + threadIdx.x;
+            xv[j] = full || i < n ? __ldcs(x + i) : lo;
+        }
+        double u[P], u2[P], c0[P], c1[P];
+        bool out[P], second[P];
+#pragma unroll
+        for (int j = 0; j < P; ++j) {
+            out[j] = (xv[j] < lo) || (xv[j] >= hi); // template.hpp:872-873; NaN compares false and stays "inside"
+            int b = __double2int_rz(__dmul_rn(__dsub_rn(xv[j], lo), inv_bin));
+            b = min(max(b, 0), last_bin);
+            uint32_t node = s_root[b];
+            double c = s_centre[node];
+            uint32_t ch = s_child[node];
+            while (!(ch & kT1LeafBit)) { // template.hpp:482-493 (at most one step in a two-leaf tree)
+                node = ch + (uint32_t)(xv[j] > c);
+                c = s_centre[node];
+                ch = s_child[node];
+            }
+            second[j] = (ch & ~kT1LeafBit) != 0;
+            u[j] = __dmul_rn(__dsub_rn(xv[j], c), s_ih[node]);
+            u2[j] = __dadd_rn(u[j], u[j]);
+            c0[j] = second[j] ? cb[0] : ca[0];
+            c1[j] = second[j] ? cb[1] : ca[1];
+        }
+#pragma unroll
+        for (int k = 2; k < ORDER; ++k) { // template.hpp:146-161, P independent chains
+#pragma unroll
+            for (int j = 0; j < P; ++j) {
+                const double ck = second[j] ? cb[k] : ca[k];
+                const double tmp = c1[j];
+                c1[j] = __dsub_rn(ck, c0[j]);
+                c0[j] = __fma_rn(c0[j], u2[j], tmp);
+            }
+        }
+        if (full) {
+#pragma unroll
+            for (int j = 0; j < P; ++j)
+                __stcs(res + base + (int64_t)j * blockDim.x + threadIdx.x, out[j] ? qnan : __fma_rn(c0[j], u[j], c1[j]));
+        } else {
+#pragma unroll
+            for (int j = 0; j < P; ++j) {
+                const int64_t i = base + (int64_t)j * blockDim.x + threadIdx.x;
+                if (i < n)
+                    __stcs(res + i, out[j] ? qnan : __fma_rn(c0[j], u[j], c1[j]));
+            }
+        }
+    }
+}
+
+static bool two_leaf_1d_fits(const DeviceTree &dt) {
+    if (const char *e = std::getenv("BAOBZI_B200_TWOLEAF1D"))
+        if (std::atoi(e) == 0)
+            return false;
+    const TreeView &tv = dt.view;
+    return tv.dim == 1 && tv.n_leaves >= 1 && tv.n_leaves <= 2 && tv.n_nodes <= (uint32_t)kU1MaxNodes &&
+           tv.n_bins <= (uint32_t)kU1MaxBins && dt.leaf_coef_1d.size() == (size_t)tv.n_leaves * tv.order;
+}
+
+template <int ORDER>
+static int launch_two_leaf_order(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream) {
+    constexpr int P = 4;
+    U1Coef cf;
+    for (int l = 0; l < kU1MaxLeaves; ++l)
+        for (int k = 0; k < 16; ++k) // a one-leaf tree: both candidates are the same block
+            cf.c[l][k] = k < ORDER && l < 2 ? dt.leaf_coef_1d[(size_t)((uint32_t)l < dt.view.n_leaves ? l : 0) * ORDER + k] : 0.0;
+    auto kern = eval_two_leaf_1d_kernel<ORDER, P>;
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, 0);
+    if (e != cudaSuccess)
+        return (int)e;
+    if (per_sm < 1)
+        return (int)cudaErrorLaunchOutOfResources;
+    const int64_t tile_pts = 256 * P;
+    const int64_t n_tiles = (n + tile_pts - 1) / tile_pts;
+    int64_t grid = (int64_t)dt.sm_count * per_sm;
+    if (grid > n_tiles)
+        grid = n_tiles;
+    kern<<<(unsigned)grid, 256, 0, stream>>>(dt.view, cf, d_x, d_res, n, n_tiles);
+    return (int)cudaGetLastError();
+}
+
+static int launch_eval_two_leaf_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream) {
+    switch (dt.view.order) {
+    case 6: return launch_two_leaf_order<6>(dt, d_x, d_res, n, stream);
+    case 8: return launch_two_leaf_order<8>(dt, d_x, d_res, n, stream);
+    case 10: return launch_two_leaf_order<10>(dt, d_x, d_res, n, stream);
+    case 12: return launch_two_leaf_order<12>(dt, d_x, d_res, n, stream);
+    case 14: return launch_two_leaf_order<14>(dt, d_x, d_res, n, stream);
+    case 16: return launch_two_leaf_order<16>(dt, d_x, d_res, n, stream);
+    default: return (int)cudaErrorInvalidValue;
+    }
+}
+
 bool sorted_1d_fits(const DeviceTree &dt) {
     const TreeView &tv = dt.view;
     static const bool off = std::getenv("BAOBZI_B200_SORTED1D") && std::atoi(std::getenv("BAOBZI_B200_SORTED1D")) == 0;
@@ -413,6 +556,8 @@ static int launch_table_order(const DeviceTree &dt, const double *d_x, double *d
 }
 
 int launch_eval_table_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream) {
+    if (two_leaf_1d_fits(dt)) // one or two leaves: coefficients selected between two constant-bank candidates
+        return launch_eval_two_leaf_1d(dt, d_x, d_res, n, stream);
     if (sorted_1d_fits(dt)) // a handful of leaves: coefficients as constant-bank operands
         return launch_eval_sorted_1d(dt, d_x, d_res, n, stream);
     switch (dt.view.order) {

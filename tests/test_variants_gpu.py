@@ -178,7 +178,7 @@ def test_eval_all_multi_output_1d(gpu_lib, ref):
 ONE_D = ["t1d_o6", "t1d_o8", "t1d_o10", "t1d_o12", "t1d_o14", "t1d_o16", "deep_1d", "tc_1d2"]
 
 
-@pytest.mark.parametrize("kernel", ["table", "sorted"])
+@pytest.mark.parametrize("kernel", ["table", "sorted", "twoleaf"])
 @pytest.mark.parametrize("name", ONE_D)
 def test_table_1d_kernel_bits(gpu_lib, ref, name, kernel, monkeypatch):
     """The shared-memory 1D kernels (eval1d.cu) forced on from the first point -- "table": the whole tree in shared
@@ -201,6 +201,7 @@ def test_table_1d_kernel_bits(gpu_lib, ref, name, kernel, monkeypatch):
     gwant = t.eval_multi(gx, ref.ARITH_AVX2)
     old = os.environ.get("BAOBZI_B200_TABLE1D_MIN")
     monkeypatch.setenv("BAOBZI_B200_SORTED1D", "1" if kernel == "sorted" else "0")
+    monkeypatch.setenv("BAOBZI_B200_TWOLEAF1D", "1" if kernel == "twoleaf" else "0")   # trees of one or two leaves only
     try:
         b = gpu_lib.Baobzi(filename=path, mode="direct")
         os.environ["BAOBZI_B200_TABLE1D_MIN"] = "-1"       # generic direct kernel
@@ -223,6 +224,40 @@ def test_table_1d_kernel_bits(gpu_lib, ref, name, kernel, monkeypatch):
             os.environ.pop("BAOBZI_B200_TABLE1D_MIN", None)
         else:
             os.environ["BAOBZI_B200_TABLE1D_MIN"] = old
+
+
+@pytest.mark.parametrize("order", [6, 8, 10, 12, 14, 16])
+@pytest.mark.parametrize("tol", [1e-3, 1e-9])
+def test_two_leaf_1d_kernel_every_order(gpu_lib, ref, tmp_path, order, tol, monkeypatch):
+    """Trees of one or two leaves (a smooth 1D function, BASELINE.json configs[1]) take the kernel whose coefficients
+    are selected between two constant-bank candidates: oracle bits at every order, points outside and NaN included."""
+    import torch
+    from test_parity_gpu import ulp
+    monkeypatch.setenv("BAOBZI_B200_TABLE1D_MIN", "0")
+    b = gpu_lib.Baobzi(fin=ref.func_ptr("testfun_1d"), dim=1, order=order, center=np.array([2.0]),
+                       half_length=np.array([1.0]), tol=tol, data=1.5)
+    path = str(tmp_path / "t.baobzi")
+    b.save(path)
+    t = ref.OracleTree(path)
+    if t.n_leaves > 2:
+        b.free()
+        pytest.skip("%d leaves at this order / tolerance" % t.n_leaves)
+    rng = np.random.default_rng(order)
+    n = 300_007
+    x = 0.98 + rng.random((n, 1)) * 2.04
+    x[::997] = np.nan
+    want = t.eval_multi(x, ref.ARITH_AVX2)
+    xd = torch.from_numpy(x).cuda()
+    launches = b.launches
+    y = b(xd).cpu().numpy()
+    assert b.launches == launches + 1
+    assert ulp(ref, y, want) == 0 and np.array_equal(np.isnan(y), np.isnan(want))
+    monkeypatch.setenv("BAOBZI_B200_TWOLEAF1D", "0")
+    monkeypatch.setenv("BAOBZI_B200_SORTED1D", "0")
+    assert b(xd).cpu().numpy().tobytes() == y.tobytes()           # the table kernel's bytes
+    for m in (1, 1023, 1025, 4097):
+        assert b(xd[3:3 + m]).cpu().numpy().tobytes() == y[3:3 + m].tobytes()
+    b.free()
 
 
 @pytest.fixture(params=["0", "1"], ids=["single_launch_sort", "split_sort"])
