@@ -529,7 +529,7 @@ void fn_eval_multi(const void *obj, const double *x, double *res, int ntrg) {
         n_dev = 1; // not worth waking other GPUs (and replicating the tree) for
     // workers per device: 3 keep H2D, kernels and D2H of a pinned-memory call overlapped; staging needs more host
     // threads than that to feed the link (measured on B200 hosts)
-    int per_dev = (job.stage_x || job.stage_res) ? 12 : 3;
+    int per_dev = (job.stage_x || job.stage_res) ? 8 : 3; // measured plateau (profiles/r02_host_path_ab.txt: 2 / 4 / 8 / 12 / 16 workers)
     per_dev = env_int("BAOBZI_B200_HOST_WORKERS", per_dev);
     per_dev = std::max(1, std::min(per_dev, 16));
     const int hw = (int)std::thread::hardware_concurrency();

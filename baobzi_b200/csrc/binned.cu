@@ -205,8 +205,10 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
                 if (coalesce)
                     cnt[l] = h[j];
                 tbl[l] = r[j];
-                if (phase == 1)
+                if (phase == 1) {
                     base_tbl[(size_t)blockIdx.x * nl + l] = r[j];
+                    base_tbl[(size_t)(gridDim.x + blockIdx.x) * nl + l] = h[j]; // this CTA's own count: the scatter launch sorts locally with it
+                }
             }
         }
     }
@@ -277,6 +279,65 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         // per lane the two atomics per point WERE the sort's duration: 16.8 M of them per 8.4 M-point chunk = 115 us.)
         constexpr uint32_t KPT = 8;
         const uint32_t per_it = KPT * nthr;
+        // Coalescing scatter (coal_cap > 0: the CTA's range fits the shared-memory staging).  What bounds the direct
+        // scatter below is not arithmetic or atomics but the rate at which the chip takes scattered 4-byte stores
+        // (ncu source view: every iteration waits for the 4096 stores of the previous one to drain; 8.4 M of them =
+        // 46 us, scripts/micro/scatter_rate.cu).  With the rank in the key a CTA-local counting sort costs no atomic at
+        // all: local position = (exclusive scan of the CTA's own counts)[leaf] + rank.  The CTA's points then leave as
+        // one run per leaf -- consecutive slots, written by neighbouring lanes: one or two sector writes per run
+        // instead of one per point.
+        if (coal_cap > 0 && hi - lo <= coal_cap) {
+            uint32_t *loc = tbl + nl; // [nl + 1] first local slot of every leaf
+            uint16_t *sorted = reinterpret_cast<uint16_t *>(loc + nl + 1 + ((nl + 1) & 1));
+            const uint32_t *cntg = base_tbl + (size_t)(gridDim.x + blockIdx.x) * nl;
+            uint32_t mine2 = 0;
+            for (uint32_t l = l0; l < l1; ++l)
+                mine2 += cntg[l];
+            uint32_t incl2 = mine2;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, incl2, o);
+                if (lane >= o)
+                    incl2 += t;
+            }
+            if (lane == 31)
+                warp_sums[warp] = incl2;
+            __syncthreads();
+            uint32_t off = incl2 - mine2;
+            for (uint32_t w = 0; w < warp; ++w)
+                off += warp_sums[w];
+            for (uint32_t l = l0; l < l1; ++l) {
+                loc[l] = off;
+                off += cntg[l];
+            }
+            if (l1 == nl)
+                loc[nl] = off; // every thread at or past the end holds the total
+            __syncthreads();
+            for (uint32_t b0 = lo; b0 < hi; b0 += per_it) { // keys -> local order (16-bit offsets inside the CTA's range)
+                const uint32_t i0 = b0 + KPT * tid;
+                uint4 qa = make_uint4(kKeyNoLeaf, kKeyNoLeaf, kKeyNoLeaf, kKeyNoLeaf), qb = qa;
+                if (i0 < hi)
+                    qa = __ldcs(reinterpret_cast<const uint4 *>(key + i0));
+                if (i0 + 4 < hi)
+                    qb = __ldcs(reinterpret_cast<const uint4 *>(key + i0 + 4));
+                const uint32_t w[KPT] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+#pragma unroll
+                for (int j = 0; j < (int)KPT; ++j) {
+                    const uint32_t leaf = w[j] & kKeyNoLeaf;
+                    if (leaf != kKeyNoLeaf && i0 + j < hi)
+                        sorted[loc[leaf] + (w[j] >> kKeyLeafBits)] = (uint16_t)(i0 + j - lo);
+                }
+            }
+            __syncthreads();
+            // copy-out: G lanes per run (8 when the runs are short, a whole warp when they are long)
+            const uint32_t G = loc[nl] >= 24u * nl ? 32u : 8u, sub = tid & (G - 1);
+            for (uint32_t l = tid / G; l < nl; l += nthr / G) {
+                const uint32_t b = loc[l], len = loc[l + 1] - b, g = tbl[l];
+                for (uint32_t e = sub; e < len; e += G)
+                    perm[g + e] = lo + sorted[b + e];
+            }
+            return;
+        }
         auto ld = [&](uint32_t b, int half) -> uint4 {
             const uint32_t i = b + KPT * tid + 4 * half;
             return b < hi && i < hi ? __ldcs(reinterpret_cast<const uint4 *>(key + i)) : make_uint4(kKeyNoLeaf, kKeyNoLeaf, kKeyNoLeaf, kKeyNoLeaf);
@@ -460,7 +521,7 @@ static cudaError_t alloc_split_buffers(BinWorkspace &ws, size_t cwords, int64_t 
     if (e == cudaSuccess)
         e = cudaMalloc((void **)&ws.alt_key, sizeof(uint32_t) * chunk);
     for (int h = 0; h < 2 && e == cudaSuccess; ++h)
-        e = cudaMalloc((void **)&ws.base_tbl[h], sizeof(uint32_t) * (size_t)ws.split_ctas * n_keys);
+        e = cudaMalloc((void **)&ws.base_tbl[h], sizeof(uint32_t) * 2 * (size_t)ws.split_ctas * n_keys); // bases | counts
     if (e == cudaSuccess)
         e = cudaStreamCreateWithFlags(&ws.sort_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess)
@@ -690,6 +751,17 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             ws.split_sbin = nl < 0xFFFFu && hist + tblb <= kFusedSortMaxSmem ? dt.view.n_bins : 0u;
             ws.split_smem_a = hist + (ws.split_sbin ? tblb : 0);
             ws.split_smem_b = hist;
+            // coalescing scatter of the scatter launch: [leaf] local starts + 16-bit local order of the CTA's range
+            ws.split_coal = 0;
+            {
+                const int64_t range = (chunk + (int64_t)dt.sm_count * per - 1) / (dt.sm_count * per) + 16;
+                const size_t need = hist + sizeof(uint32_t) * ((size_t)nl + 2) + sizeof(uint16_t) * (size_t)((range + 7) / 8 * 8);
+                const char *ce = std::getenv("BAOBZI_B200_SPLIT_COAL");
+                if (range <= 65536 && need <= kFusedSortMaxSmem && !(ce && std::atoi(ce) == 0)) {
+                    ws.split_coal = (uint32_t)range;
+                    ws.split_smem_b = need;
+                }
+            }
             ws.split_ctas = dt.sm_count * per;
             ws.split = split_wanted;
             ws.piggy = want_piggy;
@@ -928,6 +1000,7 @@ static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t ph
     const bool bybin = ws.bucketed; // bucketed path: key = grid cell >> bshift, no tile descriptors, no table
     const uint32_t TILE = bybin ? 1u : 32u * (uint32_t)ws.P;
     const size_t smem = phase == 1 ? ws.split_smem_a : ws.split_smem_b;
+    const uint32_t coal = phase == 2 && !ws.bucketed ? ws.split_coal : 0u;
     const uint32_t sbin = phase == 1 ? ws.split_sbin : 0u;
     // Threads of the two launches (one CTA of each per SM).  In 2D the lookup (grid cell + descent) is the longer of the
     // two, so it gets 768 threads and the scatter 256; in 3D 512 + 512.  Measured on B200, A+B threads -> ms per step:
@@ -946,7 +1019,7 @@ static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t ph
 #define BZ_SORT_PHASE(D, BB, PH)                                                                                     \
     bin_sort_fused_kernel<D, BB, PH><<<grid, threads, smem, st>>>(tv, d_x, d_res, key, cur, next, ws.cshift, TILE,  \
                                                                   ws.perm, tile_leaf, tile_info, ws.n_tiles, n, 0u,  \
-                                                                  nkeys, bshift, ws.start, 0u, sbin, phase, base)
+                                                                  nkeys, bshift, ws.start, coal, sbin, phase, base)
 #define BZ_SORT_PHASES(D, BB)                                                                                        \
     do {                                                                                                             \
         if (phase == 1)                                                                                              \

@@ -95,6 +95,7 @@ struct BinWorkspace {
     bool piggy = false;        // the evaluation launches carry the sort of the following chunks (launch_eval_piggy)
     int split_ctas = 0;
     uint32_t split_sbin = 0, piggy_sbin = 0;
+    uint32_t split_coal = 0;   // scatter launch: capacity of the CTA-local order in shared memory (0: direct scatter)
     size_t split_smem_a = 0, split_smem_b = 0;
     uint32_t *count3 = nullptr, *base_tbl[2] = {nullptr, nullptr};
     int rot = 0;
