@@ -133,7 +133,7 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
     const uint32_t lo = PHASE ? lo_raw & ~7u : lo_raw;
     const uint32_t hi = PHASE && blockIdx.x + 1 != gridDim.x ? hi_raw & ~7u : hi_raw;
     const bool use_skey = hi - lo <= skey_cap; // CTA uniform
-    const bool coalesce = coal_cap > 0 && hi - lo <= coal_cap;
+    const bool coalesce = PHASE == 0 && coal_cap > 0 && hi - lo <= coal_cap; // (PHASE 2 has its own use of coal_cap below)
 
     // ---- phase A
     const uint32_t lane_id = tid & 31;

@@ -51,6 +51,35 @@ def test_committed_bench_lines(path):
     assert abs(d["value"] - pts / (d["ms_per_step"] * 1e-3)) / d["value"] < 1e-6
 
 
+R02 = [p for p in LINES if os.path.basename(p).startswith("r02_bench_default")]
+
+
+@pytest.mark.parametrize("path", R02, ids=[os.path.basename(p) for p in R02])
+def test_round2_default_line_carries_every_configuration(path):
+    """The default invocation: headline C3 plus short runs of the other BASELINE.json configurations, each with a clock
+    record of >= 10 samples, its own roofline against its own bound, a cpu_baseline and a MEASURED parity block."""
+    d = _load(path)
+    par = d["config"]["parity"]
+    assert par["max_ulp"] == 0 and par["node_idx_mismatch"] == 0 and par["nan_mismatch"] == 0 and par["points"] >= 100000
+    assert d["config"]["tree"]["leaves"] == 4096 and d["config"]["tree"]["nodes"] == 4096
+    assert d["clocks"]["samples"] >= 10
+    assert d["e2e"]["pageable"]["value"] > 0 and d["e2e"]["pageable"]["matches_device_path"] is True
+    w = d["workloads"]
+    assert {"C1", "C2", "C4", "C5", "C5_8e9_sharded"} <= set(w)
+    for tag in ("C1", "C2", "C4", "C5"):
+        r = w[tag]
+        assert r["clocks"]["samples"] >= 10, tag
+        assert not set(r["clocks"]["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}, tag
+        assert r["parity"]["max_ulp"] == 0 and r["parity"]["node_idx_mismatch"] == 0, tag
+        assert r["cpu_baseline"]["kind"] in ("reference", "port") and r["cpu_baseline"]["value"] > 0, tag
+        assert r["tree"]["leaves"] > 0 and r["value"] > 0
+        for name, st in r["stages"].items():          # a sort is measured against the bytes it moves, never against flops
+            assert st["bound"] == ("hbm" if name in ("sort", "scan", "scatter") else st["bound"]), (tag, name)
+            assert abs(st["frac"] - st["achieved"] / st["peak"]) < 1e-9
+    assert w["C4"]["tree"]["leaves"] > 1_000_000
+    assert w["C5_8e9_sharded"]["points_total"] == 8_000_000_000 and w["C5_8e9_sharded"]["scaling"] == "strong"
+
+
 def test_there_are_committed_lines():
     names = [os.path.basename(p) for p in LINES]
     assert any("c3_1e9" in n for n in names) and any("ref" in n for n in names)
