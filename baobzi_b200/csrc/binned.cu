@@ -757,7 +757,11 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
                 const int64_t range = (chunk + (int64_t)dt.sm_count * per - 1) / (dt.sm_count * per) + 16;
                 const size_t need = hist + sizeof(uint32_t) * ((size_t)nl + 2) + sizeof(uint16_t) * (size_t)((range + 7) / 8 * 8);
                 const char *ce = std::getenv("BAOBZI_B200_SPLIT_COAL");
-                if (range <= 65536 && need <= kFusedSortMaxSmem && !(ce && std::atoi(ce) == 0)) {
+                // 3D only by default: measured on B200 (profiles/r02_sweep_e.txt) C3, 14 points per (CTA, leaf) run: scatter
+                // span 104 -> 65 us per chunk; the 2D benchmark tree (8860 leaves, 3 points per run: nothing to merge, one
+                // more pass through shared memory) 2.09 -> 2.72 ms per 1e8 points, so 2D keeps the direct scatter
+                const bool want_coal = ce ? std::atoi(ce) != 0 : !is2d;
+                if (range <= 65536 && need <= kFusedSortMaxSmem && want_coal) {
                     ws.split_coal = (uint32_t)range;
                     ws.split_smem_b = need;
                 }
@@ -1009,8 +1013,12 @@ static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t ph
     static const int a_env = std::getenv("BAOBZI_B200_SPLIT_ATHREADS") ? std::atoi(std::getenv("BAOBZI_B200_SPLIT_ATHREADS")) : 0;
     static const int b_env = std::getenv("BAOBZI_B200_SPLIT_BTHREADS") ? std::atoi(std::getenv("BAOBZI_B200_SPLIT_BTHREADS")) : 0;
     const bool long_lookup = tv.dim == 2 && !bybin;
-    const int a_threads = a_env >= 32 && a_env <= kSortThreadsA ? a_env / 32 * 32 : (long_lookup ? kSortThreadsA : kSortThreads);
-    const int b_threads = b_env >= 32 && b_env <= kSortThreads ? b_env / 32 * 32 : (long_lookup ? 256 : kSortThreads);
+    // 3D with the coalescing scatter: the lookup launch is the longer one (bound by its one shared atomic per point, 2 cycles
+    // per lane = 58 us per 8.4 M points), so it gets 640 threads and the scatter 384: 512+512 12.77, 768+256 12.06,
+    // 640+384 11.72 ms per 2e8 points (direct scatter, 512+512: 12.59)
+    const bool coal3d = !long_lookup && !bybin && ws.split_coal > 0;
+    const int a_threads = a_env >= 32 && a_env <= kSortThreadsA ? a_env / 32 * 32 : (long_lookup ? kSortThreadsA : (coal3d ? 640 : kSortThreads));
+    const int b_threads = b_env >= 32 && b_env <= kSortThreads ? b_env / 32 * 32 : (long_lookup ? 256 : (coal3d ? 384 : kSortThreads));
     const int threads = phase == 2 ? b_threads : a_threads;
     uint32_t *tile_leaf = bybin ? nullptr : ws.tile_leaf;
     uint2 *tile_info = bybin ? nullptr : ws.tile_info;
