@@ -1014,11 +1014,11 @@ static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t ph
     static const int b_env = std::getenv("BAOBZI_B200_SPLIT_BTHREADS") ? std::atoi(std::getenv("BAOBZI_B200_SPLIT_BTHREADS")) : 0;
     const bool long_lookup = tv.dim == 2 && !bybin;
     // 3D with the coalescing scatter: the lookup launch is the longer one (bound by its one shared atomic per point, 2 cycles
-    // per lane = 58 us per 8.4 M points), so it gets 640 threads and the scatter 384: 512+512 12.77, 768+256 12.06,
-    // 640+384 11.72 ms per 2e8 points (direct scatter, 512+512: 12.59)
+    // per lane = 58 us per 8.4 M points), so it gets 576 threads and the scatter 448: 512+512 12.77, 768+256 12.06,
+    // 640+384 11.72-11.86, 640+448 11.62, 576+448 11.58 ms per 2e8 points (direct scatter, 512+512: 12.59)
     const bool coal3d = !long_lookup && !bybin && ws.split_coal > 0;
-    const int a_threads = a_env >= 32 && a_env <= kSortThreadsA ? a_env / 32 * 32 : (long_lookup ? kSortThreadsA : (coal3d ? 640 : kSortThreads));
-    const int b_threads = b_env >= 32 && b_env <= kSortThreads ? b_env / 32 * 32 : (long_lookup ? 256 : (coal3d ? 384 : kSortThreads));
+    const int a_threads = a_env >= 32 && a_env <= kSortThreadsA ? a_env / 32 * 32 : (long_lookup ? kSortThreadsA : (coal3d ? 576 : kSortThreads));
+    const int b_threads = b_env >= 32 && b_env <= kSortThreads ? b_env / 32 * 32 : (long_lookup ? 256 : (coal3d ? 448 : kSortThreads));
     const int threads = phase == 2 ? b_threads : a_threads;
     uint32_t *tile_leaf = bybin ? nullptr : ws.tile_leaf;
     uint2 *tile_info = bybin ? nullptr : ws.tile_info;

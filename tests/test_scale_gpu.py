@@ -199,3 +199,26 @@ def test_sharded_entry_single_gpu(gpu_lib, ref):
             torch.cuda.synchronize()
             assert torch.equal(want.view(torch.int64), ys[k].view(torch.int64))
     b.free()
+
+
+def test_host_call_spread_over_all_gpus(gpu_lib, ref):
+    """ONE baobzi_eval_multi call with host pointers, chunks dealt to workers on every visible GPU
+    (baobzi_set_host_devices(0)); pageable and pinned buffers; same bits as the single-GPU call."""
+    import torch
+    cfg = CONFIGS["C3"]
+    b = make(gpu_lib, ref, cfg)
+    n = 30_000_001
+    rng = np.random.default_rng(77)
+    x = np.array(cfg["center"]) + (rng.random((n, 3)) * 2 - 1) * np.array(cfg["hl"])
+    one = b(x)
+    b.set_host_devices(0)                                  # all visible devices
+    many = b(x)
+    assert one.tobytes() == many.tobytes()
+    xp = torch.from_numpy(x).pin_memory()
+    yp = torch.empty(n, dtype=torch.float64).pin_memory()
+    b(xp.numpy(), out=yp.numpy())
+    assert yp.numpy().tobytes() == one.tobytes()
+    b.set_host_devices(1)
+    xd = torch.from_numpy(x[:200000]).cuda()
+    assert b(xd).cpu().numpy().tobytes() == one[:200000].tobytes()
+    b.free()
