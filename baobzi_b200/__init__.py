@@ -62,6 +62,7 @@ ABI = {
     "baobzi_device_view": (C.c_int, [baobzi_t, C.c_int, C.c_void_p, C.c_size_t]),
     "baobzi_tree_info": (C.c_int, [baobzi_t, C.POINTER(C.c_int64)]),
     "baobzi_set_host_devices": (C.c_int, [baobzi_t, C.c_int]),
+    "baobzi_b200_guard_check": (C.c_int, [C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "baobzi_launch_count": (C.c_int64, [baobzi_t]),
     "baobzi_profile_begin": (C.c_int, [baobzi_t]),
     "baobzi_profile_end": (C.c_int, [baobzi_t, c_double_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),

@@ -180,8 +180,8 @@ void release(Function *f, ExecContext *c) {
 }
 
 void destroy_context(ExecContext &c) {
-    cudaFree(c.d_x);
-    cudaFree(c.d_res);
+    bz_free(c.d_x);
+    bz_free(c.d_res);
     if (c.h_x)
         cudaFreeHost(c.h_x);
     if (c.h_res)
@@ -399,12 +399,12 @@ struct HostJob {
 
 bool ensure_chunk_buffers(ExecContext *c, const DeviceTree &dt, int64_t points, bool stage_x, bool stage_res) {
     if (c->slot_points < points) {
-        cudaFree(c->d_x);
-        cudaFree(c->d_res);
+        bz_free(c->d_x);
+        bz_free(c->d_res);
         c->d_x = c->d_res = nullptr;
         c->slot_points = 0;
-        if (report(cudaMalloc((void **)&c->d_x, sizeof(double) * points * dt.view.dim), "chunk alloc") ||
-            report(cudaMalloc((void **)&c->d_res, sizeof(double) * points), "chunk alloc"))
+        if (report(bz_malloc((void **)&c->d_x, sizeof(double) * points * dt.view.dim), "chunk alloc") ||
+            report(bz_malloc((void **)&c->d_res, sizeof(double) * points), "chunk alloc"))
             return false;
         c->slot_points = points;
     }
@@ -535,6 +535,10 @@ void fn_eval_multi(const void *obj, const double *x, double *res, int ntrg) {
     const int hw = (int)std::thread::hardware_concurrency();
     if (hw > 0 && n_dev * per_dev > std::max(4, hw))
         per_dev = std::max(1, std::max(4, hw) / n_dev);
+    // staging is bound by the host's memory system, not by the number of links: beyond ~12 copying threads in total the
+    // throughput FALLS (2 GPUs x 8 workers: 1.05e9 evals/s against 1.63e9 for 1 x 8, profiles/r02_host_path_ab_2gpu.txt)
+    if ((job.stage_x || job.stage_res) && n_dev * per_dev > 12 && !std::getenv("BAOBZI_B200_HOST_WORKERS"))
+        per_dev = std::max(1, 12 / n_dev);
     // chunk: 4 Mi points, or less so that every worker gets something
     int64_t chunk = int64_t(1) << 22;
     const int64_t workers_wanted = (int64_t)n_dev * per_dev;
@@ -968,6 +972,10 @@ int baobzi_set_host_devices(baobzi_t func, int n_devices) {
         return 1;
     f->host_devices = n_devices; // 0 = every visible device
     return 0;
+}
+
+int baobzi_b200_guard_check(int64_t *bad_bytes, int64_t *buffers) {
+    return bz::guard_check(bad_bytes, buffers);
 }
 
 int64_t baobzi_launch_count(const baobzi_t func) { return ((Function *)func->obj)->launches.load(); }

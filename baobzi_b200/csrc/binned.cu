@@ -515,13 +515,13 @@ bool binned_supported(int dim, int order) { return (dim == 2 || dim == 3) && ord
 
 // third histogram buffer, second key buffer, the per-CTA base tables, side stream and events of the split sort
 static cudaError_t alloc_split_buffers(BinWorkspace &ws, size_t cwords, int64_t chunk, size_t n_keys) {
-    cudaError_t e = cudaMalloc((void **)&ws.count3, sizeof(uint32_t) * cwords);
+    cudaError_t e = bz_malloc((void **)&ws.count3, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)
         e = cudaMemset(ws.count3, 0, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.alt_key, sizeof(uint32_t) * chunk);
+        e = bz_malloc((void **)&ws.alt_key, sizeof(uint32_t) * chunk);
     for (int h = 0; h < 2 && e == cudaSuccess; ++h)
-        e = cudaMalloc((void **)&ws.base_tbl[h], sizeof(uint32_t) * 2 * (size_t)ws.split_ctas * n_keys); // bases | counts
+        e = bz_malloc((void **)&ws.base_tbl[h], sizeof(uint32_t) * 2 * (size_t)ws.split_ctas * n_keys); // bases | counts
     if (e == cudaSuccess)
         e = cudaStreamCreateWithFlags(&ws.sort_stream, cudaStreamNonBlocking);
     if (e == cudaSuccess)
@@ -682,23 +682,23 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
     }
     if (is2d && !ws.fused)
         return (int)cudaErrorInvalidValue; // the four-kernel fallback sort exists for 3D only
-    cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
+    cudaError_t e = bz_malloc((void **)&ws.key, sizeof(uint32_t) * chunk);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.perm, sizeof(uint32_t) * ws.perm_capacity);
+        e = bz_malloc((void **)&ws.perm, sizeof(uint32_t) * ws.perm_capacity);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.count, sizeof(uint32_t) * cwords);
+        e = bz_malloc((void **)&ws.count, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.cursor, sizeof(uint32_t) * cwords);
+        e = bz_malloc((void **)&ws.cursor, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.cnt, sizeof(uint32_t) * (nl + 1));
+        e = bz_malloc((void **)&ws.cnt, sizeof(uint32_t) * (nl + 1));
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.start, sizeof(uint32_t) * (nl + 1));
+        e = bz_malloc((void **)&ws.start, sizeof(uint32_t) * (nl + 1));
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.tile_leaf, sizeof(uint32_t) * ws.tile_capacity);
+        e = bz_malloc((void **)&ws.tile_leaf, sizeof(uint32_t) * ws.tile_capacity);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.n_tiles, sizeof(uint32_t));
+        e = bz_malloc((void **)&ws.n_tiles, sizeof(uint32_t));
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.tile_info, sizeof(uint2) * ws.tile_capacity);
+        e = bz_malloc((void **)&ws.tile_info, sizeof(uint2) * ws.tile_capacity);
     if (e == cudaSuccess)
         e = cudaMemset(ws.count, 0, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)
@@ -795,26 +795,26 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
             }
             e = alloc_split_buffers(ws, cwords, chunk, (size_t)nl);
             if (e == cudaSuccess && ws.piggy) {
-                e = cudaMalloc((void **)&ws.alt_perm, sizeof(uint32_t) * ws.perm_capacity);
+                e = bz_malloc((void **)&ws.alt_perm, sizeof(uint32_t) * ws.perm_capacity);
                 if (e == cudaSuccess)
-                    e = cudaMalloc((void **)&ws.alt_tile_leaf, sizeof(uint32_t) * ws.tile_capacity);
+                    e = bz_malloc((void **)&ws.alt_tile_leaf, sizeof(uint32_t) * ws.tile_capacity);
                 if (e == cudaSuccess)
-                    e = cudaMalloc((void **)&ws.alt_tile_info, sizeof(uint2) * ws.tile_capacity);
+                    e = bz_malloc((void **)&ws.alt_tile_info, sizeof(uint2) * ws.tile_capacity);
                 if (e == cudaSuccess)
-                    e = cudaMalloc((void **)&ws.alt_n_tiles, sizeof(uint32_t));
+                    e = bz_malloc((void **)&ws.alt_n_tiles, sizeof(uint32_t));
             }
         }
     }
     if (e == cudaSuccess && ws.overlap) {
-        e = cudaMalloc((void **)&ws.alt_key, sizeof(uint32_t) * chunk);
+        e = bz_malloc((void **)&ws.alt_key, sizeof(uint32_t) * chunk);
         if (e == cudaSuccess)
-            e = cudaMalloc((void **)&ws.alt_perm, sizeof(uint32_t) * ws.perm_capacity);
+            e = bz_malloc((void **)&ws.alt_perm, sizeof(uint32_t) * ws.perm_capacity);
         if (e == cudaSuccess)
-            e = cudaMalloc((void **)&ws.alt_tile_leaf, sizeof(uint32_t) * ws.tile_capacity);
+            e = bz_malloc((void **)&ws.alt_tile_leaf, sizeof(uint32_t) * ws.tile_capacity);
         if (e == cudaSuccess)
-            e = cudaMalloc((void **)&ws.alt_tile_info, sizeof(uint2) * ws.tile_capacity);
+            e = bz_malloc((void **)&ws.alt_tile_info, sizeof(uint2) * ws.tile_capacity);
         if (e == cudaSuccess)
-            e = cudaMalloc((void **)&ws.alt_n_tiles, sizeof(uint32_t));
+            e = bz_malloc((void **)&ws.alt_n_tiles, sizeof(uint32_t));
         if (e == cudaSuccess)
             e = cudaStreamCreateWithFlags(&ws.sort_stream, cudaStreamNonBlocking);
         if (e == cudaSuccess)
@@ -834,23 +834,23 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
 }
 
 void free_workspace(BinWorkspace &ws) {
-    cudaFree(ws.key);
-    cudaFree(ws.perm);
-    cudaFree(ws.count);
-    cudaFree(ws.cursor);
-    cudaFree(ws.cnt);
-    cudaFree(ws.start);
-    cudaFree(ws.tile_leaf);
-    cudaFree(ws.n_tiles);
-    cudaFree(ws.tile_info);
-    cudaFree(ws.count3);
-    cudaFree(ws.base_tbl[0]);
-    cudaFree(ws.base_tbl[1]);
-    cudaFree(ws.alt_key);
-    cudaFree(ws.alt_perm);
-    cudaFree(ws.alt_tile_leaf);
-    cudaFree(ws.alt_tile_info);
-    cudaFree(ws.alt_n_tiles);
+    bz_free(ws.key);
+    bz_free(ws.perm);
+    bz_free(ws.count);
+    bz_free(ws.cursor);
+    bz_free(ws.cnt);
+    bz_free(ws.start);
+    bz_free(ws.tile_leaf);
+    bz_free(ws.n_tiles);
+    bz_free(ws.tile_info);
+    bz_free(ws.count3);
+    bz_free(ws.base_tbl[0]);
+    bz_free(ws.base_tbl[1]);
+    bz_free(ws.alt_key);
+    bz_free(ws.alt_perm);
+    bz_free(ws.alt_tile_leaf);
+    bz_free(ws.alt_tile_info);
+    bz_free(ws.alt_n_tiles);
     if (ws.sort_stream)
         cudaStreamDestroy(ws.sort_stream);
     if (ws.ev_begin)
@@ -1209,6 +1209,10 @@ int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x
             return launch_eval_piggy(dt, ws, d_x, d_res, n, stream, launches);
         if (ws.split && n > step)
             return launch_eval_split(dt, ws, d_x, d_res, n, stream, launches);
+        // experiment knob: the two ordinary launches also for a single chunk (no cooperative launch, no grid barrier)
+        static const bool split_single = std::getenv("BAOBZI_B200_SPLIT_SINGLE") && std::atoi(std::getenv("BAOBZI_B200_SPLIT_SINGLE")) != 0;
+        if (ws.split && split_single)
+            return launch_eval_split(dt, ws, d_x, d_res, n, stream, launches);
     }
     if (ws.overlap) { // fork: the side stream may start once everything queued before this call is done
         cudaEventRecord(ws.ev_begin, stream);
@@ -1320,17 +1324,17 @@ int alloc_bucket_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws
     if (rc)
         return rc;
     const size_t cwords = ws.n_keys + 1;
-    cudaError_t e = cudaMalloc((void **)&ws.key, sizeof(uint32_t) * chunk);
+    cudaError_t e = bz_malloc((void **)&ws.key, sizeof(uint32_t) * chunk);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.perm, sizeof(uint32_t) * chunk);
+        e = bz_malloc((void **)&ws.perm, sizeof(uint32_t) * chunk);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.count, sizeof(uint32_t) * cwords);
+        e = bz_malloc((void **)&ws.count, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.cursor, sizeof(uint32_t) * cwords);
+        e = bz_malloc((void **)&ws.cursor, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.n_tiles, 2 * sizeof(uint32_t));
+        e = bz_malloc((void **)&ws.n_tiles, 2 * sizeof(uint32_t));
     if (e == cudaSuccess)
-        e = cudaMalloc((void **)&ws.start, sizeof(uint32_t) * (cwords + 1));
+        e = bz_malloc((void **)&ws.start, sizeof(uint32_t) * (cwords + 1));
     if (e == cudaSuccess)
         e = cudaMemset(ws.count, 0, sizeof(uint32_t) * cwords);
     if (e == cudaSuccess)

@@ -9,14 +9,93 @@
 #include "device_tree.hpp"
 #include "host_tree.hpp"
 
+#include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <vector>
 
 namespace bz {
 
 namespace {
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+constexpr size_t kGuardBytes = 4096;
+constexpr unsigned char kGuardByte = 0xA5;
+struct GuardedBuffer {
+    char *base;
+    size_t bytes; // payload size, rounded up to 256
+    int device;
+};
+std::mutex g_guard_mu;
+std::map<void *, GuardedBuffer> g_guarded; // payload pointer -> allocation
 } // namespace
+
+cudaError_t bz_malloc(void **p, size_t bytes) {
+    static const bool guard = std::getenv("BAOBZI_B200_GUARD") && std::atoi(std::getenv("BAOBZI_B200_GUARD")) != 0;
+    if (!guard)
+        return cudaMalloc(p, bytes);
+    const size_t pay = align_up(bytes ? bytes : 1, 256);
+    char *base = nullptr;
+    cudaError_t e = cudaMalloc((void **)&base, pay + 2 * kGuardBytes);
+    if (e != cudaSuccess)
+        return e;
+    cudaMemset(base, kGuardByte, kGuardBytes);
+    cudaMemset(base + kGuardBytes + bytes, kGuardByte, pay - bytes + kGuardBytes); // the slack behind the payload counts as guard
+    e = cudaDeviceSynchronize();
+    int dev = 0;
+    cudaGetDevice(&dev);
+    *p = base + kGuardBytes;
+    std::lock_guard<std::mutex> lock(g_guard_mu);
+    g_guarded[*p] = GuardedBuffer{base, bytes, dev};
+    return e;
+}
+
+cudaError_t bz_free(void *p) {
+    if (!p)
+        return cudaSuccess;
+    {
+        std::lock_guard<std::mutex> lock(g_guard_mu);
+        auto it = g_guarded.find(p);
+        if (it != g_guarded.end()) {
+            char *base = it->second.base;
+            g_guarded.erase(it);
+            return cudaFree(base);
+        }
+    }
+    return cudaFree(p);
+}
+
+int guard_check(int64_t *bad_bytes, int64_t *buffers) {
+    std::lock_guard<std::mutex> lock(g_guard_mu);
+    int64_t bad = 0;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    cudaError_t e = cudaSuccess;
+    std::vector<unsigned char> host;
+    for (auto &kv : g_guarded) {
+        const GuardedBuffer &g = kv.second;
+        cudaSetDevice(g.device);
+        e = cudaDeviceSynchronize();
+        if (e != cudaSuccess)
+            break;
+        const size_t pay = align_up(g.bytes ? g.bytes : 1, 256), tail = pay - g.bytes + kGuardBytes;
+        host.resize(kGuardBytes + tail);
+        e = cudaMemcpy(host.data(), g.base, kGuardBytes, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess)
+            e = cudaMemcpy(host.data() + kGuardBytes, g.base + kGuardBytes + g.bytes, tail, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess)
+            break;
+        for (unsigned char c : host)
+            bad += c != kGuardByte;
+    }
+    cudaSetDevice(prev);
+    if (bad_bytes)
+        *bad_bytes = bad;
+    if (buffers)
+        *buffers = (int64_t)g_guarded.size();
+    return (int)e;
+}
 
 int upload_tree(const HostTree &h, DeviceTree &out) {
     const int dim = h.dim;

@@ -135,6 +135,14 @@ struct DeviceTree {
     std::vector<double> leaf_coef_1d;
 };
 
+// Device allocations of the evaluation path (sort workspaces, chunk buffers).  With BAOBZI_B200_GUARD=1 in the environment
+// every buffer gets a 4 KB band of a known pattern in front of and behind it; guard_check() reads the bands back and
+// counts the bytes that changed (out-of-bounds writes of any kernel into the neighbourhood of a buffer) -- the pool this
+// was developed on has compute-sanitizer closed, so this is the memory check the GPU test-suite runs instead.
+cudaError_t bz_malloc(void **p, size_t bytes);
+cudaError_t bz_free(void *p);
+int guard_check(int64_t *bad_bytes, int64_t *buffers); // synchronises the device; returns cudaError_t
+
 // flatten + upload to the current device; returns cudaError_t (0 = ok)
 int upload_tree(const HostTree &h, DeviceTree &out);
 void free_tree(DeviceTree &dt);

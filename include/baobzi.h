@@ -179,6 +179,13 @@ int baobzi_tree_info(const baobzi_t func, int64_t info[5]);
  * init / restore.  Returns 0, or 1 for a negative count. */
 int baobzi_set_host_devices(baobzi_t func, int n_devices);
 
+/* Memory check for pools where compute-sanitizer is not available: with BAOBZI_B200_GUARD=1 in the environment when the
+ * library is loaded, every device buffer of the evaluation path (sort workspaces, chunk buffers) is allocated between two
+ * 4 KB bands of a known byte pattern.  This call synchronises, reads all bands back and returns in *bad_bytes how many
+ * bytes changed (out-of-bounds writes next to a buffer) and in *buffers how many buffers are being watched.
+ * Returns 0 or a cudaError_t value. */
+int baobzi_b200_guard_check(int64_t *bad_bytes, int64_t *buffers);
+
 /* Counters for tests / benchmarks: number of kernel launches issued through this handle so far. */
 int64_t baobzi_launch_count(const baobzi_t func);
 

@@ -16,6 +16,20 @@ sys.path.insert(0, ROOT)
 import baobzi_b200  # noqa: E402
 
 G = os.path.join(ROOT, "tests", "golden")
+GUARD = {"bad": 0, "buffers": 0, "checks": 0}
+
+
+def release(b):
+    """Guard-band check (BAOBZI_B200_GUARD=1: every workspace / chunk buffer sits between two 4 KB bands of a known
+    pattern) of everything this handle allocated, then free it."""
+    import ctypes as C
+    bad, n = C.c_int64(0), C.c_int64(0)
+    rc = b._lib.baobzi_b200_guard_check(C.byref(bad), C.byref(n))
+    assert rc == 0, rc
+    GUARD["bad"] += bad.value
+    GUARD["buffers"] = max(GUARD["buffers"], n.value)
+    GUARD["checks"] += 1
+    b.free()
 
 
 def domain(path):
@@ -46,7 +60,7 @@ def extra_cases(rng):
     yh = b(xh)
     os.environ.pop("BAOBZI_B200_STAGE")
     print("staged host path", float(yh[-1]), flush=True)
-    b.free()
+    release(b)
     # 2D points that start on an odd double
     path = os.path.join(G, "t2d_o8.baobzi")
     lo, hi = domain(path)
@@ -58,7 +72,7 @@ def extra_cases(rng):
         y = b(flat[1:].view(50_000, 2))
     torch.cuda.synchronize()
     print("odd-aligned 2D", float(y[-1]), flush=True)
-    b.free()
+    release(b)
     # 3D binned with the four-kernel fallback sort
     os.environ["BAOBZI_B200_FUSED_SORT"] = "0"
     path = os.path.join(G, "t3d_o6.baobzi")
@@ -69,7 +83,7 @@ def extra_cases(rng):
     torch.cuda.synchronize()
     os.environ.pop("BAOBZI_B200_FUSED_SORT")
     print("four-kernel sort", float(y[-1]), flush=True)
-    b.free()
+    release(b)
 
 
 def main():
@@ -82,6 +96,7 @@ def main():
         os.environ["BAOBZI_B200_SORT_SPLIT"] = split
         print("--- BAOBZI_B200_SORT_SPLIT=" + split, flush=True)
         mode_loop(rng, split == "1")
+    print("guard bands: %d checks, up to %d buffers watched at once, %d bytes changed" % (GUARD["checks"], GUARD["buffers"], GUARD["bad"]))
     print("sanitize_paths: done")
 
 
@@ -119,7 +134,7 @@ def mode_loop(rng, binned_only):
                 ya = step("eval_all", lambda: b.eval_all(xd))
             torch.cuda.synchronize()
             print(name, mode, float(y[-1]), float(s), int(idx[-1]), float(np.asarray(yh)[-1]), np.asarray(ys)[0], flush=True)
-            b.free()
+            release(b)
 
 
 if __name__ == "__main__":
