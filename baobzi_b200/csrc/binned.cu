@@ -1211,7 +1211,11 @@ int launch_eval_binned(const DeviceTree &dt, BinWorkspace &ws, const double *d_x
             return launch_eval_split(dt, ws, d_x, d_res, n, stream, launches);
         // experiment knob: the two ordinary launches also for a single chunk (no cooperative launch, no grid barrier)
         static const bool split_single = std::getenv("BAOBZI_B200_SPLIT_SINGLE") && std::atoi(std::getenv("BAOBZI_B200_SPLIT_SINGLE")) != 0;
-        if (ws.split && split_single)
+        // ... and by default in 3D with the coalescing scatter, where they beat the cooperative launch even without a next
+        // chunk to overlap with (C3 tree, 8 M points: 0.509 against 0.530 ms; 2D, 1 M / 4 M points: 0.089 / 0.211 against
+        // 0.079 / 0.198 -- the fork / join of the second stream costs more than the scatter saves; profiles/r02_sweep_i.txt)
+        const bool single3d = dt.view.dim == 3 && ws.split_coal > 0 && n >= (int64_t(1) << 21);
+        if (ws.split && (split_single || single3d))
             return launch_eval_split(dt, ws, d_x, d_res, n, stream, launches);
     }
     if (ws.overlap) { // fork: the side stream may start once everything queued before this call is done
