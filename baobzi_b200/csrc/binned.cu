@@ -88,7 +88,7 @@ constexpr int64_t kSortSplitMinLeaves = 2048;
 constexpr int64_t kSortSplitMinLeaves2D = 128; // split sort (phase A of the next chunk beside the scatter of this one): CTAs per SM and kernel, 0 = off
 constexpr int kSortPts = 4; // independent lookups in flight per thread (the lookup is latency bound, not issue bound)
 
-template <int DIM, bool BYBIN, int PHASE = 0>
+template <int DIM, bool BYBIN, int PHASE = 0, int APTS = kSortPts>
 __global__ void __launch_bounds__(PHASE == 1 ? kSortThreadsA : kSortThreads)
 bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *__restrict__ res,
                       uint32_t *__restrict__ key, uint32_t *__restrict__ count, uint32_t *__restrict__ count_next,
@@ -137,19 +137,20 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
 
     // ---- phase A
     const uint32_t lane_id = tid & 31;
-    for (uint32_t b0 = lo; do_a && b0 < hi; b0 += kSortPts * nthr) { // CTA-uniform trip count: the warps stay converged
+    constexpr int PA = PHASE == 1 ? APTS : kSortPts; // points in flight per thread in the lookup loop
+    for (uint32_t b0 = lo; do_a && b0 < hi; b0 += PA * nthr) { // CTA-uniform trip count: the warps stay converged
         const uint32_t i0 = b0 + tid;
-        double p[kSortPts][DIM];
-        bool have[kSortPts];
+        double p[PA][DIM];
+        bool have[PA];
 #pragma unroll
-        for (int u = 0; u < kSortPts; ++u) {
+        for (int u = 0; u < PA; ++u) {
             const uint32_t i = i0 + u * nthr;
             have[u] = i < hi;
             load_point_keep<DIM>(x, have[u] ? i : lo, p[u]); // default cache policy: K4 gathers these again
         }
-        uint32_t leaf[kSortPts], lin[kSortPts];
+        uint32_t leaf[PA], lin[PA];
 #pragma unroll
-        for (int u = 0; u < kSortPts; ++u) { // all table lookups in flight before any (rare) descent
+        for (int u = 0; u < PA; ++u) { // all table lookups in flight before any (rare) descent
             lin[u] = linear_bin<DIM>(tv, p[u]);
             if (BYBIN) {
                 leaf[u] = lin[u] >> bshift;
@@ -161,7 +162,7 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
             }
         }
 #pragma unroll
-        for (int u = 0; u < kSortPts; ++u) {
+        for (int u = 0; u < PA; ++u) {
             if (!have[u] || outside<DIM>(tv, p[u]))
                 leaf[u] = kNotLeaf;
             else if (!BYBIN && leaf[u] == kNotLeaf)
@@ -169,7 +170,7 @@ bin_sort_fused_kernel(const TreeView tv, const double *__restrict__ x, double *_
         }
         const bool heavy = keys_repeat(leaf[0], lane_id);
 #pragma unroll
-        for (int u = 0; u < kSortPts; ++u) {
+        for (int u = 0; u < PA; ++u) {
             const uint32_t i = i0 + u * nthr;
             // rank of the point inside (this CTA, its leaf): what the histogram update returns (lanes past the end hold kNotLeaf)
             const uint32_t rank = grouped_add(tbl, leaf[u], heavy, lane_id);
@@ -792,6 +793,10 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
                 const void *fa2 = is2d ? (const void *)bin_sort_fused_kernel<2, false, 2> : (const void *)bin_sort_fused_kernel<3, false, 2>;
                 cudaFuncSetAttribute(fa1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
                 cudaFuncSetAttribute(fa2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
+                if (!is2d) { // experiment variants of the lookup launch (BAOBZI_B200_SPLIT_APTS)
+                    cudaFuncSetAttribute(bin_sort_fused_kernel<3, false, 1, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
+                    cudaFuncSetAttribute(bin_sort_fused_kernel<3, false, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFusedSortMaxSmem);
+                }
             }
             e = alloc_split_buffers(ws, cwords, chunk, (size_t)nl);
             if (e == cudaSuccess && ws.piggy) {
@@ -1045,7 +1050,17 @@ static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t ph
     } else if (tv.dim == 2) {
         BZ_SORT_PHASES(2, false);
     } else {
-        BZ_SORT_PHASES(3, false);
+        static const int apts = std::getenv("BAOBZI_B200_SPLIT_APTS") ? std::atoi(std::getenv("BAOBZI_B200_SPLIT_APTS")) : kSortPts;
+        if (phase == 1 && apts == 8)
+            bin_sort_fused_kernel<3, false, 1, 8><<<grid, threads, smem, st>>>(tv, d_x, d_res, key, cur, next, ws.cshift, TILE, ws.perm,
+                                                                              tile_leaf, tile_info, ws.n_tiles, n, 0u, nkeys, bshift,
+                                                                              ws.start, coal, sbin, phase, base);
+        else if (phase == 1 && apts == 2)
+            bin_sort_fused_kernel<3, false, 1, 2><<<grid, threads, smem, st>>>(tv, d_x, d_res, key, cur, next, ws.cshift, TILE, ws.perm,
+                                                                              tile_leaf, tile_info, ws.n_tiles, n, 0u, nkeys, bshift,
+                                                                              ws.start, coal, sbin, phase, base);
+        else
+            BZ_SORT_PHASES(3, false);
     }
 #undef BZ_SORT_PHASES
 #undef BZ_SORT_PHASE
