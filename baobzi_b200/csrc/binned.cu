@@ -786,6 +786,10 @@ int alloc_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws) {
                     const void *fa2 = is2d ? (const void *)bin_sort_fused_kernel<2, false, 2> : (const void *)bin_sort_fused_kernel<3, false, 2>;
                     cudaFuncSetAttribute(fa1, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
                     cudaFuncSetAttribute(fa2, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+                    if (!is2d) { // experiment variants of the lookup launch (BAOBZI_B200_SPLIT_APTS)
+                        cudaFuncSetAttribute(bin_sort_fused_kernel<3, false, 1, 8>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+                        cudaFuncSetAttribute(bin_sort_fused_kernel<3, false, 1, 2>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+                    }
                 }
             }
             {   // trees above ~10 K leaves: the phase launches need more than the 48 KB a kernel gets without opting in
