@@ -51,6 +51,7 @@ ABI = {
     "baobzi_stats": (None, [baobzi_t]),
     "baobzi_free": (baobzi_t, [baobzi_t]),
     "baobzi_eval_multi_device": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "baobzi_eval_multi_device_noalloc": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "baobzi_node_index_multi_device": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "baobzi_node_index_multi": (C.c_int, [baobzi_t, C.c_void_p, C.c_void_p, C.c_int64]),
     "baobzi_eval_multi_sharded": (C.c_int, [baobzi_t, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_void_p),
@@ -71,6 +72,7 @@ ABI = {
     "baobzi_b200_version": (C.c_char_p, []),
 }
 DATA_SYMBOLS = ["baobzi_input_default"]
+NOALLOC_MAX_POINTS, NOALLOC_MAX_LEAVES = 1 << 20, 1 << 16  # include/baobzi.h
 MODES = {"auto": 0, "direct": 1, "binned": 2, "bucketed": 3}
 
 
@@ -235,6 +237,24 @@ class Baobzi:
             raise TypeError("out must be a writeable C-contiguous float64 numpy array with at least one value per point")
         self._lib.baobzi_eval_multi(self.ptr, xarr.ctypes.data, res.ctypes.data, n)
         return res
+
+    def eval_noalloc(self, x, out, stream=None):
+        """baobzi_eval_multi_device_noalloc: x and out are the caller's CUDA float64 arrays; neither this method nor the
+        library call allocates (fixed scratch array in the library; at most NOALLOC_MAX_POINTS points per call, calls
+        that overlap on the GPU race -- see include/baobzi.h).  No counterpart in the reference."""
+        dp, op = _device_pointer(x), _device_pointer(out)
+        if dp is None or op is None:
+            raise TypeError("eval_noalloc takes contiguous CUDA float64 arrays for x and out")
+        n = dp[1] // self.dim
+        if op[1] < n:
+            raise TypeError("out must hold at least one value per point")
+        if stream is None and hasattr(x, "is_cuda"):
+            import torch
+            stream = torch.cuda.current_stream(x.device).cuda_stream
+        rc = self._lib.baobzi_eval_multi_device_noalloc(self.ptr, dp[0], op[0], n, stream or 0)
+        if rc != 0:
+            raise RuntimeError("baobzi_eval_multi_device_noalloc failed with CUDA error %d" % rc)
+        return out
 
     def eval(self, x):
         """One point through baobzi_eval: returns output_dim values."""

@@ -639,6 +639,19 @@ baobzi_t make_handle(std::unique_ptr<Function> f) {
 }
 
 } // namespace
+
+// noalloc.cu (baobzi_eval_multi_device_noalloc): the tree descriptor of the replica on `dev` if there is one.  Never
+// creates a replica, so it never allocates.
+bool find_replica_view(const void *obj, int dev, TreeView *out) {
+    Function *f = (Function *)obj;
+    std::lock_guard<std::mutex> lock(f->mu);
+    for (auto &r : f->replicas)
+        if (r->dt.device == dev) {
+            *out = r->dt.view;
+            return true;
+        }
+    return false;
+}
 } // namespace bz
 
 // ================================================================================================

@@ -126,6 +126,26 @@ baobzi_t baobzi_free(baobzi_t func);
  * size afterwards only enqueue kernels. */
 int baobzi_eval_multi_device(const baobzi_t func, const double *d_x, double *d_res, int64_t ntrg, void *cuda_stream);
 
+/* The same evaluation for callers that may not allocate: code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc.  This entry point has NO counterpart in the reference.
+ * It groups the points by leaf like the binned path, but its scratch (keys, order, histogram) is one
+ * fixed file-scope device array of 8.25 MB (baobzi_b200/csrc/noalloc.cu) that every GPU which loads the library holds
+ * until the process exits, so the call itself makes no cudaMalloc / cudaFree or other allocating call: it enqueues
+ * one memset and four kernels on `cuda_stream` and returns.  d_res[i] equals what baobzi_eval_multi_device writes, bit
+ * for bit (NaN outside the domain).
+ *   limits:  ntrg <= BAOBZI_NOALLOC_MAX_POINTS and a tree of at most BAOBZI_NOALLOC_MAX_LEAVES leaves; anything larger
+ *            is rejected with cudaErrorInvalidValue and a line on stderr (split the batch, or use the entry above);
+ *   set-up:  the handle must already have its replica on the device that owns d_x (baobzi_init / baobzi_restore
+ *            create one on the then-current device; baobzi_device_view creates one anywhere) -- this call never does;
+ *   sharing: ALL calls on one device, from any handle, use the same array, which keeps the last call's contents
+ *            (the call clears what must start at zero).  Calls that overlap on the GPU -- different streams, or
+ *            threads without ordering between them -- race on it: keep them on one stream or order them with events.
+ * Returns 0 or a cudaError_t value. */
+#define BAOBZI_NOALLOC_MAX_POINTS (1 << 20)
+#define BAOBZI_NOALLOC_MAX_LEAVES (1 << 16)
+int baobzi_eval_multi_device_noalloc(const baobzi_t func, const double *d_x, double *d_res, int64_t ntrg,
+                                     void *cuda_stream);
+
 /* All output components of a 1D multi-output tree, batched (extension): d_res[i * OUTPUT_DIM + k] is
  * what baobzi_eval (baobzi.cpp:61 -> template.hpp:851-860, 371-375) writes to y[k] for point i, bit for bit; NaN outside
  * the domain.  baobzi_eval_multi itself keeps the reference's behaviour (first component only).  DIM must be 1
