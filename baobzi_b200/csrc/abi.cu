@@ -231,13 +231,18 @@ bool use_bucketed(const Function *f, const DeviceTree &dt, int64_t n) {
     return dt.blob_bytes > (size_t(48) << 20) && n >= (1 << 20);
 }
 
-int64_t default_bucket_chunk() {
+int64_t default_bucket_chunk(const DeviceTree &dt) {
     if (const char *s = std::getenv("BAOBZI_B200_BCHUNK")) {
         long long v = std::atoll(s);
         if (v > 0)
             return v;
     }
-    return int64_t(1) << 24; // measured best on the 1M-leaf benchmark tree: more points per leaf and chunk
+    // The chunk's points and results (8 (dim + 1) bytes per point) should about fill the 126 MB L2: the evaluation's one
+    // gather and one scatter per point then stay out of DRAM while the tree is streamed once per chunk by the staged kernel
+    // (bucket_stage.cu).  Measured on the 2D 1M-leaf benchmark tree (profiles/r02_sweep_u_c4_chunk_stages.txt): 1.77e10
+    // evals/s at 4 Mi points, 1.91e10 at 5 Mi, 1.94e10 at 5.5 Mi, 1.83e10 at 6 Mi, 1.69e10 at 7 Mi, 1.27e10 at 16 Mi; the
+    // gathering kernel that serves trees the stage cannot hold is flat from 4 Mi to 16 Mi (1.31e10 - 1.32e10).
+    return dt.view.dim <= 2 ? int64_t(11) << 19 : int64_t(1) << 22;
 }
 
 // evaluate n device-resident points on `stream`, chunking the binned path
@@ -270,7 +275,7 @@ int eval_device(Function *f, Replica *r, BinWorkspace &ws, const double *d_x, do
             rc = launch_eval_binned(r->dt, ws, d_x, d_res, n, stream, &launches); // chunks of ws.chunk_capacity
     } else if (!odd && use_bucketed(f, r->dt, n)) {
         const int64_t fc = f->chunk.load();
-        int64_t step = fc > 0 ? fc : default_bucket_chunk();
+        int64_t step = fc > 0 ? fc : default_bucket_chunk(r->dt);
         if (step > n)
             step = n;
         if (ws.chunk_capacity < step || !ws.bucketed) {
@@ -841,7 +846,7 @@ int baobzi_eval_multi_device_dot(const baobzi_t func, const double *d_x, const d
             rc = bz::launch_sum_partials(r->dot_partial, G, d_out, stream, &launches);
     } else { // grouped evaluation chunk by chunk into an L2-sized scratch array, consumed at once
         const int64_t fc = f->chunk.load();
-        int64_t step = fc > 0 ? fc : (binned ? bz::default_chunk(r->dt) : bz::default_bucket_chunk());
+        int64_t step = fc > 0 ? fc : (binned ? bz::default_chunk(r->dt) : bz::default_bucket_chunk(r->dt));
         if (step > ntrg)
             step = ntrg;
         const int64_t n_chunks = (ntrg + step - 1) / step;

@@ -860,6 +860,8 @@ void free_workspace(BinWorkspace &ws) {
     bz_free(ws.alt_tile_leaf);
     bz_free(ws.alt_tile_info);
     bz_free(ws.alt_n_tiles);
+    bz_free(ws.bucket_desc);
+    bz_free(ws.alt_start);
     if (ws.sort_stream)
         cudaStreamDestroy(ws.sort_stream);
     if (ws.ev_begin)
@@ -1003,8 +1005,11 @@ static int launch_chunk_3d(const DeviceTree &dt, BinWorkspace &ws, const double 
 // One phase of the split sort for one chunk (ordinary launch: the kernel never reaches its grid barrier).
 static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t phase, const double *d_x, double *d_res,
                              uint32_t n, uint32_t *key, uint32_t *cur, uint32_t *next, uint32_t *base, cudaStream_t st,
-                             bool full_grid = false) {
+                             bool full_grid = false, int half = 0) {
     const TreeView &tv = dt.view;
+    // half = 1: the scatter fills the second set of output buffers (bucketed path with the sort beside the evaluation)
+    uint32_t *const out_perm = half ? ws.alt_perm : ws.perm, *const out_start = half ? ws.alt_start : ws.start;
+    uint32_t *const out_n_tiles = half ? ws.alt_n_tiles : ws.n_tiles;
     uint32_t grid = (uint32_t)ws.split_ctas;
     const uint32_t per_cta = (uint32_t)kSortThreads * kSortPts;
     const uint32_t useful = (n + per_cta - 1) / per_cta;
@@ -1035,8 +1040,8 @@ static int launch_sort_phase(const DeviceTree &dt, BinWorkspace &ws, uint32_t ph
     const int bshift = bybin ? ws.bshift : 0;
 #define BZ_SORT_PHASE(D, BB, PH)                                                                                     \
     bin_sort_fused_kernel<D, BB, PH><<<grid, threads, smem, st>>>(tv, d_x, d_res, key, cur, next, ws.cshift, TILE,  \
-                                                                  ws.perm, tile_leaf, tile_info, ws.n_tiles, n, 0u,  \
-                                                                  nkeys, bshift, ws.start, coal, sbin, phase, base)
+                                                                  out_perm, tile_leaf, tile_info, out_n_tiles, n, 0u, \
+                                                                  nkeys, bshift, out_start, coal, sbin, phase, base)
 #define BZ_SORT_PHASES(D, BB)                                                                                        \
     do {                                                                                                             \
         if (phase == 1)                                                                                              \
@@ -1112,7 +1117,8 @@ static int launch_eval_split(const DeviceTree &dt, BinWorkspace &ws, const doubl
         if (rc == 0) {
             const double *xc = d_x + dim * c * step;
             double *rcp = d_res + c * step;
-            rc = ws.bucketed ? launch_eval_buckets(dt, xc, rcp, ws.perm, ws.start, ws.n_tiles + 1, ws.n_keys, ws.bshift, stream)
+            rc = ws.bucketed ? (ws.stage_ok ? launch_eval_buckets_staged(dt, ws, xc, rcp, stream)
+                                            : launch_eval_buckets(dt, xc, rcp, ws.perm, ws.start, ws.n_tiles + 1, ws.n_keys, ws.bshift, stream))
                  : dim == 2  ? launch_bin_eval2d(dt, ws, xc, rcp, stream)
                              : launch_bin_eval3d(dt, ws, xc, rcp, stream);
         }
@@ -1122,6 +1128,72 @@ static int launch_eval_split(const DeviceTree &dt, BinWorkspace &ws, const doubl
             pf->spans.push_back({kStageLookup, ev[0], ev[1], (int64_t)m});
             pf->spans.push_back({kStageEval, ev[1], ev[2], (int64_t)m});
         }
+        if (launches)
+            *launches += 3;
+    }
+    ws.rot = (int)((ws.rot + nc) % 3);
+    return rc ? rc : (int)cudaGetLastError();
+}
+
+// Bucketed path with the pipelined staged kernel: BOTH sort launches of chunk c+1 run on the side stream beside the
+// evaluation of chunk c (the evaluation kernel is compiled for two CTAs' worth of registers per SM and uses two stages, so
+// that one sort CTA fits an SM next to it); the scatter writes the second set of perm / key_start buffers.
+static int launch_eval_bucket_overlap(const DeviceTree &dt, BinWorkspace &ws, const double *d_x, double *d_res, int64_t n,
+                                      cudaStream_t stream, int64_t *launches) {
+    const int dim = dt.view.dim;
+    const int64_t step = ws.chunk_limit > 0 && ws.chunk_limit < ws.chunk_capacity ? ws.chunk_limit : ws.chunk_capacity;
+    const int64_t nc = (n + step - 1) / step;
+    uint32_t *hist[3] = {ws.count, ws.cursor, ws.count3};
+    uint32_t *keys[2] = {ws.key, ws.alt_key};
+    cudaStream_t ss = ws.sort_stream;
+    StageProfile *pf = ws.prof;
+    auto chunk_n = [&](int64_t c) { return (uint32_t)(n - c * step < step ? n - c * step : step); };
+    cudaEventRecord(ws.ev_begin, stream);
+    cudaStreamWaitEvent(ss, ws.ev_begin, 0);
+    int rc = 0;
+    auto sort_chunk = [&](int64_t c) {
+        const int h = (int)(c & 1);
+        const uint32_t m = chunk_n(c);
+        const double *xc = d_x + dim * c * step;
+        double *rcp = d_res + c * step;
+        if (c >= 2) // evaluation c - 2 read the buffers this scatter fills
+            cudaStreamWaitEvent(ss, ws.ev_evaluated[h], 0);
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (pf) {
+            e0 = pf->get();
+            e1 = pf->get();
+            cudaEventRecord(e0, ss);
+        }
+        rc = launch_sort_phase(dt, ws, 1, xc, rcp, m, keys[h], hist[(ws.rot + c) % 3], nullptr, ws.base_tbl[h], ss, false, h);
+        if (rc == 0)
+            rc = launch_sort_phase(dt, ws, 2, xc, rcp, m, keys[h], hist[(ws.rot + c) % 3], hist[(ws.rot + c + 2) % 3],
+                                   ws.base_tbl[h], ss, false, h);
+        if (pf) {
+            cudaEventRecord(e1, ss);
+            pf->spans.push_back({kStageLookup, e0, e1, (int64_t)m});
+        }
+        cudaEventRecord(ws.ev_sorted[h], ss);
+    };
+    sort_chunk(0);
+    for (int64_t c = 0; c < nc && rc == 0; ++c) {
+        const int h = (int)(c & 1);
+        if (c + 1 < nc)
+            sort_chunk(c + 1);
+        if (rc)
+            break;
+        cudaStreamWaitEvent(stream, ws.ev_sorted[h], 0);
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (pf) {
+            e0 = pf->get();
+            e1 = pf->get();
+            cudaEventRecord(e0, stream);
+        }
+        rc = launch_eval_buckets_staged(dt, ws, d_x + dim * c * step, d_res + c * step, stream, h);
+        if (pf) {
+            cudaEventRecord(e1, stream);
+            pf->spans.push_back({kStageEval, e0, e1, (int64_t)chunk_n(c)});
+        }
+        cudaEventRecord(ws.ev_evaluated[h], stream);
         if (launches)
             *launches += 3;
     }
@@ -1331,21 +1403,43 @@ int alloc_bucket_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws
     ws.bucketed = true;
     // at most kMaxBuckets buckets of 2^bshift consecutive grid cells (cells are x-fastest, nodes and coefficient
     // blocks are stored cell by cell, so a bucket is one contiguous piece of the tree, small enough for L1)
-    uint64_t max_buckets = 4096;
+    // Bucket count: 8192 when the pipelined staged kernel (bucket_stage.cu) then serves the tree -- three stages of
+    // the > L2 benchmark tree's 48 KB pieces fit an SM; measured 1.76e10 evals/s at 8192 buckets against 1.47e10 for the
+    // one-stage kernel and 1.32e10 for the gathering kernel, whose own best is 4096 (profiles/r02_sweep_*) -- else 4096.
+    // BAOBZI_B200_BUCKETS fixes it.
+    uint64_t candidates[2] = {8192, 4096};
+    int n_cand = 2;
     if (const char *e = std::getenv("BAOBZI_B200_BUCKETS"))
-        if (std::atoll(e) > 0)
-            max_buckets = (uint64_t)std::atoll(e);
-    ws.bshift = 0;
-    while ((((uint64_t)dt.view.n_bins + (1ull << ws.bshift) - 1) >> ws.bshift) > max_buckets)
-        ws.bshift++;
-    ws.n_keys = (uint32_t)(((uint64_t)dt.view.n_bins + (1ull << ws.bshift) - 1) >> ws.bshift);
+        if (std::atoll(e) > 0) {
+            candidates[0] = (uint64_t)std::atoll(e);
+            n_cand = 1;
+        }
+    for (int c = 0; c < n_cand; ++c) {
+        const uint64_t max_buckets = candidates[c];
+        ws.bshift = 0;
+        while ((((uint64_t)dt.view.n_bins + (1ull << ws.bshift) - 1) >> ws.bshift) > max_buckets)
+            ws.bshift++;
+        ws.n_keys = (uint32_t)(((uint64_t)dt.view.n_bins + (1ull << ws.bshift) - 1) >> ws.bshift);
+        const int prc = plan_bucket_stage(dt, ws);
+        if (prc) {
+            free_workspace(ws);
+            return prc;
+        }
+        if ((ws.stage_ok && ws.stage_pipe) || c + 1 == n_cand)
+            break;
+        bz_free(ws.bucket_desc); // the next candidate describes its own buckets
+        ws.bucket_desc = nullptr;
+        ws.stage_ok = false;
+    }
     ws.cshift = 0;
     ws.fused = true;
     int rc = dt.view.dim == 1 ? configure_bucket_sort<1>(dt, ws, chunk)
              : dt.view.dim == 2 ? configure_bucket_sort<2>(dt, ws, chunk)
                                 : configure_bucket_sort<3>(dt, ws, chunk);
-    if (rc)
+    if (rc) {
+        free_workspace(ws);
         return rc;
+    }
     const size_t cwords = ws.n_keys + 1;
     cudaError_t e = bz_malloc((void **)&ws.key, sizeof(uint32_t) * chunk);
     if (e == cudaSuccess)
@@ -1384,6 +1478,8 @@ int alloc_bucket_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws
                 need = need < 32.0 * 1024.0 ? 32.0 * 1024.0 : need;
                 int pct = (int)(100.0 * need / (228.0 * 1024.0)) + 1;
                 pct = pct > 100 ? 100 : pct;
+                if (ws.bucket_overlap) // co-resident with the evaluation kernel, which takes the largest carve-out: an SM
+                    pct = 100;         // only runs CTAs of kernels that agree on the shared-memory / L1 split
                 const void *fa[6] = {(const void *)bin_sort_fused_kernel<1, true, 1>, (const void *)bin_sort_fused_kernel<1, true, 2>,
                                      (const void *)bin_sort_fused_kernel<2, true, 1>, (const void *)bin_sort_fused_kernel<2, true, 2>,
                                      (const void *)bin_sort_fused_kernel<3, true, 1>, (const void *)bin_sort_fused_kernel<3, true, 2>};
@@ -1392,6 +1488,17 @@ int alloc_bucket_workspace(const DeviceTree &dt, int64_t chunk, BinWorkspace &ws
                 cudaFuncSetAttribute(fa[d0 + 1], cudaFuncAttributePreferredSharedMemoryCarveout, pct);
                 e = alloc_split_buffers(ws, cwords, chunk, (size_t)ws.n_keys);
             }
+        }
+    }
+    if (e == cudaSuccess && ws.bucket_overlap) {
+        if (ws.split && ws.stage_ok && ws.stage_pipe) { // second set of scatter outputs
+            e = bz_malloc((void **)&ws.alt_perm, sizeof(uint32_t) * chunk);
+            if (e == cudaSuccess)
+                e = bz_malloc((void **)&ws.alt_start, sizeof(uint32_t) * (cwords + 1));
+            if (e == cudaSuccess)
+                e = bz_malloc((void **)&ws.alt_n_tiles, 2 * sizeof(uint32_t));
+        } else {
+            ws.bucket_overlap = false;
         }
     }
     if (e != cudaSuccess) {
@@ -1411,6 +1518,8 @@ int launch_eval_bucketed(const DeviceTree &dt, BinWorkspace &ws, const double *d
         return (int)cudaErrorInvalidValue;
     const int dim = dt.view.dim;
     const int64_t step = ws.chunk_limit > 0 && ws.chunk_limit < ws.chunk_capacity ? ws.chunk_limit : ws.chunk_capacity;
+    if (ws.split && ws.bucket_overlap && ws.stage_ok && n > step)
+        return launch_eval_bucket_overlap(dt, ws, d_x, d_res, n, stream, launches);
     if (ws.split && n > step)
         return launch_eval_split(dt, ws, d_x, d_res, n, stream, launches);
     StageProfile *pf = ws.prof;
@@ -1431,7 +1540,8 @@ int launch_eval_bucketed(const DeviceTree &dt, BinWorkspace &ws, const double *d
         if (pf)
             cudaEventRecord(ev[1], stream);
         if (rc == 0)
-            rc = launch_eval_buckets(dt, xc, rcp, ws.perm, ws.start, ws.n_tiles + 1, ws.n_keys, ws.bshift, stream);
+            rc = ws.stage_ok ? launch_eval_buckets_staged(dt, ws, xc, rcp, stream)
+                             : launch_eval_buckets(dt, xc, rcp, ws.perm, ws.start, ws.n_tiles + 1, ws.n_keys, ws.bshift, stream);
         if (pf) {
             cudaEventRecord(ev[2], stream);
             pf->spans.push_back({kStageLookup, ev[0], ev[1], (int64_t)m});

@@ -82,6 +82,17 @@ struct BinWorkspace {
     bool bucketed = false;      // workspace of the bucketed path (alloc_bucket_workspace)
     uint32_t n_keys = 0;        // buckets
     int bshift = 0;             // bucket = grid cell >> bshift
+    // evaluation with the bucket's nodes + coefficient blocks staged in shared memory by TMA (bucket_stage.cu)
+    bool stage_ok = false;
+    int stage_sorted = 1; // CTA-local order of a bucket's points: 1 by leaf, 2 by grid cell
+    int stage_pipe = 0;   // stages of the pipelined kernel (2 or 3), 0 = the queue kernel with one stage
+    bool stage_minb2 = false;    // the pipelined kernel's 64-register instantiation (leaves room for a sort CTA)
+    bool bucket_overlap = false; // both sort launches of chunk c+1 beside the evaluation of chunk c (binned.cu)
+    uint32_t *alt_start = nullptr;
+    uint4 *bucket_desc = nullptr; // [n_keys] {first node, nodes, first coefficient unit (16 B), units}
+    int stage_grid = 0;
+    size_t stage_smem = 0;
+    uint32_t stage_tree_cap = 0, stage_hist_cap = 0, stage_meta_cap = 0;
     bool overlap = false, sort_overlap_ok = false;
     int sort_threads = 0;
     cudaStream_t sort_stream = nullptr;
@@ -182,6 +193,11 @@ int launch_eval_bucketed(const DeviceTree &dt, BinWorkspace &ws, const double *d
                          cudaStream_t stream, int64_t *launches);
 int launch_eval_buckets(const DeviceTree &dt, const double *d_x, double *d_res, const uint32_t *d_perm,
                         const uint32_t *d_key_start, uint32_t *d_queue, uint32_t n_keys, int bshift, cudaStream_t stream);
+// ... the same with each bucket's piece of the tree staged in shared memory (bucket_stage.cu); plan_bucket_stage decides
+// per workspace whether it applies (ws.stage_ok)
+int plan_bucket_stage(const DeviceTree &dt, BinWorkspace &ws);
+int launch_eval_buckets_staged(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res,
+                               cudaStream_t stream, int half = 0);
 int launch_eval_perm(const DeviceTree &dt, const double *d_x, double *d_res, const uint32_t *d_perm,
                      const uint32_t *d_n_slots, int64_t n_max, cudaStream_t stream);
 // Evaluation fused with a reduction (reduce.cu): per-CTA partial sums of w_i * f(x_i) (d_w may be null), dot_grid(dt)

@@ -329,7 +329,10 @@ eval_sorted_1d_kernel(const TreeView tv, const U1Coef cf, const double *__restri
 // coefficient and point: two 32-bit selects (ALU pipe) + DADD + DFMA (FP64 pipe), the two pipes evenly loaded, against
 // 8 bytes of shared-memory write-back in the table kernel.  Same operations in the same order as cheb_eval_1d, so the
 // same bits.  Streaming structure of the table kernel: P loads per thread in flight, L2 bulk prefetch two tiles ahead.
-template <int ORDER, int P>
+// PF: the next tile's points are loaded into registers before the current tile's recurrences start (the four warps of a
+// scheduler otherwise all sit in the load at the top of a tile at times: long-scoreboard 1.26 per issue in
+// profiles/r02_twoleaf1d_ncu_summary.json).
+template <int ORDER, int P, bool PF>
 __global__ void __launch_bounds__(256, 2)
 eval_two_leaf_1d_kernel(const TreeView tv, const U1Coef cf, const double *__restrict__ x, double *__restrict__ res,
                         int64_t n, int64_t n_tiles) {
@@ -358,10 +361,22 @@ eval_two_leaf_1d_kernel(const TreeView tv, const U1Coef cf, const double *__rest
         cb[k] = cf.c[1][k];
         asm volatile("" : "+d"(ca[k]), "+d"(cb[k]));
     }
+    auto load_tile = [&](int64_t t, double (&dst)[P]) {
+        const int64_t b0 = t * tile_pts;
+        const bool whole = b0 + tile_pts <= n;
+#pragma unroll
+        for (int j = 0; j < P; ++j) {
+            const int64_t i = b0 + (int64_t)j * blockDim.x + threadIdx.x;
+            dst[j] = whole || i < n ? __ldcs(x + i) : lo;
+        }
+    };
+    double xn[P];
+    if (PF && (int64_t)blockIdx.x < n_tiles)
+        load_tile(blockIdx.x, xn);
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int64_t base = tile * tile_pts;
         if (threadIdx.x == 0) {
-            const int64_t ahead = tile + 2 * (int64_t)gridDim.x;
+            const int64_t ahead = tile + (PF ? 3 : 2) * (int64_t)gridDim.x;
             if (ahead + 1 < n_tiles) {
                 const uintptr_t a = (reinterpret_cast<uintptr_t>(x + ahead * tile_pts) + 15) & ~uintptr_t(15);
                 prefetch_l2_bulk(reinterpret_cast<const void *>(a), (uint32_t)(tile_pts * 8));
@@ -370,10 +385,14 @@ eval_two_leaf_1d_kernel(const TreeView tv, const U1Coef cf, const double *__rest
         const bool full = base + tile_pts <= n; // CTA uniform: whole tiles carry no per-point guards, so that the P
                                                 // recurrences stay interleaved instead of sinking into P branches
         double xv[P];
+        if (PF) {
 #pragma unroll
-        for (int j = 0; j < P; ++j) {
-            const int64_t i = base + (int64_t)j * blockDim.x + threadIdx.x;
-            xv[j] = full || i < n ? __ldcs(x + i) : lo;
+            for (int j = 0; j < P; ++j)
+                xv[j] = xn[j];
+            if (tile + gridDim.x < n_tiles)
+                load_tile(tile + gridDim.x, xn);
+        } else {
+            load_tile(tile, xv);
         }
         double u[P], u2[P], c0[P], c1[P];
         bool out[P], second[P];
@@ -421,6 +440,9 @@ eval_two_leaf_1d_kernel(const TreeView tv, const U1Coef cf, const double *__rest
     }
 }
 
+constexpr int kTwoLeafDefault = 41; // P = 4 with the register prefetch: 2.28e11 evals/s on the two-leaf order-16 tree against
+                                    // 1.99e11 without, 2.18e11 for P = 5 or 3 with it (profiles/r02_sweep_o.txt)
+
 static bool two_leaf_1d_fits(const DeviceTree &dt) {
     if (const char *e = std::getenv("BAOBZI_B200_TWOLEAF1D"))
         if (std::atoi(e) == 0)
@@ -430,14 +452,10 @@ static bool two_leaf_1d_fits(const DeviceTree &dt) {
            tv.n_bins <= (uint32_t)kU1MaxBins && dt.leaf_coef_1d.size() == (size_t)tv.n_leaves * tv.order;
 }
 
-template <int ORDER>
-static int launch_two_leaf_order(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream) {
-    constexpr int P = 4;
-    U1Coef cf;
-    for (int l = 0; l < kU1MaxLeaves; ++l)
-        for (int k = 0; k < 16; ++k) // a one-leaf tree: both candidates are the same block
-            cf.c[l][k] = k < ORDER && l < 2 ? dt.leaf_coef_1d[(size_t)((uint32_t)l < dt.view.n_leaves ? l : 0) * ORDER + k] : 0.0;
-    auto kern = eval_two_leaf_1d_kernel<ORDER, P>;
+template <int ORDER, int P, bool PF>
+static int launch_two_leaf_variant(const DeviceTree &dt, const U1Coef &cf, const double *d_x, double *d_res, int64_t n,
+                                   cudaStream_t stream) {
+    auto kern = eval_two_leaf_1d_kernel<ORDER, P, PF>;
     int per_sm = 0;
     cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, 0);
     if (e != cudaSuccess)
@@ -451,6 +469,24 @@ static int launch_two_leaf_order(const DeviceTree &dt, const double *d_x, double
         grid = n_tiles;
     kern<<<(unsigned)grid, 256, 0, stream>>>(dt.view, cf, d_x, d_res, n, n_tiles);
     return (int)cudaGetLastError();
+}
+
+template <int ORDER>
+static int launch_two_leaf_order(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream) {
+    constexpr int P = 4;
+    U1Coef cf;
+    for (int l = 0; l < kU1MaxLeaves; ++l)
+        for (int k = 0; k < 16; ++k) // a one-leaf tree: both candidates are the same block
+            cf.c[l][k] = k < ORDER && l < 2 ? dt.leaf_coef_1d[(size_t)((uint32_t)l < dt.view.n_leaves ? l : 0) * ORDER + k] : 0.0;
+    // BAOBZI_B200_TWOLEAF1D_VARIANT = 10 * P + PF (experiments; the default is the measured best)
+    static const int variant = std::getenv("BAOBZI_B200_TWOLEAF1D_VARIANT") ? std::atoi(std::getenv("BAOBZI_B200_TWOLEAF1D_VARIANT")) : kTwoLeafDefault;
+    switch (variant) {
+    case 41: return launch_two_leaf_variant<ORDER, 4, true>(dt, cf, d_x, d_res, n, stream);
+    case 50: return launch_two_leaf_variant<ORDER, 5, false>(dt, cf, d_x, d_res, n, stream);
+    case 51: return launch_two_leaf_variant<ORDER, 5, true>(dt, cf, d_x, d_res, n, stream);
+    case 31: return launch_two_leaf_variant<ORDER, 3, true>(dt, cf, d_x, d_res, n, stream);
+    default: return launch_two_leaf_variant<ORDER, P, false>(dt, cf, d_x, d_res, n, stream);
+    }
 }
 
 static int launch_eval_two_leaf_1d(const DeviceTree &dt, const double *d_x, double *d_res, int64_t n, cudaStream_t stream) {

@@ -146,6 +146,81 @@ def test_bucketed_on_refined_tree(gpu_lib, ref):
     b.free()
 
 
+STAGED = [("osc_2d", 1), ("osc_2d", 7), ("osc_2d", 64), ("osc_2d", 4096), ("aniso_2d", 16), ("t2d_o6", 2), ("t2d_o8", 16),
+          ("t2d_o12", 5), ("t2d_o16", 4096), ("tc_2d", 8), ("t3d_o6", 4), ("t3d_o8", 64), ("t3d_o10", 4096)]
+
+
+@pytest.mark.parametrize("name,buckets", STAGED)
+def test_bucket_stage_tma(gpu_lib, ref, name, buckets, monkeypatch):
+    """Bucketed path with each bucket's nodes + coefficient blocks staged in shared memory by cp.async.bulk
+    (bucket_stage.cu; BAOBZI_B200_BUCKET_STAGE=2 makes a workspace that cannot use it an error): the oracle's bits, and
+    the bits of the gathering kernel (STAGE=0), for buckets of one to many grid cells, one chunk and several, many
+    batches per bucket, points outside the domain, NaN coordinates."""
+    import torch
+    from conftest import load_golden
+    from test_parity_gpu import ulp
+    path, g = load_golden(name)
+    t = ref.OracleTree(path)
+    a = t.arrays()
+    rng = np.random.default_rng(buckets)
+    n = 300_017
+    x = a["lower_left"] + rng.random((n, t.dim)) * (a["upper_right"] - a["lower_left"]) * 1.01 - 0.005
+    x[::1013, 0] = np.nan
+    want = t.eval_multi(x, ref.ARITH_AVX2)
+    xd = torch.from_numpy(x).cuda()
+    monkeypatch.setenv("BAOBZI_B200_BUCKETS", str(buckets))
+    got = {}
+    # (stage, CTA-local order: by grid cell / by leaf / the workspace's choice, stages of the pipelined kernel or 0 = queue kernel)
+    # ... "ov": both sort launches of chunk c+1 on a side stream beside the evaluation of chunk c (2D; needs the split sort)
+    for stage, order, pipe in (("2", "2", "3"), ("2", "1", "3"), ("2", "2", "2"), ("2", "1", "2"), ("2", "2", "0"),
+                               ("2", "1", "0"), ("2", None, None), ("2", None, "ov"), ("0", None, None)):
+        monkeypatch.setenv("BAOBZI_B200_BUCKET_STAGE", stage)
+        ov = pipe == "ov"
+        pipe = None if ov else pipe
+        for var, val in (("BAOBZI_B200_BUCKET_SORT", order), ("BAOBZI_B200_BUCKET_PIPE", pipe),
+                         ("BAOBZI_B200_BUCKET_OVERLAP", "1" if ov else "0"), ("BAOBZI_B200_SORT_SPLIT", "1" if ov else None)):
+            if val is None:
+                monkeypatch.delenv(var, raising=False)
+            else:
+                monkeypatch.setenv(var, val)
+        b = gpu_lib.Baobzi(filename=path, mode="bucketed")
+        for chunk in (0, 65_537, 30_011):
+            b.set_mode("bucketed", chunk)
+            y = b(xd)
+            torch.cuda.synchronize()
+            assert ulp(ref, y.cpu().numpy(), want) == 0, (name, buckets, stage, order, pipe, ov, chunk)
+            got[(stage, order, "ov" if ov else pipe, chunk)] = y
+        b.free()
+    assert torch.equal(got[("2", "2", "3", 0)].view(torch.int64), got[("0", None, None, 0)].view(torch.int64))
+
+
+def test_bucket_stage_falls_back_when_a_bucket_does_not_fit(gpu_lib, ref, monkeypatch):
+    """Two buckets of 256 KB of coefficients each exceed the stage: the workspace keeps the gathering kernel (same bits),
+    and asking for the stage explicitly (=2) is an error instead."""
+    import torch
+    from conftest import load_golden
+    from test_parity_gpu import ulp
+    path, g = load_golden("aniso_2d")
+    t = ref.OracleTree(path)
+    a = t.arrays()
+    rng = np.random.default_rng(2)
+    x = a["lower_left"] + rng.random((100_000, 2)) * (a["upper_right"] - a["lower_left"])
+    want = t.eval_multi(x, ref.ARITH_AVX2)
+    xd = torch.from_numpy(x).cuda()
+    monkeypatch.setenv("BAOBZI_B200_BUCKETS", "2")
+    monkeypatch.setenv("BAOBZI_B200_BUCKET_STAGE", "1")
+    b = gpu_lib.Baobzi(filename=path, mode="bucketed")
+    y = b(xd)
+    torch.cuda.synchronize()
+    assert ulp(ref, y.cpu().numpy(), want) == 0
+    b.free()
+    monkeypatch.setenv("BAOBZI_B200_BUCKET_STAGE", "2")
+    b = gpu_lib.Baobzi(filename=path, mode="bucketed")
+    with pytest.raises(RuntimeError):
+        b(xd)
+    b.free()
+
+
 def test_eval_all_multi_output_1d(gpu_lib, ref):
     """baobzi_eval_multi_device_all: row i == what baobzi_eval writes for point i (every output component), and
     column 0 == baobzi_eval_multi; NaN rows outside the domain; not supported for DIM > 1."""
