@@ -49,7 +49,8 @@ WORKLOADS = {
     "C3": dict(desc="3D order 8, testfun_3d tol 1e-12 (baobzi_timing.c:195-208)", func="bench_fun_3d", dim=3, order=8,
                tol=1e-12, center=[1.5, 3.0, 1.5], hl=[1.0, 1.0, 1.0], data=None, points=1_000_000_000),
     "C4": dict(desc="2D order 6 oscillatory 2+sin(20x)cos(20y), tol 1e-10, coefficients > L2", func="bench_fun_2d_osc",
-               dim=2, order=6, tol=1e-10, center=[0.0, 0.0], hl=[1.0, 1.0], data=20.0, points=1_000_000_000),
+               dim=2, order=6, tol=1e-10, center=[0.0, 0.0], hl=[1.0, 1.0], data=20.0, points=1_000_000_000,
+               bucketed=True),
     "C5": dict(desc="3D order 12, testfun_3d tol 1e-12", func="bench_fun_3d", dim=3, order=12, tol=1e-12,
                center=[1.5, 3.0, 1.5], hl=[1.0, 1.0, 1.0], data=None, points=1_000_000_000),
 }
@@ -91,12 +92,14 @@ def git_head():
         return None
 
 
-def ncu_traffic(stage, dim, points_per_launch):
+def ncu_traffic(stage, dim, points_per_launch, bucketed=False):
     """DRAM bytes per launch of a kernel from the newest committed `ncu --set full` summary under profiles/, scaled to
     this run's points per launch.  Returns (bytes or None, provenance string): the summary carries a `_meta` record
     (git hash of the build that was profiled, points per profiled launch) written by scripts/ncu_summary.py."""
     pat = {("eval_grouped", 3): "*_k4_ncu_summary.json", ("eval_grouped", 2): "*_eval2d_ncu_summary.json",
            ("sort", 3): "*_sort_fused_ncu_summary.json", ("eval_direct", 1): "*_eval1d_ncu_summary.json"}.get((stage, dim))
+    if bucketed:  # trees larger than L2 (C4): the pipelined staged kernel of csrc/bucket_stage.cu
+        pat = "*_bucket_pipe_ncu_summary.json" if stage == "eval_grouped" else None
     if not pat:
         return None, None
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", pat)))
@@ -440,7 +443,7 @@ def stage_rooflines(ctx, cfg, stages, steps):
                         "algorithmic_flops_per_eval": flops_per_eval(dim, order),
                         "algorithmic_bytes_per_eval": bytes_per_eval(dim),
                         "hbm_gbs_achieved": gb, "hbm_frac": f_hbm, "fp64_tflops_achieved": tf, "fp64_frac": f_fp})
-        traffic, src = ncu_traffic(name, dim, pts)
+        traffic, src = ncu_traffic(name, dim, pts, bucketed=bool(cfg.get("bucketed")))
         rec["traffic"] = traffic
         if src:
             rec["traffic_source"] = src
