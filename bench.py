@@ -443,6 +443,13 @@ def stage_rooflines(ctx, cfg, stages, steps):
                         "algorithmic_flops_per_eval": flops_per_eval(dim, order),
                         "algorithmic_bytes_per_eval": bytes_per_eval(dim),
                         "hbm_gbs_achieved": gb, "hbm_frac": f_hbm, "fp64_tflops_achieved": tf, "fp64_frac": f_fp})
+        if cfg.get("bucketed") and name.startswith("eval"):
+            # a tree larger than L2 is reported against both byte models -- 8 (DIM + 1) B per evaluation
+            # (ideal: every coefficient block read once per chunk) and that plus one block gather per evaluation
+            blk = 8 * order ** dim
+            gb2 = (bytes_per_eval(dim) + blk) * pts / per_launch_s / 1e9
+            rec["one_block_gather_per_eval"] = {"bytes_per_eval": bytes_per_eval(dim) + blk, "hbm_gbs": gb2,
+                                                "hbm_frac": gb2 / ctx.hbm_peak}
         traffic, src = ncu_traffic(name, dim, pts, bucketed=bool(cfg.get("bucketed")))
         rec["traffic"] = traffic
         if src:

@@ -94,3 +94,20 @@ def test_product_arm_refuses_to_run_without_a_gpu():
     assert r.returncode != 0
     assert r.stdout.strip() == ""                       # no JSON line: nothing was measured
     assert "CUDA" in r.stderr or "cuda" in r.stderr
+
+
+def test_tree_larger_than_l2_is_reported_against_both_byte_models():
+    """C4 reports the ideal 8 (DIM + 1) B per evaluation AND that plus one coefficient-block gather per
+    evaluation; its `traffic` comes from the ncu capture of the kernel that serves it (csrc/bucket_stage.cu)."""
+    import bench
+
+    class Ctx:
+        hbm_peak, hbm_src, fp64_peak = 6542.7, "test", 36.8
+    stages = {"sort": (12.6, 156, 9e8), "eval_grouped": (33.3, 156, 9e8)}
+    r = bench.stage_rooflines(Ctx(), dict(bench.WORKLOADS["C4"]), stages, 3)["eval_grouped"]
+    assert r["bound"] == "hbm" and r["algorithmic_bytes_per_eval"] == 24
+    g = r["one_block_gather_per_eval"]
+    assert g["bytes_per_eval"] == 24 + 8 * 36 and abs(g["hbm_frac"] / r["hbm_frac"] - 312 / 24) < 1e-9
+    assert "bucket_pipe" in r["traffic_source"] and r["traffic"] > 0
+    c1 = bench.stage_rooflines(Ctx(), dict(bench.WORKLOADS["C1"]), stages, 3)["eval_grouped"]
+    assert "one_block_gather_per_eval" not in c1 and "bucket_pipe" not in (c1.get("traffic_source") or "")
