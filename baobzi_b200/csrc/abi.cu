@@ -214,6 +214,12 @@ bool use_binned(const Function *f, const DeviceTree &dt, int64_t n) {
     const int64_t block_bytes = 8 * (int64_t)std::pow((double)dt.view.order, dt.view.dim);
     if (dt.view.dim == 2) // every lane gathering its own block is bound by the L1 tag rate at any block size
         return n >= 64 * (int64_t)dt.view.n_leaves && n >= (1 << 19); // measured crossover (C1 tree): 0.25-1 M points
+    // 3D trees far larger than L2 with so many leaves that a chunk holds only a handful of points per leaf: the evaluation
+    // tiles are mostly padding and the four-kernel sort scans a huge histogram; the bucketed path is ahead there (order 6,
+    // 997 K leaves, 1.8 GB: 5.0e9 against 3.7e9 evals/s; at 249 K leaves / 449 MB the binned path still wins, 8.4e9 against
+    // 6.2e9; profiles/r02_sweep_z_3d_tree_larger_than_l2.txt)
+    if (mode == kAuto && dt.blob_bytes > (size_t(48) << 20) && default_chunk(dt) < 32 * (int64_t)dt.view.n_leaves)
+        return false;
     // 3D, measured crossover: 16 points per leaf (4096-leaf order-8 tree: 65 Ki points, 0.071 ms against 0.080 ms direct;
     // 2x ahead at 128 Ki), and from 16 Ki points on trees with few leaves (order 12: 0.038 against 0.069 ms)
     return block_bytes >= 1024 && n >= 16 * (int64_t)dt.view.n_leaves && n >= (1 << 14);

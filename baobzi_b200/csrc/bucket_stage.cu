@@ -701,6 +701,11 @@ int plan_bucket_stage(const DeviceTree &dt, BinWorkspace &ws) {
     if (rc)
         return rc;
     ws.stage_ok = ws.stage_grid > 0;
+    // The one-stage kernel lives off the other CTAs of its SM: with fewer than three of them it is behind the gathering
+    // kernel (2D 1 M-leaf tree, 95 KB stages, two CTAs per SM: 1.11e10 - 1.18e10 against 1.32e10; 3D 249 K-leaf tree, 105 KB
+    // stages, one CTA: 4.8e9 against 6.2e9), with three it is ahead (1.47e10 - 1.53e10).
+    if (ws.stage_ok && !ws.stage_pipe && !required && ws.stage_grid < 3 * dt.sm_count)
+        ws.stage_ok = false;
     if (!ws.stage_ok || ws.stage_pipe != 2)
         ws.bucket_overlap = false;
     return 0;
