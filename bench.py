@@ -97,7 +97,9 @@ def ncu_traffic(stage, dim, points_per_launch, bucketed=False):
     this run's points per launch.  Returns (bytes or None, provenance string): the summary carries a `_meta` record
     (git hash of the build that was profiled, points per profiled launch) written by scripts/ncu_summary.py."""
     pat = {("eval_grouped", 3): "*_k4_ncu_summary.json", ("eval_grouped", 2): "*_eval2d_ncu_summary.json",
-           ("sort", 3): "*_sort_fused_ncu_summary.json", ("eval_direct", 1): "*_eval1d_ncu_summary.json"}.get((stage, dim))
+           ("sort", 3): "*_sort_fused_ncu_summary.json",
+           # 1D: the two-leaf kernel serves C2 (captured before its register prefetch: same loads and stores)
+           ("eval_direct", 1): "*_twoleaf1d_ncu_summary.json"}.get((stage, dim))
     if bucketed:  # trees larger than L2 (C4): the pipelined staged kernel of csrc/bucket_stage.cu
         pat = "*_bucket_pipe_ncu_summary.json" if stage == "eval_grouped" else None
     if not pat:
