@@ -97,7 +97,7 @@ def ncu_traffic(stage, dim, points_per_launch, bucketed=False):
     this run's points per launch.  Returns (bytes or None, provenance string): the summary carries a `_meta` record
     (git hash of the build that was profiled, points per profiled launch) written by scripts/ncu_summary.py."""
     pat = {("eval_grouped", 3): "*_k4_ncu_summary.json", ("eval_grouped", 2): "*_eval2d_ncu_summary.json",
-           ("sort", 3): "*_sort_fused_ncu_summary.json",
+           ("sort", 3): "*_sort_split_coal_ncu_summary.json",  # both launches of the split sort: summed
            # 1D: the two-leaf kernel serves C2 (captured before its register prefetch: same loads and stores)
            ("eval_direct", 1): "*_twoleaf1d_ncu_summary.json"}.get((stage, dim))
     if bucketed:  # trees larger than L2 (C4): the pipelined staged kernel of csrc/bucket_stage.cu
@@ -111,11 +111,14 @@ def ncu_traffic(stage, dim, points_per_launch, bucketed=False):
     try:
         recs = json.load(open(files[-1]))
         meta = next((r["_meta"] for r in recs if "_meta" in r), None)
-        rec = next(r for r in recs if "dram__bytes_read.sum" in r)
+        kernels = [r for r in recs if "dram__bytes_read.sum" in r]
+        if stage != "sort":  # one kernel per stage, except the sort (lookup launch + scatter launch of one chunk)
+            kernels = kernels[:1]
         tot = 0.0
-        for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-            v, u = rec[k].split()
-            tot += float(v) * unit[u]
+        for rec in kernels:
+            for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                v, u = rec[k].split()
+                tot += float(v) * unit[u]
         if meta and meta.get("points_per_launch"):
             captured, src = float(meta["points_per_launch"]), "git %s" % meta.get("git")
         else:  # round-1 captures (scripts/gpu_round.sh of commit 075c245: 32 Mi points = 4 launches)
