@@ -36,6 +36,22 @@ constexpr int kMaxDevices = 64;
 __device__ __forceinline__ void cp_async8(void *smem, const void *gmem) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
 }
+// Experiment (BAOBZI_B200_K4_EVICT=1): the gathered points and the slot indices are read once per chunk and the chunk is
+// larger than L2; marked evict-first they should leave the result sectors (four scattered 8-byte stores each) and the
+// coefficient blocks alone.  The flag lives in device memory so that no kernel signature changes for it.
+__device__ int g_k4_evict_first = 0;
+__device__ __forceinline__ uint64_t gather_policy() {
+    uint64_t pol;
+    if (g_k4_evict_first)
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    else
+        asm volatile("createpolicy.fractional.L2::evict_normal.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void cp_async8_hint(void *smem, const void *gmem, uint64_t pol) {
+    asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 8, %2;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)),
+                 "l"(gmem), "l"(pol));
+}
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem));
 }
@@ -220,12 +236,14 @@ bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__res
     auto idx_of = [&](int st) -> uint32_t * { return RUN ? rs.idx[st] : stages[st].idx; };
 
     // descriptor of a tile: {node, coeff16} + the P slot indices of this lane
+    const uint64_t pol = gather_policy();
     auto load_meta = [&](uint32_t tt, uint2 &info, uint32_t (&id)[P]) {
         if (tt < t_end) {
             info = __ldg(tile_info + tt);
 #pragma unroll
             for (int p = 0; p < P; ++p)
-                id[p] = __ldg(perm + (size_t)tt * TILE + p * 32 + lane);
+                id[p] = g_k4_evict_first ? __ldcs(perm + (size_t)tt * TILE + p * 32 + lane)
+                                         : __ldg(perm + (size_t)tt * TILE + p * 32 + lane);
         } else {
             info = make_uint2(0, 0);
 #pragma unroll
@@ -252,9 +270,9 @@ bin_eval3d_kernel(const TreeView tv, const double *__restrict__ x, double *__res
                 sidxs[p * 32 + lane] = id[p];
                 if (id[p] != kInvalidSlotE) {
                     const double *q = x + 3ull * id[p];
-                    cp_async8(&pts[0 * TILE + p * 32 + lane], q);
-                    cp_async8(&pts[1 * TILE + p * 32 + lane], q + 1);
-                    cp_async8(&pts[2 * TILE + p * 32 + lane], q + 2);
+                    cp_async8_hint(&pts[0 * TILE + p * 32 + lane], q, pol);
+                    cp_async8_hint(&pts[1 * TILE + p * 32 + lane], q + 1, pol);
+                    cp_async8_hint(&pts[2 * TILE + p * 32 + lane], q + 2, pol);
                 }
             }
         }
@@ -1250,6 +1268,19 @@ bool bin_eval_footprint(int variant, int *cta_regs, size_t *cta_smem) {
 }
 
 int launch_bin_eval3d(const DeviceTree &dt, const BinWorkspace &ws, const double *d_x, double *d_res, cudaStream_t st) {
+    { // experiment knob, read per call (tests flip it); the device copy of the flag is updated when it changes
+        static int on_device[64] = {};
+        const char *ev = std::getenv("BAOBZI_B200_K4_EVICT");
+        const int evict = ev && std::atoi(ev) != 0 ? 1 : 0;
+        const int d = dt.device >= 0 && dt.device < 64 ? dt.device : 0;
+        if (evict != on_device[d]) {
+            static int values[2] = {0, 1};
+            cudaError_t e = cudaMemcpyToSymbolAsync(g_k4_evict_first, &values[evict], sizeof(int), 0, cudaMemcpyHostToDevice, st);
+            if (e != cudaSuccess)
+                return (int)e;
+            on_device[d] = evict;
+        }
+    }
     if (ws.variant < 0 || ws.variant >= (int)(sizeof(kVariants) / sizeof(kVariants[0])) ||
         kVariants[ws.variant].order != dt.view.order)
         return (int)cudaErrorInvalidValue;

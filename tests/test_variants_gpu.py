@@ -25,6 +25,7 @@ VARIANTS = [
     {"BAOBZI_B200_K4": "4,8,1,1,1"},         # T(z) advanced on the fly
     {"BAOBZI_B200_K4": "3,12,1,1,1"},
     {"BAOBZI_B200_K4": "4,12,1,0,1"},
+    {"BAOBZI_B200_K4_EVICT": "1"},           # L2 evict-first hint on the gathered points and slot indices
 ]
 
 
